@@ -1,0 +1,162 @@
+"""CPU tests of the oracle itself: the restatement must reproduce every
+known-answer fact the reference tree holds for this path."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import descriptor as D
+from oracle import hpsi_ref as R
+
+
+@pytest.fixture(scope="module")
+def kat(golden_dir):
+    return json.load(open(os.path.join(golden_dir, "fft_test0.json")))
+
+
+@pytest.fixture(scope="module")
+def kat_desc(kat):
+    A = np.array(kat["at_rows"]) * kat["alat_in"]
+    alat = np.sqrt((A[:, 0] ** 2).sum())
+    return D.build_descriptor(A / alat, alat, kat["ecutwfc"], gamma_only=False), alat
+
+
+def test_descriptor_matches_fft_test0_header(kat, kat_desc):
+    d, alat = kat_desc
+    assert abs(alat - kat["alat"]) < 1e-6  # the reference literal 18.65 is single precision
+    assert [d.nr1, d.nr2, d.nr3] == kat["grid"]
+    assert d.ngm == kat["g_smooth"]
+    assert d.npw == kat["g_pw"]
+    assert d.nst == kat["sticks_pw"]
+
+
+def test_descriptor_matches_testsuite_si():
+    # test-suite/pw_scf/benchmark.out.git.inp=scf.in: FFT 15x15x15, 180 / 186 PWs
+    d = D.config_descriptor("si2_small")
+    assert (d.nr1, d.nr2, d.nr3) == (15, 15, 15)
+    assert d.npw in (180, 186)
+    # SURVEY 8 table
+    d = D.config_descriptor("si2")
+    assert (d.nr1, d.nr2, d.nr3, d.npw) == (25, 25, 25, 734)
+    d = D.config_descriptor("al4")
+    assert (d.nr1, d.nr2, d.nr3, d.npw) == (27, 27, 27, 1246)
+
+
+def test_good_fft_order():
+    assert [D.good_fft_order(n) for n in (119, 167, 7, 11, 13, 121, 128)] == [120, 180, 8, 12, 15, 125, 128]
+
+
+def test_hpsort_eps_ties_by_index():
+    ra = np.array([3.0, 1.0, 1.0 + 1e-10, 2.0, 1.0 - 1e-10])
+    s, ind = D.hpsort_eps(ra)
+    assert list(ind) == [2, 3, 5, 4, 1]
+    rng = np.random.default_rng(0)
+    x = rng.random(1000)
+    s, ind = D.hpsort_eps(x)
+    assert np.all(np.diff(s) >= 0) and np.array_equal(x[ind - 1], s)
+
+
+def test_g_sorted_and_maps(kat_desc):
+    d, _ = kat_desc
+    assert np.all(np.diff(d.gg) > -1e-8)
+    assert d.gstart == 2 and d.nl[0] == 1
+    # nl is a bijection onto distinct box points, igk sorted by |k+G|^2
+    assert np.unique(d.nl).size == d.ngm
+    assert np.all(np.diff(d.g2kin) > -1e-6)
+    # every PW lies on a wave stick and active plane
+    col = (d.nl[d.igk - 1] - 1) % (d.nr1 * d.nr2)
+    assert np.all(d.isind[col] == 1)
+    assert np.all(d.iplw[col % d.nr1] == 1)
+
+
+def _kat_box(kat):
+    nr = kat["grid"]
+    box = np.zeros(nr[0] * nr[1] * nr[2], dtype=np.complex128)
+    for key, (re_, im_) in kat["coeff"].items():
+        i, j, k = (int(t) - 1 for t in key.split(","))
+        box[i + j * nr[0] + k * nr[0] * nr[1]] = re_ + 1j * im_
+    return nr, box
+
+
+def test_invfft_known_answer_numpy(kat, kat_desc):
+    d, _ = kat_desc
+    nr, box = _kat_box(kat)
+    out = R.cfft3ds(box, nr, +1, d.isind, d.iplw).reshape(nr[2], nr[1], nr[0])
+    gold = np.array(kat["real_space_5x5x5_kji"]).reshape(5, 5, 5, 2)
+    got = out[:5, :5, :5]
+    assert np.abs(got.real - gold[..., 0]).max() < 1.01e-6
+    assert np.abs(got.imag - gold[..., 1]).max() < 1.01e-6
+    # analytic form, full precision
+    z, y, x = np.meshgrid(np.arange(5), np.arange(5), np.arange(5), indexing="ij")
+    ana = 1 + 0.5j * np.exp(2j * np.pi * x / nr[0]) + 0.3j * np.exp(2j * np.pi * y / nr[1]) + 0.7j * np.exp(2j * np.pi * z / nr[2])
+    assert np.abs(got - ana).max() < 1e-13
+    # R->G returns the inputs (scaling 1/N)
+    back = R.cfft3ds(out.reshape(-1), nr, -1, d.isind, d.iplw)
+    sel = np.nonzero(box)[0]
+    assert np.abs(back[sel] - box[sel]).max() < 1e-14
+
+
+@pytest.mark.skipif(R.ref_lib() is None, reason="oracle/_ref not built")
+def test_invfft_known_answer_reference_engine(kat, kat_desc):
+    d, _ = kat_desc
+    nr, box = _kat_box(kat)
+    out = R.ref_cfft3ds(box, nr, +1, d.isind, d.iplw).reshape(nr[2], nr[1], nr[0])
+    gold = np.array(kat["real_space_5x5x5_kji"]).reshape(5, 5, 5, 2)
+    assert np.abs(out[:5, :5, :5].real - gold[..., 0]).max() < 1.01e-6
+    assert np.abs(out[:5, :5, :5].imag - gold[..., 1]).max() < 1.01e-6
+
+
+@pytest.mark.skipif(R.ref_lib() is None, reason="oracle/_ref not built")
+@pytest.mark.parametrize("name", ["si2_small", "ortho_small", "si2_small_gamma", "ortho_small_gamma"])
+def test_restatement_vs_reference_fft_engine(name):
+    """numpy restatement of vloc_psi == restated driver on the reference's C FFT."""
+    d = D.config_descriptor(name)
+    c = d.extra["config"]
+    m = c["nbnd"]
+    inp = R.synthetic_inputs(d, m, [c["nh"]] * c["nat"], seed=3, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    h0 = np.zeros((m, lda), dtype=np.complex128)
+    h1 = np.zeros((m, lda), dtype=np.complex128)
+    (R.vloc_psi_gamma if d.gamma_only else R.vloc_psi_k)(d, lda, n, m, inp["psi"], inp["vrs"], h0)
+    R.ref_vloc_psi(d, lda, n, m, inp["psi"], inp["vrs"], h1)
+    scale = np.abs(h0[:, :n]).max()
+    assert np.abs(h0[:, :n] - h1[:, :n]).max() <= 1e-13 * max(scale, 1.0)
+    assert np.all(h1[:, n:] == 0)
+
+
+def test_random_box_fft_against_full_fft():
+    """cfft3ds on a contract-respecting box (zeros off the sticks) == plain 3-D FFT."""
+    d = D.config_descriptor("ortho_small")
+    nr = (d.nr1, d.nr2, d.nr3)
+    rng = np.random.default_rng(5)
+    box = np.zeros(d.nnr, dtype=np.complex128)
+    idx = d.nl[d.igk - 1] - 1
+    box[idx] = rng.standard_normal(idx.size) + 1j * rng.standard_normal(idx.size)
+    a = R.cfft3ds(box, nr, +1, d.isind, d.iplw).reshape(nr[2], nr[1], nr[0])
+    b = np.fft.ifftn(box.reshape(nr[2], nr[1], nr[0])) * d.nnr
+    assert np.abs(a - b).max() < 1e-12
+
+
+def test_hpsi_hermitian_and_gamma_real():
+    """H built from the restatement is Hermitian: <a|H b> = conj(<b|H a>)."""
+    for name in ("ortho_small", "ortho_small_gamma"):
+        d = D.config_descriptor(name)
+        c = d.extra["config"]
+        inp = R.synthetic_inputs(d, 2, [c["nh"]] * c["nat"], seed=11, poison=False)
+        lda, n = inp["lda"], inp["n"]
+        h, becp = R.h_psi(d, lda, n, 2, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+        a, b = inp["psi"][0, :n], inp["psi"][1, :n]
+        if d.gamma_only:
+            def dot(x, y):  # real-space inner product of Gamma-trick vectors
+                return 2.0 * np.vdot(x, y).real - (x[0].conjugate() * y[0]).real
+            assert abs(dot(a, h[1, :n]) - dot(b, h[0, :n])) < 1e-12
+            assert np.all(h[:, 0].imag == 0)
+        else:
+            assert abs(np.vdot(a, h[1, :n]) - np.conj(np.vdot(b, h[0, :n]))) < 1e-12
+        assert np.all(h[:, n:] == 0)
+
+
+def test_divide_all():
+    c, dsp = R.divide_all(10, 4)
+    assert list(c) == [3, 3, 2, 2] and list(dsp) == [0, 3, 6, 8]
