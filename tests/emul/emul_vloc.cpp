@@ -1,0 +1,131 @@
+// TEST INFRASTRUCTURE (not product code): executes the phase functions of the
+// V_loc CUDA kernels (q-e_b200/csrc/vloc_kernels.cuh) serially on the CPU so
+// that the index / twiddle / table logic can be checked against the oracle in
+// the "-m 'not gpu'" suite. Built by tests/emul/build.sh with plain g++.
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+#include "vloc_setup.h"
+
+using namespace qeb;
+
+static void upload_plan(const HostPlan& hp, FftPlan& pl) { fill_plan(hp, hp.tw.data(), hp.rev.data(), pl); }
+
+extern "C" int emul_fft1d(int n, int sign, int nlines, const double* in, double* out, int nthr, int maxr)
+{
+    // nlines lines of length n, layout [line][n]; out same layout, natural order.
+    HostPlan hp;
+    if (!make_host_plan(n, hp, maxr)) return 1;
+    FftPlan pl;
+    upload_plan(hp, pl);
+    std::vector<cplx> s((size_t)n * nlines);
+    const cplx* ci = (const cplx*)in;
+    cplx* co = (cplx*)out;
+    FastDiv dnl = make_fastdiv(nlines);
+    SmemTile st{s.data(), nlines};
+    NoMid nm;
+    if (sign > 0) {  // DIF natural in
+        for (int l = 0; l < nlines; ++l)
+            for (int i = 0; i < n; ++i) s[(size_t)i * nlines + l] = ci[(size_t)l * n + i];
+        for (int p = 0; p < pl.npass; ++p) {
+            PassDesc pd = pass_of(pl, p);
+            for (int tid = 0; tid < nthr; ++tid) fft_pass<false, false>(tid, nthr, nlines, dnl, pd, pl.tw, +1.0, st, st, nm);
+        }
+        for (int l = 0; l < nlines; ++l)
+            for (int i = 0; i < n; ++i) co[(size_t)l * n + hp.rev[i]] = s[(size_t)i * nlines + l];
+    } else {  // DIT digit-reversed in
+        for (int l = 0; l < nlines; ++l)
+            for (int i = 0; i < n; ++i) s[(size_t)i * nlines + l] = ci[(size_t)l * n + hp.rev[i]];
+        for (int p = pl.npass - 1; p >= 0; --p) {
+            PassDesc pd = pass_of(pl, p);
+            for (int tid = 0; tid < nthr; ++tid) fft_pass<true, false>(tid, nthr, nlines, dnl, pd, pl.tw, -1.0, st, st, nm);
+        }
+        for (int l = 0; l < nlines; ++l)
+            for (int i = 0; i < n; ++i) co[(size_t)l * n + i] = s[(size_t)i * nlines + l];
+    }
+    return 0;
+}
+
+extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, const int* nlm, const int* igk, int ngm,
+                         int lda, int m, const double* psi, const double* v, const double* g2kin, double* hpsi,
+                         int nthr, int batch)
+{
+    HostVlocTables H;
+    std::string err = build_vloc_tables(nr1, nr2, nr3, npw, nl, nlm, igk, ngm, H);
+    if (!err.empty()) {
+        fprintf(stderr, "emul_vloc: %s\n", err.c_str());
+        return 1;
+    }
+    VlocTables t;
+    memset(&t, 0, sizeof(t));
+    t.nr1 = nr1; t.nr2 = nr2; t.nr3 = nr3;
+    t.nst = H.nst; t.nxw = H.nxw; t.npos = nr2 * nr3;
+    upload_plan(H.px, t.px); upload_plan(H.py, t.py); upload_plan(H.pz, t.pz);
+    t.xmap = H.xmap.data(); t.plane_s0 = H.plane_s0.data(); t.plane_ns = H.plane_ns.data(); t.ymap = H.ymap.data();
+    t.TZ = H.TZ; t.ngrp = H.ngrp;
+    t.grp_stick = H.grp_stick.data(); t.grp_nl = H.grp_nl.data(); t.grp_div = H.grp_div.data();
+    t.grp_coef_off = H.grp_coef_off.data(); t.coef_ig = H.coef_ig.data(); t.coef_slot = H.coef_slot.data();
+    t.coef_slot2 = H.gamma ? H.coef_slot2.data() : nullptr;
+    t.TY = H.TY; t.nty = H.nty; t.divTY = make_fastdiv(H.TY);
+    { int last = nr3 - (H.nty - 1) * H.TY; t.divTYlast = make_fastdiv(last); }
+    t.TX = H.TX; t.ntx = H.ntx; t.divTX = make_fastdiv(H.TX);
+    { int last = t.npos - (H.ntx - 1) * H.TX; t.divTXlast = make_fastdiv(last); }
+    t.nsmax = H.nsmax;
+    // potential: permuted by rev_x and scaled
+    std::vector<double> vp((size_t)nr1 * t.npos);
+    const double sc = 1.0 / ((double)nr1 * nr2 * nr3);
+    for (int xp = 0; xp < nr1; ++xp) {
+        int x = H.px.rev[xp];
+        for (int y = 0; y < nr2; ++y)
+            for (int z = 0; z < nr3; ++z)
+                vp[(size_t)xp * t.npos + (size_t)y * nr3 + z] = v[x + (size_t)nr1 * (y + (size_t)nr2 * z)] * sc;
+    }
+    t.vp = vp.data();
+    t.g1_box = (size_t)H.nst * nr3;
+    t.g2_box = (size_t)H.nxw * t.npos;
+    std::vector<cplx> g1(t.g1_box * batch), g2(t.g2_box * batch);
+    t.g1 = g1.data(); t.g2 = g2.data();
+    const cplx nanv = mk(0.0 / 0.0, 0.0 / 0.0);
+    std::vector<cplx> smem(std::max(std::max(H.smem_z, H.smem_y), H.smem_x) / 16 + 16);
+
+    VlocIO io;
+    io.psi = (const cplx*)psi; io.hpsi = (cplx*)hpsi; io.g2kin = g2kin; io.lda = lda; io.n = npw; io.nbands = m;
+    io.gamma = H.gamma;
+    const int nboxes_total = H.gamma ? (m + 1) / 2 : m;
+    for (int bx0 = 0; bx0 < nboxes_total; bx0 += batch) {
+        const int nb = std::min(batch, nboxes_total - bx0);
+        io.band0 = H.gamma ? 2 * bx0 : bx0;
+        for (auto& x : g1) x = nanv;  // poison: every element read must have been written
+        for (auto& x : g2) x = nanv;
+        for (int box = 0; box < nb; ++box) {
+            for (int g = 0; g < H.ngrp; ++g) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < zinv_nphase(t); ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) zinv_phase(ph, tid, nthr, t, io, g, box, smem.data());
+            }
+            for (int xa = 0; xa < H.nxw; ++xa)
+                for (int zt = 0; zt < H.nty; ++zt) {
+                    for (auto& x : smem) x = nanv;
+                    for (int ph = 0; ph < ypass_nphase(t); ++ph)
+                        for (int tid = 0; tid < nthr; ++tid) yinv_phase(ph, tid, nthr, t, zt, xa, box, smem.data());
+                }
+            for (int tile = 0; tile < H.ntx; ++tile) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < xfus_nphase(t); ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) xfus_phase(ph, tid, nthr, t, tile, box, smem.data());
+            }
+            for (int xa = 0; xa < H.nxw; ++xa)
+                for (int zt = 0; zt < H.nty; ++zt) {
+                    for (auto& x : smem) x = nanv;
+                    for (int ph = 0; ph < ypass_nphase(t); ++ph)
+                        for (int tid = 0; tid < nthr; ++tid) yfwd_phase(ph, tid, nthr, t, zt, xa, box, smem.data());
+                }
+            for (int g = 0; g < H.ngrp; ++g) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < zfwd_nphase(t); ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) zfwd_phase(ph, tid, nthr, t, io, g, box, smem.data());
+            }
+        }
+    }
+    return 0;
+}
