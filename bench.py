@@ -1,0 +1,374 @@
+#!/usr/bin/env python3
+"""bench.py - H|psi> band-applications/s on B200 (BASELINE.json metric).
+
+Workload (N=1): AUSURF112 (BASELINE configs[3]): smooth grid 125x64x200, npw = 95394,
+nbnd = m = 800 bands (first Davidson call), nkb = 2016 ultrasoft projectors, one k-point.
+A step = one h_psi(lda,n,m,psi,hpsi) call on synthetic random psi / V_loc / vkb / deeq.
+N>1: k-point pools (one k-point per GPU, no collective inside the path) ->
+"scaling": "weak"; `--mode bgrp` instead splits the m bands of ONE k-point over band groups
+with an NCCL all-gather of hpsi (PW/src/h_psi.f90:53-67) -> "strong".
+
+`--impl reference` times the reference's CPU algorithm for the same path on the host cores:
+V_loc through the reference's own C FFT engine (oracle/_ref, compiled from
+/root/reference/FFTXlib/src/fftw_dp.c, bands over OpenMP threads) and the projector GEMMs
+through OpenBLAS (numpy), on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="ausurf112")
+    ap.add_argument("--bands", type=int, default=0, help="override m (default nbnd of the workload)")
+    ap.add_argument("--mode", default="pools", choices=["pools", "bgrp"])
+    ap.add_argument("--cpu-sample-bands", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--batch", type=int, default=0)
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------
+# clocks sampling (nvidia-smi during the timed region)
+# ---------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------
+def workload(name: str, seed: int = 0):
+    """descriptor + sizes from the restated grid rules (host setup, not timed)."""
+    from oracle import descriptor as D
+
+    c = dict(D.CONFIGS[name])
+    xk = np.array(c["xk"], dtype=float)
+    if not c["gamma"] and seed:
+        xk = xk + 0.01 * seed  # a different k-point per pool
+    d = D.build_descriptor(c["at"], c["alat"], c["ecutwfc"], xk=xk, gamma_only=c["gamma"], ecutrho=c["ecutrho"])
+    nh = c.get("nh_list") or [c["nh"]] * c["nat"]
+    return d, c, np.asarray(nh, dtype=np.int32)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return float(j.get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference_run(d, c, nh, m_sample: int, nthreads: int, reps: int = 1):
+    """The reference's CPU algorithm on a bounded sample of m_sample bands: V_loc via the reference's
+    C FFT engine (oracle/_ref), projectors via OpenBLAS zgemm/dgemm (numpy). Returns seconds per pass."""
+    from oracle import hpsi_ref as R
+
+    n = d.npw
+    lda = n
+    rng = np.random.default_rng(99)
+    psi = (rng.standard_normal((m_sample, lda)) + 1j * rng.standard_normal((m_sample, lda))) / np.sqrt(2 * n)
+    vrs = rng.uniform(-1, 0, d.nnr)
+    nkb = int(nh.sum())
+    vkb = np.empty((nkb, lda), dtype=np.complex128)
+    for i0 in range(0, nkb, 256):  # chunked to bound temporary memory
+        k = min(256, nkb - i0)
+        vkb[i0:i0 + k] = (rng.standard_normal((k, lda)) + 1j * rng.standard_normal((k, lda))) / np.sqrt(n)
+    nhm = int(nh.max())
+    deeq = rng.uniform(-1, 1, (len(nh), nhm, nhm))
+    ofs = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
+    use_ref = R.ref_lib() is not None
+    best = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        hpsi = np.zeros((m_sample, lda), dtype=np.complex128)
+        hpsi[:, :n] = d.g2kin[None, :n] * psi[:, :n]
+        if use_ref:
+            R.ref_vloc_psi(d, lda, n, m_sample, psi, vrs, hpsi, nthreads)
+        else:
+            (R.vloc_psi_gamma if d.gamma_only else R.vloc_psi_k)(d, lda, n, m_sample, psi, vrs, hpsi)
+        if d.gamma_only:
+            becp = R.calbec_gamma(n, vkb, psi, m_sample, d.gstart)
+            ps = R.apply_deeq(becp, deeq, nh, ofs)
+            R.add_vuspsi_gamma(n, m_sample, vkb, ps, hpsi)
+        else:
+            becp = R.calbec_k(n, vkb, psi, m_sample)
+            ps = R.apply_deeq(becp, deeq, nh, ofs)
+            R.add_vuspsi_k(n, m_sample, vkb, ps, hpsi)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return best, ("reference" if use_ref else "port")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    d, c, nh = workload(args.workload)
+    cores = os.cpu_count() or 1
+    m_s = args.cpu_sample_bands or 16
+    times = []
+    kind = "port"
+    for i in range(args.warmup + args.steps):
+        dt, kind = cpu_reference_run(d, c, nh, m_s, cores)
+        if i >= args.warmup:
+            times.append(dt)
+    t = float(np.mean(times))
+    val = m_s / t
+    line = {
+        "impl": "reference", "metric": "h_psi band-applications/s", "value": val, "unit": "band-applications/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "grid": [d.nr1, d.nr2, d.nr3], "npw": d.npw, "nkb": int(nh.sum()),
+                   "bands_per_step": m_s, "note": "bounded sample of the m-band workload"},
+        "cpu_baseline": {"value": val, "unit": "band-applications/s", "cores": cores, "kind": kind,
+                         "sample": f"{m_s} bands of the {args.workload} h_psi: V_loc via the reference C FFT engine "
+                                   f"(OpenMP over bands), projectors via OpenBLAS zgemm"},
+        "e2e": {"value": val, "unit": "band-applications/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import qe_b200
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: a CUDA device is required (no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    pools = args.mode == "pools"
+    d, c, nh = workload(args.workload, seed=rank if pools else 0)
+    n = d.npw
+    lda = n
+    m_total = args.bands or c["nbnd"]
+    nkb = int(nh.sum())
+    if pools:
+        m0, m1 = 0, m_total
+    else:
+        m0, m1 = qe_b200.divide_all(m_total, world, rank)
+    m_loc = m1 - m0
+
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    psi = torch.randn((m_total, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(2 * n)
+    hpsi = torch.zeros_like(psi)
+    vkb = torch.randn((nkb, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(n)
+    rng = np.random.default_rng(2234 + rank)
+    vrs = rng.uniform(-1.0, 0.0, d.nnr)
+    nhm = int(nh.max())
+    deeq = rng.uniform(-1, 1, (len(nh), nhm, nhm))
+    deeq = 0.5 * (deeq + deeq.transpose(0, 2, 1))
+    ofs = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
+
+    stream = torch.cuda.current_stream().cuda_stream
+    h = qe_b200.HPsi(device=local, stream=stream, batch=args.batch or None)
+    h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
+    h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
+    h.set_vloc(vrs)
+    h.set_nonlocal(nh, ofs, deeq)
+    h.set_async(True)
+    st = h.stats()
+
+    def step():
+        if pools or world == 1:
+            h.h_psi(lda, n, m_total, psi, hpsi)
+        else:
+            h.h_psi_bgrp(lda, n, m_total, psi, hpsi, world, rank)
+            # all-gather of the column blocks over inter_bgrp_comm (h_psi.f90:58-63)
+            blocks = [hpsi[s:e] for s, e in (qe_b200.divide_all(m_total, world, r) for r in range(world))]
+            dist.all_gather(blocks, hpsi[m0:m1]) if len({b.shape[0] for b in blocks}) == 1 else [
+                dist.broadcast(b, src=r) for r, b in enumerate(blocks)]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    units = m_total * (world if pools else 1)
+    value = units / (ms_step * 1e-3)
+
+    # ---- per-section timing on the launching stream (V_loc alone, projectors alone) ----
+    def time_section(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    mm = m_total if pools else m_loc
+    ms_vloc = time_section(lambda: (h.vloc_psi_gamma if d.gamma_only else h.vloc_psi_k)(lda, n, mm, psi, None, hpsi))
+    ms_nl = time_section(lambda: h.nonlocal_only(lda, n, mm, psi, hpsi)) if nkb else 0.0
+    peak, peak_src = peaks()
+    boxes = (mm + 1) // 2 if d.gamma_only else mm
+    nbatches = -(-boxes // st["batch"])
+    vloc_bytes = st["vloc_bytes_per_band"] * mm
+    achieved = vloc_bytes / (ms_vloc * 1e-3) / 1e9
+    # per launch of the dominant V_loc kernel family: 5 pass kernels per batch
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "V_loc pass pipeline (5 kernels/batch: zinv,yinv,xfus,yfwd,zfwd)",
+                "algorithmic_bytes_per_band": st["vloc_bytes_per_band"], "ms_vloc_section": ms_vloc,
+                "peak_source": peak_src}
+    gemm_tf = st["gemm_flops_per_band"] * mm / (ms_nl * 1e-3) / 1e12 if ms_nl > 0 else None
+    launches_step = nbatches * 5 + (4 if nkb else 0) + 1
+
+    # ---- end to end through the public API with HOST (pinned) buffers ----
+    e2e = None
+    if not args.no_e2e:
+        h.set_async(False)
+        psi_h = torch.empty((mm, lda, 2), dtype=torch.float64).pin_memory()
+        psi_h.copy_(psi[:mm].cpu())
+        hpsi_h = torch.empty((mm, lda, 2), dtype=torch.float64).pin_memory()
+        pn, hn = psi_h.numpy(), hpsi_h.numpy()
+        h.h_psi(lda, n, mm, pn, hn)
+        barrier()
+        t0 = time.perf_counter()
+        reps = max(2, min(args.steps, 3))
+        for _ in range(reps):
+            h.h_psi(lda, n, mm, pn, hn)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / reps
+        tt = torch.tensor([dt], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e = {"value": (mm * world if (pools or world == 1) else m_total) / dt, "unit": "band-applications/s",
+               "h2d_bytes_per_step": int(mm * lda * 16), "d2h_bytes_per_step": int(mm * lda * 16),
+               "ms_per_step": dt * 1e3}
+        h.set_async(True)
+
+    if rank == 0:
+        line = {
+            "metric": "h_psi band-applications/s", "value": value, "unit": "band-applications/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak" if pools else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "grid": [d.nr1, d.nr2, d.nr3], "npw": n, "bands_per_step": m_total,
+                       "nkb": nkb, "gamma_only": bool(d.gamma_only), "parallelism": ("k-pools" if pools else "band-groups") + f" x{world}",
+                       "vloc_batch_boxes": st["batch"], "l2": "inputs larger than L2 (psi+hpsi+vkb = %.1f GB)" % ((2 * m_total * lda * 16 + nkb * lda * 16) / 1e9)},
+            "roofline": roofline,
+            "projectors": {"ms": ms_nl, "tflops_fp64": gemm_tf},
+            "gpu_launches": launches_step * args.steps,
+            "clocks": clocks,
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if not args.no_cpu_baseline and world == 1:
+            cores = os.cpu_count() or 1
+            m_s = args.cpu_sample_bands or 8
+            dt, kind = cpu_reference_run(d, c, nh, m_s, cores)
+            line["cpu_baseline"] = {"value": m_s / dt, "unit": "band-applications/s", "cores": cores, "kind": kind,
+                                    "sample": f"{m_s} bands of the same h_psi (V_loc: reference C FFT engine, OpenMP "
+                                              f"over bands; projectors: OpenBLAS zgemm), {dt:.1f} s"}
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

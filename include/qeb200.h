@@ -1,0 +1,144 @@
+/*
+ * qeb200 - C ABI of the B200-native H|psi> path of PWscf.
+ *
+ * This is the drop-in boundary: a Fortran ISO_C_BINDING shim (fortran/qeb200_shim.f90,
+ * INTEGRATION.md) keeps the reference's entry points and forwards to these
+ * functions. Every pointer may be a HOST or a DEVICE pointer (detected with
+ * cudaPointerGetAttributes); host data is staged through the context's own
+ * device buffers. All arrays use the reference's layout: Fortran column-major,
+ * COMPLEX(DP) = interleaved (re,im) doubles, index maps INT32 and 1-based.
+ *
+ * The reference keeps the state h_psi reads in Fortran modules; here it lives
+ * in an explicit context whose setters mirror the cadence at which that module
+ * state changes (file:line relative to the QE 7.5 tree):
+ *   qeb_set_grid      after fft_type_init + fft_set_nl  (PW/src/data_structure.f90:74, Modules/recvec_subs.f90:309)
+ *   qeb_set_kpoint    after g2_kin + init_us_2          (PW/src/c_bands.f90:105-109)
+ *   qeb_set_vloc      after set_vrs                     (PW/src/electrons.f90:1038)
+ *   qeb_set_nonlocal  after newd                        (PW/src/electrons.f90:1045)
+ *
+ * Return value: 0 on success, non-zero on error (the shim turns it into
+ * errore(routine, qeb_last_error(ctx), code), UtilXlib/error_handler.f90:10).
+ * There is no CPU fallback: without a CUDA device every compute call fails.
+ */
+#ifndef QEB200_H
+#define QEB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct qeb_ctx qeb_ctx;
+
+/* ---- lifetime ---------------------------------------------------------- */
+/* One context per (process, device) - the analogue of one MPI rank's module
+ * state (Modules/mp_world.f90:94 binds rank -> device). stream: a cudaStream_t
+ * cast to void* (NULL = the context creates its own non-blocking stream and
+ * synchronises it before every entry point returns, which reproduces the
+ * reference's blocking OpenACC regions). */
+int qeb_create(qeb_ctx** ctx, int device, void* stream);
+int qeb_destroy(qeb_ctx* ctx);
+const char* qeb_last_error(const qeb_ctx* ctx);
+/* version / build info string */
+const char* qeb_version(void);
+/* bands (k) or band pairs (Gamma) in flight per V_loc batch; the reference's
+ * many_fft = 16 (Modules/control_flags.f90:285-288). 0 = automatic. */
+int qeb_set_batch(qeb_ctx* ctx, int nboxes);
+/* asynchronous mode: 1 = entry points return without synchronising the
+ * stream (for callers that own the stream, e.g. the benchmark). */
+int qeb_set_async(qeb_ctx* ctx, int async);
+
+/* ---- state setters ----------------------------------------------------- */
+/* FFT grid + G-vector maps of dffts (serial descriptor):
+ *   fft_type_descriptor nr1,nr2,nr3,nr1x,nr2x,nr3x,nnr   FFTXlib/src/fft_types.f90:35-185
+ *   nl, nlm (nlm NULL unless gamma_only)                 FFTXlib/src/fft_ggen.f90:28-108
+ * nr?x must equal nr? (true on every non-ESSL build, fft_support.f90:40-54). */
+int qeb_set_grid(qeb_ctx* ctx, int nr1, int nr2, int nr3, int nr1x, int nr2x, int nr3x, int ngm, const int* nl,
+                 const int* nlm, int gamma_only);
+
+/* Per-k-point state: npw = ngk(ik), npwx, igk_k(:,ik) (NULL for gamma_only:
+ * igk(i)=i), g2kin(1:npw) (PW/src/g2_kin.f90:37-43), vkb(npwx,nkb)
+ * (upflib/init_us_2_acc.f90:10), gstart (Modules/recvec_subs.f90:256-260).
+ * vkb may be NULL when nkb == 0. */
+int qeb_set_kpoint(qeb_ctx* ctx, int npw, int npwx, const int* igk, const double* g2kin, const void* vkb, int nkb,
+                   int gstart);
+
+/* Local potential on the smooth grid for current_spin: vrs(1:nnr,current_spin)
+ * (PW/src/set_vrs.f90), x-fastest box. */
+int qeb_set_vloc(qeb_ctx* ctx, const double* vrs);
+
+/* Nonlocal D matrices for current_spin: deeq(nhm,nhm,nat,current_spin) real
+ * (upflib/uspp.f90:56-89), nh(ityp(na)) per atom and ofsbeta(na)
+ * (0-based row offset into vkb/becp of atom na's projectors). */
+int qeb_set_nonlocal(qeb_ctx* ctx, int nat, int nhm, const int* nh_of_atom, const int* ofsbeta, const double* deeq);
+
+/* ---- the reference entry points ---------------------------------------- */
+/* h_psi(lda,n,m,psi,hpsi)           PW/src/h_psi.f90:9-80 / h_psi_gpu.f90:9-84
+ * hpsi = (g2kin + V_loc + V_NL) psi for m bands; rows n+1..lda of hpsi are
+ * zeroed; Gamma: Im hpsi(G=0) = 0 when gstart == 2. Side effect kept from the
+ * reference: the projections <beta|psi> of these m bands are
+ * left in the context and can be read with qeb_get_becp (the shim copies them
+ * into becmod::becp for the s_psi call that follows, PW/src/s_psi.f90:15). */
+int qeb_h_psi(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* hpsi);
+
+/* vloc_psi_k(lda,n,m,psi,v,hpsi)    PW/src/vloc_psi_acc.f90:148-266
+ * hpsi (INOUT) += V_loc psi. v == NULL: use the potential of qeb_set_vloc. */
+int qeb_vloc_psi_k(qeb_ctx* ctx, int lda, int n, int m, const void* psi, const double* v, void* hpsi);
+/* vloc_psi_gamma(lda,n,m,psi,v,hpsi) PW/src/vloc_psi_acc.f90:9-145 */
+int qeb_vloc_psi_gamma(qeb_ctx* ctx, int lda, int n, int m, const void* psi, const double* v, void* hpsi);
+
+/* invfft / fwfft (kind, f, dfft, howmany)  FFTXlib/src/fft_interfaces.f90:19-80,
+ * fft_fwinv.f90:10-216: in-place 3-D transform of howmany boxes f(nnr*howmany).
+ * sign > 0: G->R, exp(+i), unscaled; sign < 0: R->G, exp(-i), scaled 1/(nr1 nr2 nr3).
+ * kind: QEB_FFT_RHO full box, QEB_FFT_WAVE the reference's "reduced" transform
+ * (only the wave sticks/planes carry data; the rest of the box is
+ * unspecified after R->G, exactly like cfft3ds, fft_scalar.FFTW3.f90:498-694;
+ * here the full transform is always computed, like cfft3d_gpu,
+ * fft_scalar.cuFFT.f90:695-698). */
+#define QEB_FFT_RHO 0
+#define QEB_FFT_WAVE 1
+int qeb_fft(qeb_ctx* ctx, int sign, int kind, void* f, int howmany);
+
+/* calbec(npw,beta,psi,betapsi,nbnd)  Modules/becmod.f90:138-172 (k: :431-486,
+ * Gamma: :274-334): becp(nkb,m) = beta(1:n,:)^H psi(1:n,1:m); Gamma: real
+ * result 2*Re(...) - [gstart==2] beta(1,i) psi(1,j). beta (npwx,nkb) with the
+ * npwx/gstart of the last qeb_set_kpoint; beta == NULL uses the context's vkb.
+ * becp: complex(nkb,m) for k, real(nkb,m) for Gamma. */
+int qeb_calbec(qeb_ctx* ctx, int n, const void* beta, int nkb, const void* psi, int lda, int m, void* becp);
+
+/* add_vuspsi(lda,n,m,hpsi)  PW/src/add_vuspsi.f90:10-237:
+ * hpsi(1:n,1:m) += vkb * (blockdiag(deeq) * becp). becp == NULL: use the
+ * projections left in the context by the last qeb_h_psi / qeb_calbec. */
+int qeb_add_vuspsi(qeb_ctx* ctx, int lda, int n, int m, void* hpsi, const void* becp);
+
+/* becp of the last qeb_h_psi / qeb_calbec: (nkb,m) complex (k) or real (Gamma) */
+int qeb_get_becp(qeb_ctx* ctx, void* becp, int m);
+
+/* ---- multi-GPU (one process per GPU) ----------------------------------- */
+/* divide_all(comm, m, m_start, m_end, recv_counts, displs)  UtilXlib/divide.f90:55-106.
+ * 0-based start/end(exclusive) of group `me` of `nproc`. */
+int qeb_divide_all(int m, int nproc, int me, int* start, int* end);
+/* h_psi over band groups (PW/src/h_psi.f90:53-67): this rank applies H to its
+ * own column block [start,end) of psi/hpsi (device or host pointers to the
+ * FULL lda x m arrays); the all-gather of hpsi column blocks over
+ * inter_bgrp_comm is done by the caller's NCCL communicator (the host-side
+ * mirror q-e_b200/hpsi.py does it with torch.distributed; a Fortran caller
+ * passes ncclComm through qeb_set_nccl). */
+int qeb_h_psi_bgrp(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* hpsi, int nbgrp, int my_bgrp);
+/* optional: ncclComm_t (as void*) of inter_bgrp_comm; when set, qeb_h_psi_bgrp
+ * all-gathers the column blocks of a DEVICE hpsi itself. */
+int qeb_set_nccl(qeb_ctx* ctx, void* nccl_comm, int nranks, int rank);
+
+/* ---- introspection for benchmarks / tests ------------------------------ */
+/* algorithmic HBM bytes per band of the V_loc path:
+ * 16*(4*nst*nr3 + 4*nxw*nr2*nr3)[/2 Gamma] + 60*npw, and the table sizes */
+int qeb_get_stats(qeb_ctx* ctx, double* vloc_bytes_per_band, double* gemm_flops_per_band, int* nst, int* nxw,
+                  int* nboxes_batch);
+/* FP64 DMMA GEMM self-test entry used by the benchmark to time the projector
+ * kernels alone: runs calbec + add_vuspsi on the context's vkb for m bands of
+ * a device psi/hpsi. */
+int qeb_nonlocal_only(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* hpsi);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QEB200_H */

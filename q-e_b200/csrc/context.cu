@@ -1,0 +1,741 @@
+// C ABI of the qeb200 library (include/qeb200.h): explicit context replacing
+// the Fortran module state h_psi reads, host/device pointer
+// handling, and the orchestration of the V_loc passes and projector GEMMs in
+// the reference's order (PW/src/h_psi.f90:138-147 kinetic, :180/:220 V_loc,
+// :229-236 nonlocal, :294-295 Gamma fix).
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/qeb200.h"
+#include "fullfft.h"
+#include "gemm.h"
+#include "vloc.h"
+#include "vloc_setup.h"
+
+using namespace qeb;
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+bool is_device_ptr(const void* p)
+{
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace
+
+struct qeb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    bool async = false;
+    int num_sms = 148;
+    size_t max_smem = 0;
+    std::string err;
+
+    // grid
+    bool have_grid = false;
+    int nr1 = 0, nr2 = 0, nr3 = 0, ngm = 0;
+    bool gamma = false;
+    std::vector<int> nl, nlm;
+    // k-point
+    bool have_k = false;
+    int npw = 0, npwx = 0, nkb = 0, gstart = 1;
+    DevBuf g2kin_d, vkb_own;
+    const cplx* vkb_d = nullptr;
+    // V_loc tables
+    HostVlocTables H;
+    DevBuf tab_d;  // all int tables
+    DevBuf plan_d;  // twiddles + rev of the three plans
+    VlocTables T;
+    VlocLaunchCfg cfg;
+    int batch_user = 0, batch = 1;
+    DevBuf g1_d, g2_d;
+    // potential
+    bool have_v = false;
+    DevBuf v_d, vp_d;
+    DevBuf revx_d;
+    // full-box FFT plans
+    DevBuf full_plan_d;
+    FftPlan fpx, fpy, fpz;
+    bool have_full = false;
+    // nonlocal
+    bool have_nl = false;
+    int nat = 0, nhm = 0, nl_rows = 0;
+    DevBuf nlint_d, deeq_d;
+    const int *row_atom_d = nullptr, *ofs_d = nullptr, *nh_d = nullptr;
+    DevBuf becp_d, ps_d, part_d;
+    int becp_m = 0;
+    // staging
+    DevBuf psi_stage, hpsi_stage, beta_stage, misc_stage;
+    // nccl
+    void* nccl = nullptr;
+    int nranks = 1, rank = 0;
+};
+
+#define QEB_FAIL(ctx, code, msg)   \
+    do {                           \
+        (ctx)->err = (msg);        \
+        return (code);             \
+    } while (0)
+#define QEB_CUDA(ctx, call)                                                                 \
+    do {                                                                                    \
+        cudaError_t e__ = (call);                                                           \
+        if (e__ != cudaSuccess) {                                                           \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);               \
+            return 100 + (int)e__;                                                          \
+        }                                                                                   \
+    } while (0)
+
+static int finish(qeb_ctx* c)
+{
+    if (!c->async) QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// returns a device pointer for `p` (copying host data into `stage` if needed)
+static int stage_in(qeb_ctx* c, const void* p, size_t bytes, DevBuf& stage, const void** out)
+{
+    if (is_device_ptr(p)) {
+        *out = p;
+        return 0;
+    }
+    QEB_CUDA(c, stage.ensure(bytes));
+    QEB_CUDA(c, cudaMemcpyAsync(stage.p, p, bytes, cudaMemcpyHostToDevice, c->stream));
+    *out = stage.p;
+    return 0;
+}
+
+extern "C" {
+
+const char* qeb_version(void) { return "qeb200 0.1 (sm_100a; FP64 DMMA projectors; radix-2/3/5 pencil FFT)"; }
+
+int qeb_create(qeb_ctx** out, int device, void* stream)
+{
+    if (!out) return 1;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return 2;  // no CPU fallback
+    if (device < 0 || device >= ndev) return 3;
+    if (cudaSetDevice(device) != cudaSuccess) return 4;
+    qeb_ctx* c = new qeb_ctx();
+    c->device = device;
+    if (stream) {
+        c->stream = (cudaStream_t)stream;
+    } else {
+        if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+            delete c;
+            return 5;
+        }
+        c->own_stream = true;
+    }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    c->num_sms = prop.multiProcessorCount;
+    c->max_smem = prop.sharedMemPerBlockOptin;
+    if (vloc_init_attrs(c->max_smem) != cudaSuccess) {
+        delete c;
+        return 6;
+    }
+    if (const char* e = getenv("QEB_BATCH")) c->batch_user = atoi(e);
+    *out = c;
+    return 0;
+}
+
+int qeb_destroy(qeb_ctx* c)
+{
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->g2kin_d, &c->vkb_own, &c->tab_d, &c->plan_d, &c->g1_d, &c->g2_d, &c->v_d, &c->vp_d,
+                      &c->revx_d, &c->full_plan_d, &c->nlint_d, &c->deeq_d, &c->becp_d, &c->ps_d, &c->part_d,
+                      &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage};
+    for (DevBuf* b : bufs) b->release();
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return 0;
+}
+
+const char* qeb_last_error(const qeb_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int qeb_set_batch(qeb_ctx* c, int nboxes)
+{
+    if (!c || nboxes < 0) return 1;
+    c->batch_user = nboxes;
+    c->have_k = false;  // workspaces are re-sized by the next qeb_set_kpoint
+    return 0;
+}
+
+int qeb_set_async(qeb_ctx* c, int async)
+{
+    if (!c) return 1;
+    c->async = async != 0;
+    return 0;
+}
+
+int qeb_set_grid(qeb_ctx* c, int nr1, int nr2, int nr3, int nr1x, int nr2x, int nr3x, int ngm, const int* nl,
+                 const int* nlm, int gamma_only)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (nr1 < 1 || nr2 < 1 || nr3 < 1 || ngm < 1 || !nl) QEB_FAIL(c, 10, "qeb_set_grid: bad arguments");
+    if (nr1x != nr1 || nr2x != nr2 || nr3x != nr3)
+        QEB_FAIL(c, 11, "qeb_set_grid: padded leading dimensions (nr?x != nr?) are not supported");
+    if (gamma_only && !nlm) QEB_FAIL(c, 12, "qeb_set_grid: gamma_only requires nlm");
+    HostPlan hx, hy, hz;
+    if (!make_host_plan(nr1, hx) || !make_host_plan(nr2, hy) || !make_host_plan(nr3, hz))
+        QEB_FAIL(c, 13, "qeb_set_grid: FFT dimensions must factor into 2, 3, 5 (fft_support.f90:61-120)");
+    c->nr1 = nr1;
+    c->nr2 = nr2;
+    c->nr3 = nr3;
+    c->ngm = ngm;
+    c->gamma = gamma_only != 0;
+    c->nl.assign(nl, nl + ngm);
+    if (c->gamma)
+        c->nlm.assign(nlm, nlm + ngm);
+    else
+        c->nlm.clear();
+    // plans for the x direction permutation of V and for the full-box FFT
+    {
+        const size_t ntw = (size_t)nr1 + nr2 + nr3;
+        QEB_CUDA(c, c->full_plan_d.ensure(ntw * 16 + ntw * 4));
+        cplx* tw = (cplx*)c->full_plan_d.p;
+        int* rv = (int*)(tw + ntw);
+        const HostPlan* hp[3] = {&hx, &hy, &hz};
+        FftPlan* fp[3] = {&c->fpx, &c->fpy, &c->fpz};
+        size_t off = 0;
+        for (int d = 0; d < 3; ++d) {
+            QEB_CUDA(c, cudaMemcpyAsync(tw + off, hp[d]->tw.data(), hp[d]->tw.size() * 16, cudaMemcpyHostToDevice, c->stream));
+            QEB_CUDA(c, cudaMemcpyAsync(rv + off, hp[d]->rev.data(), hp[d]->rev.size() * 4, cudaMemcpyHostToDevice, c->stream));
+            fill_plan(*hp[d], tw + off, rv + off, *fp[d]);
+            off += hp[d]->n;
+        }
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->have_full = true;
+    }
+    c->have_grid = true;
+    c->have_k = false;
+    c->have_v = false;
+    return 0;
+}
+
+static int upload_tables(qeb_ctx* c)
+{
+    HostVlocTables& H = c->H;
+    // integer tables in one allocation
+    std::vector<const std::vector<int>*> vs = {&H.xmap, &H.plane_s0, &H.plane_ns, &H.ymap, &H.grp_stick, &H.grp_nl,
+                                               &H.grp_coef_off, &H.coef_ig, &H.coef_slot, &H.coef_slot2};
+    size_t tot = 0;
+    std::vector<size_t> offs;
+    for (auto v : vs) {
+        offs.push_back(tot);
+        tot += (v->size() + 3) & ~(size_t)3;
+    }
+    const size_t div_off = tot;
+    tot += H.grp_div.size() * 3;
+    QEB_CUDA(c, c->tab_d.ensure(tot * 4 + 16));
+    std::vector<int> host(tot, 0);
+    for (size_t i = 0; i < vs.size(); ++i)
+        if (!vs[i]->empty()) memcpy(host.data() + offs[i], vs[i]->data(), vs[i]->size() * 4);
+    if (!H.grp_div.empty()) memcpy(host.data() + div_off, H.grp_div.data(), H.grp_div.size() * 12);
+    QEB_CUDA(c, cudaMemcpyAsync(c->tab_d.p, host.data(), tot * 4, cudaMemcpyHostToDevice, c->stream));
+    const int* base = (const int*)c->tab_d.p;
+    VlocTables& t = c->T;
+    memset(&t, 0, sizeof(t));
+    t.nr1 = H.nr1;
+    t.nr2 = H.nr2;
+    t.nr3 = H.nr3;
+    t.nst = H.nst;
+    t.nxw = H.nxw;
+    t.npos = H.nr2 * H.nr3;
+    t.xmap = base + offs[0];
+    t.plane_s0 = base + offs[1];
+    t.plane_ns = base + offs[2];
+    t.ymap = base + offs[3];
+    t.grp_stick = base + offs[4];
+    t.grp_nl = base + offs[5];
+    t.grp_coef_off = base + offs[6];
+    t.coef_ig = base + offs[7];
+    t.coef_slot = base + offs[8];
+    t.coef_slot2 = H.gamma ? base + offs[9] : nullptr;
+    t.grp_div = (const FastDiv*)(base + div_off);
+    t.TZ = H.TZ;
+    t.ngrp = H.ngrp;
+    t.TY = H.TY;
+    t.nty = H.nty;
+    t.divTY = make_fastdiv(H.TY);
+    t.divTYlast = make_fastdiv(H.nr3 - (H.nty - 1) * H.TY);
+    t.TX = H.TX;
+    t.ntx = H.ntx;
+    t.divTX = make_fastdiv(H.TX);
+    t.divTXlast = make_fastdiv(t.npos - (H.ntx - 1) * H.TX);
+    t.nsmax = H.nsmax;
+    // plans
+    const size_t ntw = (size_t)H.nr1 + H.nr2 + H.nr3;
+    QEB_CUDA(c, c->plan_d.ensure(ntw * 20));
+    cplx* tw = (cplx*)c->plan_d.p;
+    int* rv = (int*)(tw + ntw);
+    const HostPlan* hp[3] = {&H.px, &H.py, &H.pz};
+    FftPlan* fp[3] = {&t.px, &t.py, &t.pz};
+    size_t off = 0;
+    for (int d = 0; d < 3; ++d) {
+        QEB_CUDA(c, cudaMemcpyAsync(tw + off, hp[d]->tw.data(), hp[d]->tw.size() * 16, cudaMemcpyHostToDevice, c->stream));
+        QEB_CUDA(c, cudaMemcpyAsync(rv + off, hp[d]->rev.data(), hp[d]->rev.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        fill_plan(*hp[d], tw + off, rv + off, *fp[d]);
+        off += hp[d]->n;
+    }
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));  // host vectors go out of scope
+    // workspaces
+    t.g1_box = (size_t)H.nst * H.nr3;
+    t.g2_box = (size_t)H.nxw * t.npos;
+    int nb = c->batch_user;
+    if (nb <= 0) {
+        const size_t target = (size_t)56 << 20;  // keep the batch's G2 planes L2-resident
+        nb = (int)(target / (t.g2_box * 16 + 1));
+        if (nb < 1) nb = 1;
+        if (nb > 64) nb = 64;
+    }
+    c->batch = nb;
+    QEB_CUDA(c, c->g1_d.ensure(t.g1_box * 16 * nb));
+    QEB_CUDA(c, c->g2_d.ensure(t.g2_box * 16 * nb));
+    t.g1 = (cplx*)c->g1_d.p;
+    t.g2 = (cplx*)c->g2_d.p;
+    t.vp = (const double*)c->vp_d.p;
+    c->cfg.smem_z = H.smem_z;
+    c->cfg.smem_y = H.smem_y;
+    c->cfg.smem_x = H.smem_x;
+    c->cfg.threads_z = c->cfg.threads_y = c->cfg.threads_x = 256;
+    if (H.smem_z > c->max_smem || H.smem_y > c->max_smem || H.smem_x > c->max_smem)
+        QEB_FAIL(c, 21, "FFT dimension too large for the shared-memory pencil kernels");
+    return 0;
+}
+
+int qeb_set_kpoint(qeb_ctx* c, int npw, int npwx, const int* igk, const double* g2kin, const void* vkb, int nkb,
+                   int gstart)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_grid) QEB_FAIL(c, 20, "qeb_set_kpoint: qeb_set_grid has not been called");
+    if (npw < 1 || npwx < npw || nkb < 0 || !g2kin || (nkb > 0 && !vkb)) QEB_FAIL(c, 22, "qeb_set_kpoint: bad arguments");
+    if (c->gamma && igk) {
+        for (int i = 0; i < npw; ++i)
+            if (igk[i] != i + 1) QEB_FAIL(c, 23, "qeb_set_kpoint: gamma_only expects igk(i) = i");
+        igk = nullptr;
+    }
+    if (!c->gamma && !igk) QEB_FAIL(c, 24, "qeb_set_kpoint: igk required for k-points");
+    std::string e = build_vloc_tables(c->nr1, c->nr2, c->nr3, npw, c->nl.data(), c->gamma ? c->nlm.data() : nullptr, igk,
+                                      c->ngm, c->H, 72 * 1024);
+    if (!e.empty()) QEB_FAIL(c, 25, "qeb_set_kpoint: " + e);
+    c->npw = npw;
+    c->npwx = npwx;
+    c->nkb = nkb;
+    c->gstart = gstart;
+    int rc = upload_tables(c);
+    if (rc) return rc;
+    QEB_CUDA(c, c->g2kin_d.ensure((size_t)npw * 8));
+    QEB_CUDA(c, cudaMemcpyAsync(c->g2kin_d.p, g2kin, (size_t)npw * 8,
+                                is_device_ptr(g2kin) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    if (nkb > 0) {
+        if (is_device_ptr(vkb)) {
+            c->vkb_d = (const cplx*)vkb;  // borrowed: the caller keeps it alive (like the reference's module array)
+        } else {
+            QEB_CUDA(c, c->vkb_own.ensure((size_t)npwx * nkb * 16));
+            QEB_CUDA(c, cudaMemcpyAsync(c->vkb_own.p, vkb, (size_t)npwx * nkb * 16, cudaMemcpyHostToDevice, c->stream));
+            c->vkb_d = (const cplx*)c->vkb_own.p;
+        }
+    } else {
+        c->vkb_d = nullptr;
+    }
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_k = true;
+    c->becp_m = 0;
+    return 0;
+}
+
+static int prepare_v(qeb_ctx* c, const double* v)
+{
+    const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
+    const void* vd = nullptr;
+    int rc = stage_in(c, v, nnr * 8, c->v_d, &vd);
+    if (rc) return rc;
+    QEB_CUDA(c, c->vp_d.ensure(nnr * 8));
+    const double scale = 1.0 / ((double)c->nr1 * c->nr2 * c->nr3);
+    QEB_CUDA(c, vloc_prepare_v((const double*)vd, (double*)c->vp_d.p, c->fpx.rev, c->nr1, c->nr2, c->nr3, scale, c->stream));
+    c->T.vp = (const double*)c->vp_d.p;
+    c->have_v = true;
+    return 0;
+}
+
+int qeb_set_vloc(qeb_ctx* c, const double* vrs)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_grid) QEB_FAIL(c, 30, "qeb_set_vloc: qeb_set_grid has not been called");
+    if (!vrs) QEB_FAIL(c, 31, "qeb_set_vloc: null potential");
+    int rc = prepare_v(c, vrs);
+    if (rc) return rc;
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int qeb_set_nonlocal(qeb_ctx* c, int nat, int nhm, const int* nh_of_atom, const int* ofsbeta, const double* deeq)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (nat < 0 || nhm < 0) QEB_FAIL(c, 40, "qeb_set_nonlocal: bad arguments");
+    if (nat > 0 && (!nh_of_atom || !ofsbeta || !deeq)) QEB_FAIL(c, 40, "qeb_set_nonlocal: null arrays");
+    int nkb_max = 0;
+    for (int a = 0; a < nat; ++a) {
+        if (nh_of_atom[a] < 0 || nh_of_atom[a] > nhm || ofsbeta[a] < 0) QEB_FAIL(c, 41, "qeb_set_nonlocal: bad nh/ofsbeta");
+        nkb_max = std::max(nkb_max, ofsbeta[a] + nh_of_atom[a]);
+    }
+    std::vector<int> host((size_t)nkb_max + 2 * (size_t)nat + 4, -1);
+    for (int a = 0; a < nat; ++a)
+        for (int ih = 0; ih < nh_of_atom[a]; ++ih) host[ofsbeta[a] + ih] = a;
+    for (int a = 0; a < nat; ++a) {
+        host[nkb_max + a] = ofsbeta[a];
+        host[nkb_max + nat + a] = nh_of_atom[a];
+    }
+    QEB_CUDA(c, c->nlint_d.ensure(host.size() * 4));
+    QEB_CUDA(c, cudaMemcpyAsync(c->nlint_d.p, host.data(), host.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    c->row_atom_d = (const int*)c->nlint_d.p;
+    c->ofs_d = c->row_atom_d + nkb_max;
+    c->nh_d = c->ofs_d + nat;
+    const size_t nd = (size_t)nhm * nhm * nat;
+    QEB_CUDA(c, c->deeq_d.ensure(nd * 8 + 8));
+    if (nd)
+        QEB_CUDA(c, cudaMemcpyAsync(c->deeq_d.p, deeq, nd * 8,
+                                    is_device_ptr(deeq) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->nat = nat;
+    c->nhm = nhm;
+    c->have_nl = true;
+    c->nl_rows = nkb_max;
+    return 0;
+}
+
+// ---- internal pieces ----------------------------------------------------
+static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hpsi, bool kinetic)
+{
+    if (!c->have_v) QEB_FAIL(c, 50, "V_loc: no potential set (qeb_set_vloc)");
+    VlocIO io;
+    io.psi = psi;
+    io.hpsi = hpsi;
+    io.g2kin = kinetic ? (const double*)c->g2kin_d.p : nullptr;
+    io.lda = lda;
+    io.n = n;
+    io.nbands = m;
+    io.gamma = c->gamma ? 1 : 0;
+    const int nboxes = c->gamma ? (m + 1) / 2 : m;
+    for (int b0 = 0; b0 < nboxes; b0 += c->batch) {
+        const int nb = std::min(c->batch, nboxes - b0);
+        io.band0 = c->gamma ? 2 * b0 : b0;
+        QEB_CUDA(c, vloc_launch_batch(c->T, io, c->cfg, nb, c->stream));
+    }
+    return 0;
+}
+
+static int ensure_becp(qeb_ctx* c, int nkb, int m)
+{
+    const size_t el = c->gamma ? 8 : 16;
+    QEB_CUDA(c, c->becp_d.ensure((size_t)nkb * m * el));
+    const int ldps = (nkb + 1) & ~1;
+    const size_t need = (size_t)ldps * m * el;
+    if (need > c->ps_d.cap) {
+        QEB_CUDA(c, c->ps_d.ensure(need));
+    }
+    QEB_CUDA(c, cudaMemsetAsync(c->ps_d.p, 0, need, c->stream));
+    return 0;
+}
+
+static int run_calbec(qeb_ctx* c, const cplx* beta, int npwx, int nkb, const cplx* psi, int lda, int n, int m, void* becp_out)
+{
+    int nsplit, gchunk;
+    calbec_plan(n, nkb, m, !c->gamma, c->num_sms, &nsplit, &gchunk);
+    QEB_CUDA(c, c->part_d.ensure(calbec_workspace_bytes(nkb, m, nsplit, !c->gamma)));
+    QEB_CUDA(c, launch_calbec(beta, npwx, psi, lda, n, nkb, m, !c->gamma, c->gstart, nsplit, gchunk, c->part_d.p,
+                              becp_out, c->stream));
+    return 0;
+}
+
+static int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi)
+{
+    if (!c->have_nl) QEB_FAIL(c, 51, "add_vuspsi: qeb_set_nonlocal has not been called");
+    const int nkb = c->nkb;
+    if (nkb > c->nl_rows) QEB_FAIL(c, 52, "add_vuspsi: vkb has projectors not covered by ofsbeta/nh of qeb_set_nonlocal");
+    const int ldps = (nkb + 1) & ~1;
+    QEB_CUDA(c, launch_apply_deeq(c->becp_d.p, nkb, m, !c->gamma, c->row_atom_d, c->ofs_d, c->nh_d,
+                                  (const double*)c->deeq_d.p, c->nhm, c->ps_d.p, ldps, c->stream));
+    QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, c->ps_d.p, ldps, n, nkb, m, !c->gamma, hpsi, lda, c->stream));
+    return 0;
+}
+
+static int check_call(qeb_ctx* c, int lda, int n, int m, const void* psi, const void* hpsi, const char* who)
+{
+    if (!c->have_k) QEB_FAIL(c, 60, std::string(who) + ": qeb_set_kpoint has not been called");
+    if (n != c->npw) QEB_FAIL(c, 61, std::string(who) + ": n differs from the npw of qeb_set_kpoint");
+    if (lda < n || m < 0 || !psi || !hpsi) QEB_FAIL(c, 62, std::string(who) + ": bad arguments");
+    return 0;
+}
+
+static int h_psi_cols(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool do_vloc, bool do_nl,
+                      bool kinetic)
+{
+    int rc;
+    if (kinetic && lda > n)
+        QEB_CUDA(c, cudaMemset2DAsync(hpsi_d + n, (size_t)lda * 16, 0, (size_t)(lda - n) * 16, m, c->stream));
+    if (do_vloc && (rc = run_vloc(c, lda, n, m, psi_d, hpsi_d, kinetic))) return rc;
+    if (do_nl && c->nkb > 0) {
+        if ((rc = ensure_becp(c, c->nkb, m))) return rc;
+        if ((rc = run_calbec(c, c->vkb_d, c->npwx, c->nkb, psi_d, lda, n, m, c->becp_d.p))) return rc;
+        c->becp_m = m;
+        if ((rc = run_addvus(c, lda, n, m, hpsi_d))) return rc;
+    }
+    if (kinetic && c->gamma && c->gstart == 2) QEB_CUDA(c, launch_zero_im_g0(hpsi_d, lda, m, c->stream));
+    return 0;
+}
+
+int qeb_h_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_h_psi");
+    if (rc) return rc;
+    if (m == 0) return 0;
+    const size_t bytes = (size_t)lda * m * 16;
+    const void* psi_d;
+    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
+    const bool out_dev = is_device_ptr(hpsi);
+    cplx* hpsi_d = (cplx*)hpsi;
+    if (!out_dev) {
+        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
+        hpsi_d = (cplx*)c->hpsi_stage.p;
+    }
+    if ((rc = h_psi_cols(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true, true, true))) return rc;
+    if (!out_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hpsi_d, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+static int vloc_entry(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v, void* hpsi, bool want_gamma,
+                      const char* who)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, psi, hpsi, who);
+    if (rc) return rc;
+    if (want_gamma != c->gamma) QEB_FAIL(c, 63, std::string(who) + ": grid was set with a different gamma_only");
+    if (m == 0) return 0;
+    if (v && (rc = prepare_v(c, v))) return rc;
+    const size_t bytes = (size_t)lda * m * 16;
+    const void* psi_d;
+    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
+    const bool out_dev = is_device_ptr(hpsi);
+    const void* hin;
+    if ((rc = stage_in(c, hpsi, bytes, c->hpsi_stage, &hin))) return rc;  // INOUT
+    cplx* hpsi_d = (cplx*)hin;
+    if ((rc = h_psi_cols(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true, false, false))) return rc;
+    if (!out_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hpsi_d, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+int qeb_vloc_psi_k(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v, void* hpsi)
+{
+    return vloc_entry(c, lda, n, m, psi, v, hpsi, false, "qeb_vloc_psi_k");
+}
+int qeb_vloc_psi_gamma(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v, void* hpsi)
+{
+    return vloc_entry(c, lda, n, m, psi, v, hpsi, true, "qeb_vloc_psi_gamma");
+}
+
+int qeb_calbec(qeb_ctx* c, int n, const void* beta, int nkb, const void* psi, int lda, int m, void* becp)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_k) QEB_FAIL(c, 70, "qeb_calbec: qeb_set_kpoint has not been called");
+    if (n < 1 || n > c->npwx || lda < n || m < 0 || !psi || !becp) QEB_FAIL(c, 71, "qeb_calbec: bad arguments");
+    if (!beta) {
+        if (nkb != c->nkb) QEB_FAIL(c, 72, "qeb_calbec: nkb differs from the context's vkb");
+        beta = c->vkb_d;
+    }
+    if (nkb == 0 || m == 0) return 0;
+    int rc;
+    const void *beta_d, *psi_d;
+    if ((rc = stage_in(c, beta, (size_t)c->npwx * nkb * 16, c->beta_stage, &beta_d))) return rc;
+    if ((rc = stage_in(c, psi, (size_t)lda * m * 16, c->psi_stage, &psi_d))) return rc;
+    const size_t el = c->gamma ? 8 : 16;
+    const bool keep = (beta_d == (const void*)c->vkb_d);
+    void* out_d;
+    if (keep) {
+        if ((rc = ensure_becp(c, nkb, m))) return rc;
+        out_d = c->becp_d.p;
+    } else {
+        QEB_CUDA(c, c->misc_stage.ensure((size_t)nkb * m * el));
+        out_d = c->misc_stage.p;
+    }
+    if ((rc = run_calbec(c, (const cplx*)beta_d, c->npwx, nkb, (const cplx*)psi_d, lda, n, m, out_d))) return rc;
+    if (keep) c->becp_m = m;
+    QEB_CUDA(c, cudaMemcpyAsync(becp, out_d, (size_t)nkb * m * el,
+                                is_device_ptr(becp) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    if (!is_device_ptr(becp)) {
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+int qeb_add_vuspsi(qeb_ctx* c, int lda, int n, int m, void* hpsi, const void* becp)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, hpsi, hpsi, "qeb_add_vuspsi");
+    if (rc) return rc;
+    if (m == 0 || c->nkb == 0) return 0;
+    const size_t el = c->gamma ? 8 : 16;
+    if (becp) {
+        if ((rc = ensure_becp(c, c->nkb, m))) return rc;
+        QEB_CUDA(c, cudaMemcpyAsync(c->becp_d.p, becp, (size_t)c->nkb * m * el,
+                                    is_device_ptr(becp) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+        c->becp_m = m;
+    } else if (c->becp_m < m) {
+        QEB_FAIL(c, 73, "qeb_add_vuspsi: no projections in the context for these bands");
+    }
+    const size_t bytes = (size_t)lda * m * 16;
+    const bool out_dev = is_device_ptr(hpsi);
+    const void* hin;
+    if ((rc = stage_in(c, hpsi, bytes, c->hpsi_stage, &hin))) return rc;
+    if ((rc = run_addvus(c, lda, n, m, (cplx*)hin))) return rc;
+    if (!out_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hin, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+int qeb_get_becp(qeb_ctx* c, void* becp, int m)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (m > c->becp_m || !becp) QEB_FAIL(c, 74, "qeb_get_becp: no projections for that many bands");
+    const size_t el = c->gamma ? 8 : 16;
+    QEB_CUDA(c, cudaMemcpyAsync(becp, c->becp_d.p, (size_t)c->nkb * m * el,
+                                is_device_ptr(becp) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int qeb_nonlocal_only(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_nonlocal_only");
+    if (rc) return rc;
+    if (!is_device_ptr(psi) || !is_device_ptr(hpsi)) QEB_FAIL(c, 75, "qeb_nonlocal_only: device pointers required");
+    if ((rc = h_psi_cols(c, lda, n, m, (const cplx*)psi, (cplx*)hpsi, false, true, false))) return rc;
+    return finish(c);
+}
+
+int qeb_fft(qeb_ctx* c, int sign, int kind, void* f, int howmany)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_grid) QEB_FAIL(c, 80, "qeb_fft: qeb_set_grid has not been called");
+    if (!f || howmany < 1 || sign == 0 || (kind != QEB_FFT_RHO && kind != QEB_FFT_WAVE)) QEB_FAIL(c, 81, "qeb_fft: bad arguments");
+    const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
+    const size_t bytes = nnr * 16 * howmany;
+    const bool dev = is_device_ptr(f);
+    const void* fin;
+    int rc;
+    if ((rc = stage_in(c, f, bytes, c->hpsi_stage, &fin))) return rc;
+    QEB_CUDA(c, fullfft_launch(c->fpx, c->fpy, c->fpz, (cplx*)fin, howmany, sign, c->max_smem, c->stream));
+    if (!dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(f, fin, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+int qeb_divide_all(int m, int nproc, int me, int* start, int* end)
+{
+    if (m < 0 || nproc < 1 || me < 0 || me >= nproc || !start || !end) return 1;
+    const int base = m / nproc, rest = m % nproc;
+    // first `rest` groups get base+1 columns (UtilXlib/divide.f90:55-106)
+    const int s = me * base + (me < rest ? me : rest);
+    *start = s;
+    *end = s + base + (me < rest ? 1 : 0);
+    return 0;
+}
+
+int qeb_set_nccl(qeb_ctx* c, void* comm, int nranks, int rank)
+{
+    if (!c || nranks < 1 || rank < 0 || rank >= nranks) return 1;
+    c->nccl = comm;
+    c->nranks = nranks;
+    c->rank = rank;
+    return 0;
+}
+
+int qeb_h_psi_bgrp(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi, int nbgrp, int my_bgrp)
+{
+    if (!c) return 1;
+    int s, e;
+    if (qeb_divide_all(m, nbgrp, my_bgrp, &s, &e)) QEB_FAIL(c, 90, "qeb_h_psi_bgrp: bad band-group arguments");
+    if (e == s) return 0;
+    const char* p = (const char*)psi + (size_t)s * lda * 16;
+    char* h = (char*)hpsi + (size_t)s * lda * 16;
+    return qeb_h_psi(c, lda, n, e - s, p, h);
+}
+
+int qeb_get_stats(qeb_ctx* c, double* vloc_bytes_per_band, double* gemm_flops_per_band, int* nst, int* nxw, int* nboxes)
+{
+    if (!c || !c->have_k) return 1;
+    const HostVlocTables& H = c->H;
+    double fftb = 16.0 * (4.0 * H.nst * H.nr3 + 4.0 * (double)H.nxw * H.nr2 * H.nr3);
+    if (c->gamma) fftb *= 0.5;
+    if (vloc_bytes_per_band) *vloc_bytes_per_band = fftb + 60.0 * c->npw;
+    if (gemm_flops_per_band) *gemm_flops_per_band = (c->gamma ? 8.0 : 16.0) * (double)c->nkb * c->npw;
+    if (nst) *nst = H.nst;
+    if (nxw) *nxw = H.nxw;
+    if (nboxes) *nboxes = c->batch;
+    return 0;
+}
+
+}  // extern "C"

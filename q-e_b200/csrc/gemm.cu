@@ -1,0 +1,480 @@
+// Nonlocal projector contractions on the FP64 tensor pipe (DMMA, SASS
+// DMMA.8x8x4 via mma.sync.m8n8k4.f64):
+//   calbec      becp = vkb^H psi                  Modules/becmod.f90:431-486 (k), :274-334 (Gamma)
+//   add_vuspsi  hpsi += vkb (blockdiag(D) becp)   PW/src/add_vuspsi.f90:125-171 (k), :68-122 (Gamma)
+// Complex arithmetic is mapped onto the real MMA without de-interleaving:
+//   calbec : the K index runs over the 2*npw real numbers of a column; the
+//            imaginary part of the result uses the same A fragment and the B
+//            fragment J*psi = (Im psi, -Re psi), formed in registers.
+//   add_vu : computed transposed (MMA-M = bands, MMA-N = real rows of hpsi,
+//            K = (projector, re/im)); the B fragment [vr -vi; vi vr] is formed
+//            in registers from one 16-byte load of vkb(g,i).
+// Both kernels: 256 threads, 8 warps, warp tile 32x(64 real columns), cp.async
+// multi-stage pipeline, split-K with a fixed-order reduction (deterministic).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "common.cuh"
+#include "gemm.h"
+
+namespace qeb {
+
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, bool valid)
+{
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    const int sz = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+
+// ---------------------------------------------------------------------------
+// calbec partial products
+// ---------------------------------------------------------------------------
+constexpr int CB_MT = 128;      // projectors per CTA
+constexpr int CB_KC = 32;       // doubles of K per stage (16 complex G-vectors)
+constexpr int CB_LDK = CB_KC + 4;
+constexpr int CB_STAGES = 3;
+template <bool CPLX>
+struct CbCfg {
+    static constexpr int NT = CPLX ? 64 : 128;  // bands per CTA
+    static constexpr int NJ = CPLX ? 4 : 8;     // 8-band blocks per warp
+    static constexpr size_t stage_doubles = (size_t)(CB_MT + NT) * CB_LDK;
+    static constexpr size_t smem = stage_doubles * 8 * CB_STAGES;
+};
+
+template <bool CPLX>
+__global__ void __launch_bounds__(256, 1)
+k_calbec(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi, int lda, int n, int nkb, int m,
+         int gchunk, void* __restrict__ part)
+{
+    using C = CbCfg<CPLX>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* sm = reinterpret_cast<double*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 3, wn = warp >> 2;
+    const int r = lane >> 2, k = lane & 3;
+    const int i0 = blockIdx.x * CB_MT, j0 = blockIdx.y * C::NT;
+    const int g_beg = blockIdx.z * gchunk;
+    const int g_end = min(n, g_beg + gchunk);
+    const int nkt = (g_end - g_beg + 15) / 16;
+
+    double acc[4][CPLX ? 8 : 8][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+
+    auto load_stage = [&](int st, int kt) {
+        double* As = sm + (size_t)st * C::stage_doubles;
+        double* Bs = As + (size_t)CB_MT * CB_LDK;
+        const int g0 = g_beg + kt * 16;
+#pragma unroll
+        for (int it = 0; it < CB_MT * 16 / 256; ++it) {
+            const int c = tid + it * 256;
+            const int row = c >> 4, cc = c & 15;
+            const bool ok = (i0 + row < nkb) && (g0 + cc < g_end) && kt < nkt;
+            const cplx* src = ok ? vkb + (size_t)(i0 + row) * npwx + g0 + cc : vkb;
+            cp_async16(As + row * CB_LDK + 2 * cc, src, ok);
+        }
+#pragma unroll
+        for (int it = 0; it < C::NT * 16 / 256; ++it) {
+            const int c = tid + it * 256;
+            const int row = c >> 4, cc = c & 15;
+            const bool ok = (j0 + row < m) && (g0 + cc < g_end) && kt < nkt;
+            const cplx* src = ok ? psi + (size_t)(j0 + row) * lda + g0 + cc : psi;
+            cp_async16(Bs + row * CB_LDK + 2 * cc, src, ok);
+        }
+    };
+
+#pragma unroll
+    for (int s = 0; s < CB_STAGES - 1; ++s) {
+        load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nkt; ++kt) {
+        cp_async_wait<CB_STAGES - 2>();
+        __syncthreads();
+        load_stage((kt + CB_STAGES - 1) % CB_STAGES, kt + CB_STAGES - 1);
+        cp_async_commit();
+        const double* As = sm + (size_t)(kt % CB_STAGES) * C::stage_doubles;
+        const double* Bs = As + (size_t)CB_MT * CB_LDK;
+        const double* Aw = As + (size_t)(wm * 32 + r) * CB_LDK + k;
+#pragma unroll
+        for (int kk = 0; kk < CB_KC; kk += 4) {
+            double a[4];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi) a[mi] = Aw[(size_t)mi * 8 * CB_LDK + kk];
+            if (CPLX) {
+                const double* Bw = Bs + (size_t)(wn * 32 + r) * CB_LDK + (k & 2);
+#pragma unroll
+                for (int nj = 0; nj < 4; ++nj) {
+                    const double2 bb = *reinterpret_cast<const double2*>(Bw + (size_t)nj * 8 * CB_LDK + kk);
+                    const double bre = (k & 1) ? bb.y : bb.x;
+                    const double bim = (k & 1) ? -bb.x : bb.y;
+#pragma unroll
+                    for (int mi = 0; mi < 4; ++mi) {
+                        dmma(acc[mi][nj][0], acc[mi][nj][1], a[mi], bre);
+                        dmma(acc[mi][nj + 4][0], acc[mi][nj + 4][1], a[mi], bim);
+                    }
+                }
+            } else {
+                const double* Bw = Bs + (size_t)(wn * 64 + r) * CB_LDK + k;
+#pragma unroll
+                for (int nj = 0; nj < 8; ++nj) {
+                    const double b = Bw[(size_t)nj * 8 * CB_LDK + kk];
+#pragma unroll
+                    for (int mi = 0; mi < 4; ++mi) dmma(acc[mi][nj][0], acc[mi][nj][1], a[mi], b);
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+    // partials: part[s][j][i]
+    const size_t sbase = (size_t)blockIdx.z * m;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi) {
+        const int i = i0 + wm * 32 + mi * 8 + r;
+        if (i >= nkb) continue;
+        if (CPLX) {
+            cplx* P = reinterpret_cast<cplx*>(part);
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int j = j0 + wn * 32 + nj * 8 + 2 * k + e;
+                    if (j < m) P[(sbase + j) * nkb + i] = mk(acc[mi][nj][e], acc[mi][nj + 4][e]);
+                }
+        } else {
+            double* P = reinterpret_cast<double*>(part);
+#pragma unroll
+            for (int nj = 0; nj < 8; ++nj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int j = j0 + wn * 64 + nj * 8 + 2 * k + e;
+                    if (j < m) P[(sbase + j) * nkb + i] = acc[mi][nj][e];
+                }
+        }
+    }
+}
+
+// fixed-order reduction over the K splits (+ Gamma correction, becmod.f90:315-324)
+template <bool CPLX>
+__global__ void k_calbec_reduce(const void* __restrict__ part, int nsplit, int nkb, int m, void* __restrict__ becp,
+                                const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi, int lda,
+                                int gstart)
+{
+    const size_t tot = (size_t)nkb * m;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < tot; e += (size_t)gridDim.x * blockDim.x) {
+        if (CPLX) {
+            const cplx* P = reinterpret_cast<const cplx*>(part);
+            double sx = 0.0, sy = 0.0;
+            for (int s = 0; s < nsplit; ++s) {
+                const cplx v = P[(size_t)s * tot + e];
+                sx += v.x;
+                sy += v.y;
+            }
+            reinterpret_cast<cplx*>(becp)[e] = mk(sx, sy);
+        } else {
+            const double* P = reinterpret_cast<const double*>(part);
+            double sx = 0.0;
+            for (int s = 0; s < nsplit; ++s) sx += P[(size_t)s * tot + e];
+            sx *= 2.0;
+            if (gstart == 2) {
+                const int j = (int)(e / nkb), i = (int)(e - (size_t)j * nkb);
+                sx -= vkb[(size_t)i * npwx].x * psi[(size_t)j * lda].x;
+            }
+            reinterpret_cast<double*>(becp)[e] = sx;
+        }
+    }
+}
+
+// ps(ofs+ih, j) = sum_jh deeq(ih,jh,na) becp(ofs+jh, j)   (add_vuspsi.f90:151-155, :92-97)
+template <bool CPLX>
+__global__ void k_apply_deeq(const void* __restrict__ becp, int nkb, int m, const int* __restrict__ row_atom,
+                             const int* __restrict__ ofs, const int* __restrict__ nh, const double* __restrict__ deeq,
+                             int nhm, void* __restrict__ ps, int ldps)
+{
+    const size_t tot = (size_t)nkb * m;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < tot; e += (size_t)gridDim.x * blockDim.x) {
+        const int j = (int)(e / nkb), i = (int)(e - (size_t)j * nkb);
+        const int na = row_atom[i];
+        if (na < 0) {  // row not covered by any atom: contributes nothing
+            if (CPLX)
+                reinterpret_cast<cplx*>(ps)[(size_t)j * ldps + i] = mk(0.0, 0.0);
+            else
+                reinterpret_cast<double*>(ps)[(size_t)j * ldps + i] = 0.0;
+            continue;
+        }
+        const int o = ofs[na], ih = i - o, nn = nh[na];
+        const double* D = deeq + (size_t)na * nhm * nhm + ih;
+        if (CPLX) {
+            const cplx* B = reinterpret_cast<const cplx*>(becp) + (size_t)j * nkb + o;
+            double sx = 0.0, sy = 0.0;
+            for (int jh = 0; jh < nn; ++jh) {
+                const double d = D[(size_t)jh * nhm];
+                sx += d * B[jh].x;
+                sy += d * B[jh].y;
+            }
+            reinterpret_cast<cplx*>(ps)[(size_t)j * ldps + i] = mk(sx, sy);
+        } else {
+            const double* B = reinterpret_cast<const double*>(becp) + (size_t)j * nkb + o;
+            double sx = 0.0;
+            for (int jh = 0; jh < nn; ++jh) sx += D[(size_t)jh * nhm] * B[jh];
+            reinterpret_cast<double*>(ps)[(size_t)j * ldps + i] = sx;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// add_vuspsi: hpsi(g,j) += sum_i vkb(g,i) ps(i,j)
+// ---------------------------------------------------------------------------
+constexpr int AV_BT = 64;    // bands per CTA
+constexpr int AV_GT = 128;   // G-vectors per CTA
+constexpr int AV_LDV = AV_GT + 2;
+constexpr int AV_KI = 16;    // projectors per stage
+constexpr int AV_STAGES = 4;
+template <bool CPLX>
+struct AvCfg {
+    static constexpr int KD = CPLX ? 32 : 16;  // doubles of ps per band per stage
+    static constexpr int LDK = KD + 4;
+    static constexpr size_t ps_doubles = (size_t)AV_BT * LDK;
+    static constexpr size_t stage_doubles = ps_doubles + (size_t)AV_KI * AV_LDV * 2;
+    static constexpr size_t smem = stage_doubles * 8 * AV_STAGES;
+};
+
+template <bool CPLX>
+__global__ void __launch_bounds__(256, 1)
+k_addvus(const cplx* __restrict__ vkb, int npwx, const void* __restrict__ ps_, int ldps, int n, int nkb, int m,
+         cplx* __restrict__ hpsi, int lda)
+{
+    using C = AvCfg<CPLX>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* sm = reinterpret_cast<double*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 1, wn = warp >> 1;
+    const int r = lane >> 2, k = lane & 3;
+    const int j0 = blockIdx.x * AV_BT, g0 = blockIdx.y * AV_GT;
+    const int nkt = (nkb + AV_KI - 1) / AV_KI;
+    const double* psd = reinterpret_cast<const double*>(ps_);
+    const int ldps_d = CPLX ? 2 * ldps : ldps;  // doubles per band column
+
+    double acc[4][8][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+
+    auto load_stage = [&](int st, int kt) {
+        double* Ps = sm + (size_t)st * C::stage_doubles;
+        cplx* Vs = reinterpret_cast<cplx*>(Ps + C::ps_doubles);
+        const int ib = kt * AV_KI;
+        // ps tile: AV_BT bands x KD doubles, 16-byte chunks
+        constexpr int CH = C::KD / 2;  // chunks per band
+#pragma unroll
+        for (int it = 0; it < (AV_BT * CH + 255) / 256; ++it) {
+            const int c = tid + it * 256;
+            if (c < AV_BT * CH) {
+                const int row = c / CH, cc = c % CH;
+                const int d0 = (CPLX ? 2 * ib : ib) + 2 * cc;  // first double index within the band column
+                const bool ok = (j0 + row < m) && (d0 < (CPLX ? 2 * nkb : ldps)) && kt < nkt;
+                const double* src = ok ? psd + (size_t)(j0 + row) * ldps_d + d0 : psd;
+                cp_async16(Ps + row * C::LDK + 2 * cc, src, ok);
+            }
+        }
+        // vkb tile: AV_KI projectors x AV_GT G-vectors
+#pragma unroll
+        for (int it = 0; it < AV_KI * AV_GT / 256; ++it) {
+            const int c = tid + it * 256;
+            const int row = c / AV_GT, cc = c % AV_GT;
+            const bool ok = (ib + row < nkb) && (g0 + cc < n) && kt < nkt;
+            const cplx* src = ok ? vkb + (size_t)(ib + row) * npwx + g0 + cc : vkb;
+            cp_async16(Vs + row * AV_LDV + cc, src, ok);
+        }
+    };
+
+#pragma unroll
+    for (int s = 0; s < AV_STAGES - 1; ++s) {
+        load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nkt; ++kt) {
+        cp_async_wait<AV_STAGES - 2>();
+        __syncthreads();
+        load_stage((kt + AV_STAGES - 1) % AV_STAGES, kt + AV_STAGES - 1);
+        cp_async_commit();
+        const double* Ps = sm + (size_t)(kt % AV_STAGES) * C::stage_doubles;
+        const cplx* Vs = reinterpret_cast<const cplx*>(Ps + C::ps_doubles);
+        const double* Aw = Ps + (size_t)(wm * 32 + r) * C::LDK + k;
+#pragma unroll
+        for (int kk = 0; kk < C::KD; kk += 4) {
+            double a[4];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi) a[mi] = Aw[(size_t)mi * 8 * C::LDK + kk];
+            if (CPLX) {
+                // K index (i, c'): i = kk/2 + (k>>1), c' = k&1 ; N index (g, c): g = .. + (r>>1), c = r&1
+                const cplx* Vw = Vs + (size_t)(kk / 2 + (k >> 1)) * AV_LDV + wn * 32 + (r >> 1);
+#pragma unroll
+                for (int nj = 0; nj < 8; ++nj) {
+                    const double2 v = *reinterpret_cast<const double2*>(Vw + nj * 4);
+                    const double b = (r & 1) ? ((k & 1) ? v.x : v.y) : ((k & 1) ? -v.y : v.x);
+#pragma unroll
+                    for (int mi = 0; mi < 4; ++mi) dmma(acc[mi][nj][0], acc[mi][nj][1], a[mi], b);
+                }
+            } else {
+                // K index i = kk + k ; N index: real row 2*g + c = 2*(wn*32 + nj*4) + r
+                const double* Vw = reinterpret_cast<const double*>(Vs + (size_t)(kk + k) * AV_LDV + wn * 32) + r;
+#pragma unroll
+                for (int nj = 0; nj < 8; ++nj) {
+                    const double b = Vw[nj * 8];
+#pragma unroll
+                    for (int mi = 0; mi < 4; ++mi) dmma(acc[mi][nj][0], acc[mi][nj][1], a[mi], b);
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi) {
+        const int j = j0 + wm * 32 + mi * 8 + r;
+        if (j >= m) continue;
+#pragma unroll
+        for (int nj = 0; nj < 8; ++nj) {
+            const int g = g0 + wn * 32 + nj * 4 + k;
+            if (g < n) {
+                cplx* h = hpsi + (size_t)j * lda + g;
+                const cplx o = *h;
+                *h = mk(o.x + acc[mi][nj][0], o.y + acc[mi][nj][1]);
+            }
+        }
+    }
+}
+
+// Gamma: Im hpsi(G=0) = 0 (h_psi.f90:294-295)
+__global__ void k_zero_im_g0(cplx* hpsi, int lda, int m)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < m) hpsi[(size_t)j * lda].y = 0.0;
+}
+
+// ---------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------
+static int g_smem_set = 0;
+static cudaError_t set_smem_attrs()
+{
+    if (g_smem_set) return cudaSuccess;
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_calbec<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CbCfg<true>::smem))) return e;
+    if ((e = cudaFuncSetAttribute(k_calbec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CbCfg<false>::smem))) return e;
+    if ((e = cudaFuncSetAttribute(k_addvus<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AvCfg<true>::smem))) return e;
+    if ((e = cudaFuncSetAttribute(k_addvus<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AvCfg<false>::smem))) return e;
+    g_smem_set = 1;
+    return cudaSuccess;
+}
+
+void calbec_plan(int n, int nkb, int m, bool cplx_mode, int num_sms, int* nsplit, int* gchunk)
+{
+    const int NT = cplx_mode ? 64 : 128;
+    const long tiles = (long)((nkb + CB_MT - 1) / CB_MT) * ((m + NT - 1) / NT);
+    const int max_split = 64;
+    // each split handles >= 256 G-vectors (16 k-tiles); pick the split count
+    // that best fills whole waves of num_sms CTAs
+    int smax = n / 256;
+    if (smax < 1) smax = 1;
+    if (smax > max_split) smax = max_split;
+    int best = 1;
+    double beste = -1.0;
+    for (int s = 1; s <= smax; ++s) {
+        const long ctas = tiles * s;
+        const long waves = (ctas + num_sms - 1) / num_sms;
+        double eff = (double)ctas / (double)(waves * num_sms);
+        // mild preference for fewer splits (less reduction traffic)
+        eff -= 0.002 * s;
+        if (eff > beste) {
+            beste = eff;
+            best = s;
+        }
+    }
+    int chunk = (n + best - 1) / best;
+    chunk = (chunk + 15) / 16 * 16;
+    if (chunk < 16) chunk = 16;
+    best = (n + chunk - 1) / chunk;
+    if (best < 1) best = 1;
+    *nsplit = best;
+    *gchunk = chunk;
+}
+
+size_t calbec_workspace_bytes(int nkb, int m, int nsplit, bool cplx_mode)
+{
+    return (size_t)nsplit * nkb * m * (cplx_mode ? 16 : 8);
+}
+
+cudaError_t launch_calbec(const cplx* vkb, int npwx, const cplx* psi, int lda, int n, int nkb, int m, bool cplx_mode,
+                          int gstart, int nsplit, int gchunk, void* part, void* becp, cudaStream_t st)
+{
+    cudaError_t e = set_smem_attrs();
+    if (e) return e;
+    if (nkb <= 0 || m <= 0) return cudaSuccess;
+    const int NT = cplx_mode ? 64 : 128;
+    dim3 grid((nkb + CB_MT - 1) / CB_MT, (m + NT - 1) / NT, nsplit);
+    if (cplx_mode)
+        k_calbec<true><<<grid, 256, CbCfg<true>::smem, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, part);
+    else
+        k_calbec<false><<<grid, 256, CbCfg<false>::smem, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, part);
+    const size_t tot = (size_t)nkb * m;
+    int blocks = (int)((tot + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (cplx_mode)
+        k_calbec_reduce<true><<<blocks, 256, 0, st>>>(part, nsplit, nkb, m, becp, vkb, npwx, psi, lda, gstart);
+    else
+        k_calbec_reduce<false><<<blocks, 256, 0, st>>>(part, nsplit, nkb, m, becp, vkb, npwx, psi, lda, gstart);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_apply_deeq(const void* becp, int nkb, int m, bool cplx_mode, const int* row_atom, const int* ofs,
+                              const int* nh, const double* deeq, int nhm, void* ps, int ldps, cudaStream_t st)
+{
+    if (nkb <= 0 || m <= 0) return cudaSuccess;
+    const size_t tot = (size_t)nkb * m;
+    int blocks = (int)((tot + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (cplx_mode)
+        k_apply_deeq<true><<<blocks, 256, 0, st>>>(becp, nkb, m, row_atom, ofs, nh, deeq, nhm, ps, ldps);
+    else
+        k_apply_deeq<false><<<blocks, 256, 0, st>>>(becp, nkb, m, row_atom, ofs, nh, deeq, nhm, ps, ldps);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_addvus(const cplx* vkb, int npwx, const void* ps, int ldps, int n, int nkb, int m, bool cplx_mode,
+                          cplx* hpsi, int lda, cudaStream_t st)
+{
+    cudaError_t e = set_smem_attrs();
+    if (e) return e;
+    if (nkb <= 0 || m <= 0 || n <= 0) return cudaSuccess;
+    dim3 grid((m + AV_BT - 1) / AV_BT, (n + AV_GT - 1) / AV_GT);
+    if (cplx_mode)
+        k_addvus<true><<<grid, 256, AvCfg<true>::smem, st>>>(vkb, npwx, ps, ldps, n, nkb, m, hpsi, lda);
+    else
+        k_addvus<false><<<grid, 256, AvCfg<false>::smem, st>>>(vkb, npwx, ps, ldps, n, nkb, m, hpsi, lda);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_zero_im_g0(cplx* hpsi, int lda, int m, cudaStream_t st)
+{
+    if (m <= 0) return cudaSuccess;
+    k_zero_im_g0<<<(m + 127) / 128, 128, 0, st>>>(hpsi, lda, m);
+    return cudaGetLastError();
+}
+
+}  // namespace qeb

@@ -1,0 +1,112 @@
+// CUDA kernels of the V_loc path: thin wrappers that run the barrier-separated
+// phases of vloc_kernels.cuh. See that file for the algorithm and the
+// reference lines it replaces.
+#include "vloc.h"
+
+namespace qeb {
+
+#define QEB_SMEM extern __shared__ __align__(16) unsigned char smem_raw[]; cplx* smem = reinterpret_cast<cplx*>(smem_raw)
+
+__global__ void __launch_bounds__(256) k_vloc_zinv(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
+{
+    QEB_SMEM;
+    const int nph = zinv_nphase(t);
+    for (int ph = 0; ph < nph; ++ph) {
+        zinv_phase(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_vloc_zfwd(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
+{
+    QEB_SMEM;
+    const int nph = zfwd_nphase(t);
+    for (int ph = 0; ph < nph; ++ph) {
+        zfwd_phase(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_vloc_yinv(const __grid_constant__ VlocTables t)
+{
+    QEB_SMEM;
+    const int nph = ypass_nphase(t);
+    for (int ph = 0; ph < nph; ++ph) {
+        yinv_phase(ph, threadIdx.x, blockDim.x, t, blockIdx.x, blockIdx.y, blockIdx.z, smem);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_vloc_yfwd(const __grid_constant__ VlocTables t)
+{
+    QEB_SMEM;
+    const int nph = ypass_nphase(t);
+    for (int ph = 0; ph < nph; ++ph) {
+        yfwd_phase(ph, threadIdx.x, blockDim.x, t, blockIdx.x, blockIdx.y, blockIdx.z, smem);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_vloc_xfus(const __grid_constant__ VlocTables t)
+{
+    QEB_SMEM;
+    const int nph = xfus_nphase(t);
+    for (int ph = 0; ph < nph; ++ph) {
+        xfus_phase(ph, threadIdx.x, blockDim.x, t, blockIdx.x, blockIdx.y, smem);
+        __syncthreads();
+    }
+}
+
+__global__ void k_prepare_v(const double* __restrict__ v, double* __restrict__ vp, const int* __restrict__ rev_x,
+                            int nr1, int nr2, int nr3, double scale)
+{
+    // one block per (y, z-chunk); stage a [32 z][nr1 x] tile through shared memory so that both the
+    // x-fastest reads of v and the z-fastest writes of vp are coalesced
+    extern __shared__ double tile[];  // [32][nr1+1]
+    const int y = blockIdx.y, z0 = blockIdx.x * 32;
+    const int ld = nr1 + 1;
+    for (int i = threadIdx.x; i < 32 * nr1; i += blockDim.x) {
+        const int zl = i / nr1, x = i - zl * nr1;
+        if (z0 + zl < nr3) tile[zl * ld + x] = v[x + (size_t)nr1 * (y + (size_t)nr2 * (z0 + zl))];
+    }
+    __syncthreads();
+    const size_t npos = (size_t)nr2 * nr3;
+    for (int i = threadIdx.x; i < 32 * nr1; i += blockDim.x) {
+        const int xp = i / 32, zl = i - xp * 32;
+        if (z0 + zl < nr3) vp[(size_t)xp * npos + (size_t)y * nr3 + z0 + zl] = tile[zl * ld + rev_x[xp]] * scale;
+    }
+}
+
+cudaError_t vloc_init_attrs(size_t max_smem)
+{
+    cudaError_t e;
+    const int s = (int)max_smem;
+    if ((e = cudaFuncSetAttribute(k_vloc_zinv, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
+    if ((e = cudaFuncSetAttribute(k_vloc_zfwd, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
+    if ((e = cudaFuncSetAttribute(k_vloc_yinv, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
+    if ((e = cudaFuncSetAttribute(k_vloc_yfwd, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
+    if ((e = cudaFuncSetAttribute(k_vloc_xfus, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
+    return cudaSuccess;
+}
+
+cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
+                              cudaStream_t st)
+{
+    if (nboxes <= 0) return cudaSuccess;
+    k_vloc_zinv<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
+    k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
+    k_vloc_xfus<<<dim3(t.ntx, nboxes), cfg.threads_x, cfg.smem_x, st>>>(t);
+    k_vloc_yfwd<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
+    k_vloc_zfwd<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
+    return cudaGetLastError();
+}
+
+cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr1, int nr2, int nr3, double scale,
+                           cudaStream_t st)
+{
+    dim3 grid((nr3 + 31) / 32, nr2);
+    k_prepare_v<<<grid, 256, (size_t)32 * (nr1 + 1) * 8, st>>>(v, vp, rev_x, nr1, nr2, nr3, scale);
+    return cudaGetLastError();
+}
+
+}  // namespace qeb

@@ -1,0 +1,17 @@
+// Host launchers of the V_loc pass kernels (vloc.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include "vloc_kernels.cuh"
+namespace qeb {
+struct VlocLaunchCfg {
+    size_t smem_z, smem_y, smem_x;
+    int threads_z, threads_y, threads_x;
+};
+cudaError_t vloc_init_attrs(size_t max_smem);
+// one batch of nboxes boxes (bands for k, band pairs for Gamma)
+cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
+                              cudaStream_t st);
+// vp[xpos*npos + y*nr3 + z] = v[x = rev_x[xpos] + nr1*(y + nr2*z)] * scale
+cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr1, int nr2, int nr3, double scale,
+                           cudaStream_t st);
+}  // namespace qeb

@@ -1,0 +1,239 @@
+"""ctypes mirror of include/qeb200.h with the reference's names and argument
+meaning (PW/src/h_psi.f90:9, PW/src/vloc_psi_acc.f90:9,148,
+FFTXlib/src/fft_interfaces.f90:19-80, Modules/becmod.f90:138,
+PW/src/add_vuspsi.f90:10). Arrays follow the reference's memory layout: a
+Fortran psi(lda, m) is a C-contiguous numpy/torch array of shape (m, lda).
+Arguments may be numpy arrays (host) or torch CUDA tensors (device).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+FFT_RHO = 0
+FFT_WAVE = 1
+
+
+class QebError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return os.path.join(_HERE, "libqeb200.so")
+
+
+def load_library():
+    """Loads libqeb200.so (building it is __graft_entry__.build()'s job)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        raise QebError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (no CPU fallback)")
+    L = ctypes.CDLL(path)
+    P, I = ctypes.c_void_p, ctypes.c_int
+    L.qeb_create.argtypes = [ctypes.POINTER(P), I, P]
+    L.qeb_destroy.argtypes = [P]
+    L.qeb_last_error.argtypes = [P]
+    L.qeb_last_error.restype = ctypes.c_char_p
+    L.qeb_version.restype = ctypes.c_char_p
+    L.qeb_set_batch.argtypes = [P, I]
+    L.qeb_set_async.argtypes = [P, I]
+    L.qeb_set_grid.argtypes = [P, I, I, I, I, I, I, I, P, P, I]
+    L.qeb_set_kpoint.argtypes = [P, I, I, P, P, P, I, I]
+    L.qeb_set_vloc.argtypes = [P, P]
+    L.qeb_set_nonlocal.argtypes = [P, I, I, P, P, P]
+    L.qeb_h_psi.argtypes = [P, I, I, I, P, P]
+    L.qeb_vloc_psi_k.argtypes = [P, I, I, I, P, P, P]
+    L.qeb_vloc_psi_gamma.argtypes = [P, I, I, I, P, P, P]
+    L.qeb_fft.argtypes = [P, I, I, P, I]
+    L.qeb_calbec.argtypes = [P, I, P, I, P, I, I, P]
+    L.qeb_add_vuspsi.argtypes = [P, I, I, I, P, P]
+    L.qeb_get_becp.argtypes = [P, P, I]
+    L.qeb_divide_all.argtypes = [I, I, I, ctypes.POINTER(I), ctypes.POINTER(I)]
+    L.qeb_h_psi_bgrp.argtypes = [P, I, I, I, P, P, I, I]
+    L.qeb_set_nccl.argtypes = [P, P, I, I]
+    L.qeb_get_stats.argtypes = [P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                                ctypes.POINTER(I), ctypes.POINTER(I), ctypes.POINTER(I)]
+    L.qeb_nonlocal_only.argtypes = [P, I, I, I, P, P]
+    for name in ("qeb_create", "qeb_destroy", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
+                 "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_fft",
+                 "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
+                 "qeb_get_stats", "qeb_nonlocal_only"):
+        getattr(L, name).restype = I
+    _LIB = L
+    return L
+
+
+def divide_all(m: int, nproc: int, me: int):
+    """UtilXlib/divide.f90:55-106 -> 0-based [start, end) of group `me`."""
+    L = load_library()
+    s, e = ctypes.c_int(), ctypes.c_int()
+    if L.qeb_divide_all(m, nproc, me, ctypes.byref(s), ctypes.byref(e)):
+        raise QebError("divide_all: bad arguments")
+    return s.value, e.value
+
+
+def _ptr(a):
+    """address of a numpy array / torch tensor / None / int"""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return ctypes.c_void_p(a)
+    if isinstance(a, np.ndarray):
+        if not a.flags.c_contiguous:
+            raise QebError("array must be C-contiguous")
+        return ctypes.c_void_p(a.ctypes.data)
+    if hasattr(a, "data_ptr"):
+        if not a.is_contiguous():
+            raise QebError("tensor must be contiguous")
+        return ctypes.c_void_p(a.data_ptr())
+    raise QebError(f"unsupported array type {type(a)}")
+
+
+def _i32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.int32)
+
+
+class HPsi:
+    """One context per (process, device): the explicit form of the module state
+    h_psi reads in the reference."""
+
+    def __init__(self, device: int = 0, stream: int | None = None, batch: int | None = None):
+        self._L = load_library()
+        self._h = ctypes.c_void_p()
+        rc = self._L.qeb_create(ctypes.byref(self._h), device, ctypes.c_void_p(stream) if stream else None)
+        if rc:
+            self._h = None
+            raise QebError(f"qeb_create failed (code {rc}): a CUDA device is required, there is no CPU fallback")
+        self.gamma_only = False
+        self._keep = {}
+        if batch:
+            self.set_batch(batch)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.qeb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc, who):
+        if rc:
+            raise QebError(f"{who} failed (code {rc}): {self._L.qeb_last_error(self._h).decode()}")
+
+    # -- state setters ------------------------------------------------------
+    def set_batch(self, nboxes: int):
+        self._ck(self._L.qeb_set_batch(self._h, nboxes), "qeb_set_batch")
+
+    def set_async(self, flag: bool):
+        self._ck(self._L.qeb_set_async(self._h, int(flag)), "qeb_set_async")
+
+    def set_grid(self, nr1, nr2, nr3, nl, nlm=None, gamma_only=False, nr1x=None, nr2x=None, nr3x=None):
+        nl = _i32(nl)
+        nlm = _i32(nlm)
+        self.gamma_only = bool(gamma_only)
+        self.nr = (nr1, nr2, nr3)
+        self._ck(self._L.qeb_set_grid(self._h, nr1, nr2, nr3, nr1x or nr1, nr2x or nr2, nr3x or nr3, nl.size, _ptr(nl),
+                                      _ptr(nlm), int(gamma_only)), "qeb_set_grid")
+
+    def set_kpoint(self, npw, npwx, igk, g2kin, vkb=None, nkb=0, gstart=1):
+        igk = _i32(igk)
+        if isinstance(g2kin, np.ndarray):
+            g2kin = np.ascontiguousarray(g2kin, dtype=np.float64)
+        self.npw, self.npwx, self.nkb = npw, npwx, nkb
+        self._keep["vkb"] = vkb  # a device vkb is borrowed by the library
+        self._ck(self._L.qeb_set_kpoint(self._h, npw, npwx, _ptr(igk), _ptr(g2kin), _ptr(vkb), nkb, gstart),
+                 "qeb_set_kpoint")
+
+    def set_vloc(self, vrs):
+        self._ck(self._L.qeb_set_vloc(self._h, _ptr(vrs)), "qeb_set_vloc")
+
+    def set_nonlocal(self, nh_of_atom, ofsbeta, deeq):
+        """deeq: array laid out like Fortran deeq(nhm,nhm,nat) for the current spin, i.e. numpy shape (nat,nhm,nhm)."""
+        nh = _i32(nh_of_atom)
+        ofs = _i32(ofsbeta)
+        deeq = np.ascontiguousarray(deeq, dtype=np.float64)
+        nat = nh.size
+        nhm = deeq.shape[-1] if deeq.size else 0
+        self._ck(self._L.qeb_set_nonlocal(self._h, nat, nhm, _ptr(nh), _ptr(ofs), _ptr(deeq)), "qeb_set_nonlocal")
+
+    # -- reference entry points --------------------------------------------
+    def h_psi(self, lda, n, m, psi, hpsi):
+        self._ck(self._L.qeb_h_psi(self._h, lda, n, m, _ptr(psi), _ptr(hpsi)), "qeb_h_psi")
+        return hpsi
+
+    def h_psi_bgrp(self, lda, n, m, psi, hpsi, nbgrp, my_bgrp):
+        self._ck(self._L.qeb_h_psi_bgrp(self._h, lda, n, m, _ptr(psi), _ptr(hpsi), nbgrp, my_bgrp), "qeb_h_psi_bgrp")
+        return hpsi
+
+    def vloc_psi_k(self, lda, n, m, psi, v, hpsi):
+        self._ck(self._L.qeb_vloc_psi_k(self._h, lda, n, m, _ptr(psi), _ptr(v), _ptr(hpsi)), "qeb_vloc_psi_k")
+        return hpsi
+
+    def vloc_psi_gamma(self, lda, n, m, psi, v, hpsi):
+        self._ck(self._L.qeb_vloc_psi_gamma(self._h, lda, n, m, _ptr(psi), _ptr(v), _ptr(hpsi)), "qeb_vloc_psi_gamma")
+        return hpsi
+
+    def invfft(self, kind, f, howmany=1):
+        """invfft(kind, f, dfft, howmany): G->R, in place."""
+        self._ck(self._L.qeb_fft(self._h, +1, FFT_WAVE if kind in ("Wave", FFT_WAVE) else FFT_RHO, _ptr(f), howmany),
+                 "qeb_fft")
+        return f
+
+    def fwfft(self, kind, f, howmany=1):
+        """fwfft(kind, f, dfft, howmany): R->G, scaled, in place."""
+        self._ck(self._L.qeb_fft(self._h, -1, FFT_WAVE if kind in ("Wave", FFT_WAVE) else FFT_RHO, _ptr(f), howmany),
+                 "qeb_fft")
+        return f
+
+    def calbec(self, npw, beta, psi, betapsi, nbnd, lda=None, nkb=None):
+        """calbec(npw, beta, psi, betapsi, nbnd). beta None -> the context's vkb."""
+        if lda is None:
+            lda = psi.shape[-1]
+        if nkb is None:
+            nkb = self.nkb if beta is None else beta.shape[0]
+        self._ck(self._L.qeb_calbec(self._h, npw, _ptr(beta), nkb, _ptr(psi), lda, nbnd, _ptr(betapsi)), "qeb_calbec")
+        return betapsi
+
+    def add_vuspsi(self, lda, n, m, hpsi, becp=None):
+        self._ck(self._L.qeb_add_vuspsi(self._h, lda, n, m, _ptr(hpsi), _ptr(becp)), "qeb_add_vuspsi")
+        return hpsi
+
+    def get_becp(self, m):
+        out = np.empty((m, self.nkb), dtype=np.float64 if self.gamma_only else np.complex128)
+        self._ck(self._L.qeb_get_becp(self._h, _ptr(out), m), "qeb_get_becp")
+        return out
+
+    def nonlocal_only(self, lda, n, m, psi, hpsi):
+        self._ck(self._L.qeb_nonlocal_only(self._h, lda, n, m, _ptr(psi), _ptr(hpsi)), "qeb_nonlocal_only")
+
+    def stats(self):
+        vb, gf = ctypes.c_double(), ctypes.c_double()
+        nst, nxw, nb = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        self._ck(self._L.qeb_get_stats(self._h, ctypes.byref(vb), ctypes.byref(gf), ctypes.byref(nst),
+                                       ctypes.byref(nxw), ctypes.byref(nb)), "qeb_get_stats")
+        return dict(vloc_bytes_per_band=vb.value, gemm_flops_per_band=gf.value, nst=nst.value, nxw=nxw.value,
+                    batch=nb.value)
+
+    # -- convenience: load everything from an oracle-style descriptor --------
+    def setup_from(self, d, inp, lda=None):
+        """d: object with nr1..3, nl, nlm, gamma_only, npw, igk, g2kin, gstart (1-based maps as in the reference);
+        inp: dict with vrs, vkb (nkb, npwx), deeq, nh_at, ofsbeta."""
+        self.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
+        npwx = lda if lda is not None else inp["lda"]
+        vkb = inp.get("vkb")
+        nkb = 0 if vkb is None else vkb.shape[0]
+        self.set_kpoint(d.npw, npwx, None if d.gamma_only else d.igk, d.g2kin, vkb if nkb else None, nkb, d.gstart)
+        self.set_vloc(inp["vrs"])
+        if nkb:
+            self.set_nonlocal(inp["nh_at"], inp["ofsbeta"], inp["deeq"])

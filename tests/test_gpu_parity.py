@@ -1,0 +1,258 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through
+the C ABI (ctypes mirror qe_b200.HPsi), against the CPU oracle on identical
+seeded inputs. Tolerance: 1e-11 relative (north_star), FP64."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-11
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import torch
+
+    if not torch.cuda.is_available():
+        pytest.fail("GPU tests need a CUDA device; there is no CPU fallback")
+    import qe_b200
+    from oracle import descriptor as D
+    from oracle import hpsi_ref as R
+
+    return qe_b200, D, R, torch
+
+
+def relerr(a, b):
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+
+
+@pytest.mark.parametrize("shape", [(15, 15, 15), (25, 25, 25), (24, 20, 18), (27, 27, 27), (64, 45, 50), (75, 120, 180)])
+def test_fft_roundtrip_and_numpy(mods, shape):
+    qe, D, R, torch = mods
+    nr1, nr2, nr3 = shape
+    h = qe.HPsi()
+    h.set_grid(nr1, nr2, nr3, nl=np.array([1], dtype=np.int32))
+    rng = np.random.default_rng(1)
+    how = 2
+    f = rng.standard_normal((how, nr3, nr2, nr1)) + 1j * rng.standard_normal((how, nr3, nr2, nr1))
+    g = f.copy()
+    h.invfft("Rho", g, how)
+    ref = np.fft.ifftn(f, axes=(1, 2, 3)) * (nr1 * nr2 * nr3)
+    assert relerr(g, ref) < 1e-13
+    h.fwfft("Rho", g, how)
+    assert relerr(g, f) < 1e-13
+    # device pointer path
+    t = torch.from_numpy(f.copy()).cuda()
+    h.fwfft("Wave", t, how)
+    torch.cuda.synchronize()
+    assert relerr(t.cpu().numpy(), np.fft.fftn(f, axes=(1, 2, 3)) / (nr1 * nr2 * nr3)) < 1e-13
+    h.close()
+
+
+def test_fft_known_answer_fft_test0(mods, golden_dir):
+    """FFTXlib/examples/reference/fft_test0.out: analytic 4-coefficient transform on 75x120x180."""
+    qe, D, R, torch = mods
+    kat = json.load(open(os.path.join(golden_dir, "fft_test0.json")))
+    nr = kat["grid"]
+    box = np.zeros(nr[0] * nr[1] * nr[2], dtype=np.complex128)
+    for key, (re_, im_) in kat["coeff"].items():
+        i, j, k = (int(t) - 1 for t in key.split(","))
+        box[i + j * nr[0] + k * nr[0] * nr[1]] = re_ + 1j * im_
+    h = qe.HPsi()
+    h.set_grid(nr[0], nr[1], nr[2], nl=np.array([1], dtype=np.int32))
+    f = box.copy()
+    h.invfft("Wave", f)
+    b3 = f.reshape(nr[2], nr[1], nr[0])
+    for key, (re_, im_) in kat["fr"].items():
+        i, j, k = (int(t) for t in key.split(","))
+        assert abs(b3[k, j, i] - (re_ + 1j * im_)) < 2e-6  # printed to 6 decimals
+    h.fwfft("Wave", f)
+    assert np.abs(f - box).max() < 1e-14
+    h.close()
+
+
+SMALL = ["si2_small", "ortho_small", "si2_small_gamma", "ortho_small_gamma"]
+
+
+@pytest.mark.parametrize("name", SMALL)
+@pytest.mark.parametrize("m", [1, 2, 5, 8])
+def test_vloc_psi(mods, name, m):
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    inp = R.synthetic_inputs(d, m, [4, 4], seed=m)
+    lda, n = inp["lda"], inp["n"]
+    rng = np.random.default_rng(5)
+    h0 = rng.standard_normal((m, lda)) + 1j * rng.standard_normal((m, lda))
+    ref = h0.copy()
+    (R.vloc_psi_gamma if d.gamma_only else R.vloc_psi_k)(d, lda, n, m, inp["psi"], inp["vrs"], ref)
+    h = qe.HPsi(batch=3)
+    h.setup_from(d, inp)
+    out = h0.copy()
+    (h.vloc_psi_gamma if d.gamma_only else h.vloc_psi_k)(lda, n, m, inp["psi"], inp["vrs"], out)
+    assert relerr(out[:, :n], ref[:, :n]) < TOL
+    assert np.array_equal(out[:, n:], h0[:, n:])  # rows beyond n untouched
+    # device pointers, potential from the context
+    psi_t = torch.from_numpy(np.nan_to_num(inp["psi"])).cuda()
+    out_t = torch.from_numpy(h0.copy()).cuda()
+    (h.vloc_psi_gamma if d.gamma_only else h.vloc_psi_k)(lda, n, m, psi_t, None, out_t)
+    torch.cuda.synchronize()
+    assert relerr(out_t.cpu().numpy()[:, :n], ref[:, :n]) < TOL
+    h.close()
+
+
+@pytest.mark.parametrize("name", SMALL + ["si2", "al4"])
+@pytest.mark.parametrize("m", [1, 3, 4, 10])
+def test_h_psi(mods, name, m):
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    c = d.extra["config"]
+    nh = c.get("nh_list") or [c["nh"]] * c["nat"]
+    inp = R.synthetic_inputs(d, m, nh, seed=3)
+    lda, n = inp["lda"], inp["n"]
+    ref, becp_ref = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    out = np.full((m, lda), np.nan + 1j * np.nan)
+    h.h_psi(lda, n, m, inp["psi"], out)  # psi rows n..lda are NaN-poisoned: must be ignored
+    assert relerr(out, ref) < TOL
+    assert np.all(out[:, n:] == 0)
+    becp = h.get_becp(m)
+    assert relerr(becp, becp_ref) < TOL
+    if d.gamma_only and d.gstart == 2:
+        assert np.all(out[:, 0].imag == 0)
+    h.close()
+
+
+@pytest.mark.parametrize("name", ["ortho_small", "ortho_small_gamma"])
+def test_calbec_add_vuspsi(mods, name):
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    m = 6
+    inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=11, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    if d.gamma_only:
+        ref = R.calbec_gamma(n, inp["vkb"], inp["psi"], m, d.gstart)
+        out = np.zeros((m, inp["nkb"]))
+    else:
+        ref = R.calbec_k(n, inp["vkb"], inp["psi"], m)
+        out = np.zeros((m, inp["nkb"]), dtype=complex)
+    h.calbec(n, inp["vkb"], inp["psi"], out, m, lda=lda)  # explicit beta (host)
+    assert relerr(out, ref) < TOL
+    out2 = np.zeros_like(out)
+    h.calbec(n, None, inp["psi"], out2, m, lda=lda)  # the context's vkb
+    assert relerr(out2, ref) < TOL
+    # m == 1 edge (the reference switches to GEMV, becmod.f90:468)
+    o1 = np.zeros_like(out[:1])
+    h.calbec(n, None, inp["psi"][:1], o1, 1, lda=lda)
+    assert relerr(o1, ref[:1]) < TOL
+    ps = R.apply_deeq(ref, inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    rng = np.random.default_rng(2)
+    h0 = rng.standard_normal((m, lda)) + 1j * rng.standard_normal((m, lda))
+    href = h0.copy()
+    (R.add_vuspsi_gamma if d.gamma_only else R.add_vuspsi_k)(n, m, inp["vkb"], ps, href)
+    hout = h0.copy()
+    h.add_vuspsi(lda, n, m, hout, ref.copy())
+    assert relerr(hout, href) < TOL
+    h.close()
+
+
+def test_errors(mods):
+    qe, D, R, torch = mods
+    h = qe.HPsi()
+    with pytest.raises(qe.QebError):
+        h.set_grid(14, 15, 15, nl=np.array([1], dtype=np.int32))  # factor 7 not allowed (fft_support.f90)
+    d = D.config_descriptor("si2_small")
+    inp = R.synthetic_inputs(d, 2, [4, 4])
+    with pytest.raises(qe.QebError):
+        h.h_psi(inp["lda"], inp["n"], 2, inp["psi"], inp["psi"].copy())  # no grid/k-point yet
+    h.setup_from(d, inp)
+    with pytest.raises(qe.QebError):
+        h.h_psi(inp["lda"], inp["n"] - 1, 2, inp["psi"], inp["psi"].copy())  # n != npw of the context
+    with pytest.raises(qe.QebError):
+        h.vloc_psi_gamma(inp["lda"], inp["n"], 2, inp["psi"], None, inp["psi"].copy())  # k-point context
+    h.close()
+
+
+def test_band_groups_match_full_call(mods):
+    """h_psi over band groups (PW/src/h_psi.f90:53-67): the column blocks of divide_all, applied
+    independently, reproduce the full call bit for bit (no collective on one GPU)."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor("ortho_small")
+    m = 7
+    inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=4, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    full = np.zeros((m, lda), dtype=complex)
+    h.h_psi(lda, n, m, inp["psi"], full)
+    parts = np.zeros_like(full)
+    for g in range(3):
+        h.h_psi_bgrp(lda, n, m, inp["psi"], parts, 3, g)
+    assert relerr(parts, full) < 1e-14
+    h.close()
+
+
+@pytest.mark.parametrize("name,m,nat_used", [("h2o64", 3, 6), ("ausurf112", 2, 4)])
+def test_h_psi_full_grid_reduced_projectors(mods, name, m, nat_used):
+    """BASELINE grids at full size (135^3 Gamma, 125x64x200 k) against the oracle, with a reduced
+    projector count so that the CPU oracle finishes in seconds."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    c = d.extra["config"]
+    nh = (c.get("nh_list") or [c["nh"]] * c["nat"])[:nat_used]
+    inp = R.synthetic_inputs(d, m, nh, seed=9, lda=d.npw + 5)
+    lda, n = inp["lda"], inp["n"]
+    ref, becp_ref = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    out = np.full((m, lda), np.nan + 1j * np.nan)
+    h.h_psi(lda, n, m, inp["psi"], out)
+    assert relerr(out, ref) < TOL
+    h.close()
+
+
+def test_hermiticity_full_size_ausurf(mods):
+    """Size-independent property at BASELINE size (AUSURF112 grid, all 2016 projectors, synthetic
+    vkb generated on the device): <a|H b> = conj(<b|H a>) and linearity."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor("ausurf112")
+    n = d.npw
+    lda = n
+    nkb = 2016
+    g = torch.Generator(device="cuda").manual_seed(0)
+    vkb = torch.randn((nkb, lda, 2), generator=g, device="cuda", dtype=torch.float64) / np.sqrt(n)
+    m = 8
+    psi = torch.randn((m, lda, 2), generator=g, device="cuda", dtype=torch.float64)
+    rng = np.random.default_rng(3)
+    vrs = rng.uniform(-1, 0, d.nnr)
+    nh = np.full(112, 18, dtype=np.int32)
+    ofs = (np.arange(112) * 18).astype(np.int32)
+    deeq = rng.uniform(-1, 1, (112, 18, 18))
+    deeq = 0.5 * (deeq + deeq.transpose(0, 2, 1))
+    h = qe.HPsi()
+    h.set_grid(d.nr1, d.nr2, d.nr3, d.nl)
+    h.set_kpoint(n, lda, d.igk, d.g2kin, vkb, nkb, d.gstart)
+    h.set_vloc(vrs)
+    h.set_nonlocal(nh, ofs, deeq)
+    hpsi = torch.empty_like(psi)
+    h.h_psi(lda, n, m, psi, hpsi)
+    torch.cuda.synchronize()
+    P = torch.view_as_complex(psi)
+    Hm = torch.view_as_complex(hpsi)
+    A = P.conj() @ Hm.T  # A[a,b] = <a|H b>
+    herm = (A - A.conj().T).abs().max().item() / A.abs().max().item()
+    assert herm < 1e-11
+    # linearity: H(psi0 + 2 psi1) = H psi0 + 2 H psi1
+    comb = (P[0] + 2.0 * P[1]).contiguous()
+    cin = torch.view_as_real(comb).contiguous().reshape(1, lda, 2)
+    cout = torch.empty_like(cin)
+    h.h_psi(lda, n, 1, cin, cout)
+    torch.cuda.synchronize()
+    lin = (torch.view_as_complex(cout)[0] - (Hm[0] + 2.0 * Hm[1])).abs().max().item() / Hm.abs().max().item()
+    assert lin < 1e-12
+    h.close()
