@@ -233,7 +233,11 @@ def run_ours(args):
     deeq = 0.5 * (deeq + deeq.transpose(0, 2, 1))
     ofs = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
 
-    stream = torch.cuda.current_stream().cuda_stream
+    # a dedicated (non-default) stream: the library launches on it and the CUDA events below time it
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
     h = qe_b200.HPsi(device=local, stream=stream, batch=args.batch or None)
     h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
     h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
