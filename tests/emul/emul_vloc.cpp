@@ -6,6 +6,7 @@
 #include <string.h>
 #include <vector>
 #include "vloc_setup.h"
+#include "fullfft_kernels.cuh"
 
 using namespace qeb;
 
@@ -126,6 +127,38 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
                     for (int tid = 0; tid < nthr; ++tid) zfwd_phase(ph, tid, nthr, t, io, g, box, smem.data());
             }
         }
+    }
+    return 0;
+}
+
+extern "C" int emul_fullfft(int nr1, int nr2, int nr3, int howmany, int sign, double* f, int nthr)
+{
+    HostPlan hx, hy, hz;
+    if (!make_host_plan(nr1, hx) || !make_host_plan(nr2, hy) || !make_host_plan(nr3, hz)) return 1;
+    FullFftParams p;
+    p.nr1 = nr1; p.nr2 = nr2; p.nr3 = nr3;
+    upload_plan(hx, p.px); upload_plan(hy, p.py); upload_plan(hz, p.pz);
+    p.f = (cplx*)f;
+    p.sgn = sign > 0 ? 1.0 : -1.0;
+    p.scale = sign > 0 ? 1.0 : 1.0 / ((double)nr1 * nr2 * nr3);
+    const int ncol = nr1 * nr2, nrows = nr2 * nr3;
+    p.TZ = std::min(6, ncol); p.TYx = std::min(4, nr1); p.TXr = std::min(5, nrows);  // small odd tiles: exercise the edges
+    const int ntz = (ncol + p.TZ - 1) / p.TZ, nty = (nr1 + p.TYx - 1) / p.TYx, ntx = (nrows + p.TXr - 1) / p.TXr;
+    p.dTZ = make_fastdiv(p.TZ); p.dTZl = make_fastdiv(ncol - (ntz - 1) * p.TZ);
+    p.dTY = make_fastdiv(p.TYx); p.dTYl = make_fastdiv(nr1 - (nty - 1) * p.TYx);
+    p.dTX = make_fastdiv(p.TXr); p.dTXl = make_fastdiv(nrows - (ntx - 1) * p.TXr);
+    std::vector<cplx> smem((size_t)std::max(std::max(nr3 * p.TZ, nr2 * p.TYx), nr1 * (p.TXr + 1)) + 16);
+    for (int box = 0; box < howmany; ++box) {
+        for (int t = 0; t < ntz; ++t)
+            for (int ph = 0; ph < p.pz.npass; ++ph)
+                for (int tid = 0; tid < nthr; ++tid) fullz_phase(ph, tid, nthr, p, t, box, smem.data());
+        for (int z = 0; z < nr3; ++z)
+            for (int t = 0; t < nty; ++t)
+                for (int ph = 0; ph < p.py.npass; ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) fully_phase(ph, tid, nthr, p, t, z, box, smem.data());
+        for (int t = 0; t < ntx; ++t)
+            for (int ph = 0; ph < fullx_nphase(p); ++ph)
+                for (int tid = 0; tid < nthr; ++tid) fullx_phase(ph, tid, nthr, p, t, box, smem.data());
     }
     return 0;
 }

@@ -1,0 +1,100 @@
+"""CPU execution of the CUDA kernels' phase functions (tests/emul): the index /
+twiddle / stick-table logic of q-e_b200/csrc/vloc_kernels.cuh, run serially
+with plain g++, must reproduce the oracle. This is test infrastructure only -
+the product path never runs on the CPU."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import descriptor as D
+from oracle import hpsi_ref as R
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def emul():
+    so = os.path.join(HERE, "emul", "libemul.so")
+    subprocess.check_call(["sh", os.path.join(HERE, "emul", "build.sh")])
+    L = ctypes.CDLL(so)
+    P, I = ctypes.c_void_p, ctypes.c_int
+    L.emul_fft1d.argtypes = [I, I, I, P, P, I, I]
+    L.emul_vloc.argtypes = [I, I, I, I, P, P, P, I, I, I, P, P, P, P, I, I]
+    L.emul_fullfft.argtypes = [I, I, I, I, I, P, I]
+    return L
+
+
+def p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 5, 6, 8, 9, 10, 12, 15, 16, 18, 20, 24, 25, 27, 30, 32, 36, 45, 48, 50, 64, 72,
+                               75, 80, 90, 96, 100, 108, 120, 125, 128, 135, 144, 180, 200, 216, 243, 256, 288, 300, 375])
+def test_radix_passes_all_lengths(emul, n):
+    rng = np.random.default_rng(n)
+    nl = 5
+    x = rng.standard_normal((nl, n)) + 1j * rng.standard_normal((nl, n))
+    for sign, ref in ((1, np.fft.ifft(x, axis=1) * n), (-1, np.fft.fft(x, axis=1))):
+        y = np.zeros_like(x)
+        assert emul.emul_fft1d(n, sign, nl, p(x), p(y), 11, 10) == 0
+        assert np.abs(y - ref).max() / np.abs(ref).max() < 1e-14
+
+
+@pytest.mark.parametrize("maxr", [2, 3, 4, 5])
+def test_radix_passes_small_radices_only(emul, maxr):
+    """forces multi-pass plans out of the primitive butterflies (2,3,4,5)"""
+    rng = np.random.default_rng(maxr)
+    for n in (16, 27, 60, 125, 64, 81):
+        if maxr == 2 and n % 2:
+            continue
+        if maxr == 2 and n in (60,):
+            continue
+        if maxr == 3 and n % 5 == 0:
+            continue
+        if maxr == 4 and n % 5 == 0:
+            continue
+        x = rng.standard_normal((3, n)) + 1j * rng.standard_normal((3, n))
+        y = np.zeros_like(x)
+        assert emul.emul_fft1d(n, 1, 3, p(x), p(y), 7, maxr) == 0
+        ref = np.fft.ifft(x, axis=1) * n
+        assert np.abs(y - ref).max() / np.abs(ref).max() < 1e-14
+
+
+@pytest.mark.parametrize("name", ["si2_small", "ortho_small", "si2_small_gamma", "ortho_small_gamma", "si2", "al4"])
+@pytest.mark.parametrize("m,batch", [(1, 1), (3, 2), (4, 3)])
+def test_vloc_phases_match_oracle(emul, name, m, batch):
+    d = D.config_descriptor(name)
+    inp = R.synthetic_inputs(d, m, [4, 4], seed=m)
+    lda, n = inp["lda"], inp["n"]
+    rng = np.random.default_rng(0)
+    nl_ = np.ascontiguousarray(d.nl, dtype=np.int32)
+    nlm = np.ascontiguousarray(d.nlm, dtype=np.int32) if d.gamma_only else None
+    igk = None if d.gamma_only else np.ascontiguousarray(d.igk, dtype=np.int32)
+    for kin in (False, True):
+        h0 = np.zeros((m, lda), complex) if kin else rng.standard_normal((m, lda)) + 0j
+        ref = h0.copy()
+        if kin:
+            ref[:, :n] = d.g2kin[None, :n] * inp["psi"][:, :n]
+        (R.vloc_psi_gamma if d.gamma_only else R.vloc_psi_k)(d, lda, n, m, inp["psi"], inp["vrs"], ref)
+        out = h0.copy()
+        g2 = np.ascontiguousarray(d.g2kin) if kin else None
+        rc = emul.emul_vloc(d.nr1, d.nr2, d.nr3, n, p(nl_), p(nlm), p(igk), d.ngm, lda, m, p(inp["psi"]),
+                            p(inp["vrs"]), p(g2), p(out), 37, batch)
+        assert rc == 0
+        assert np.abs(out[:, :n] - ref[:, :n]).max() / np.abs(ref[:, :n]).max() < 1e-13
+
+
+@pytest.mark.parametrize("shape", [(15, 15, 15), (24, 20, 18), (25, 27, 16), (45, 8, 50)])
+def test_fullbox_fft_phases(emul, shape):
+    nr1, nr2, nr3 = shape
+    rng = np.random.default_rng(2)
+    f = rng.standard_normal((2, nr3, nr2, nr1)) + 1j * rng.standard_normal((2, nr3, nr2, nr1))
+    g = f.copy()
+    assert emul.emul_fullfft(nr1, nr2, nr3, 2, 1, p(g), 19) == 0
+    ref = np.fft.ifftn(f, axes=(1, 2, 3)) * (nr1 * nr2 * nr3)
+    assert np.abs(g - ref).max() / np.abs(ref).max() < 1e-13
+    assert emul.emul_fullfft(nr1, nr2, nr3, 2, -1, p(g), 19) == 0
+    assert np.abs(g - f).max() / np.abs(f).max() < 1e-13
