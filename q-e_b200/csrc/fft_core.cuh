@@ -155,7 +155,9 @@ template <> struct Bfly<10> { static QEB_HD void run(cplx* v, double s) { BflyCo
 template <> struct Bfly<12> { static QEB_HD void run(cplx* v, double s) { BflyComp<12, 4, 3>::run(v, s); } };
 template <> struct Bfly<15> { static QEB_HD void run(cplx* v, double s) { BflyComp<15, 3, 5>::run(v, s); } };
 template <> struct Bfly<16> { static QEB_HD void run(cplx* v, double s) { BflyComp<16, 4, 4>::run(v, s); } };
+template <> struct Bfly<20> { static QEB_HD void run(cplx* v, double s) { BflyComp<20, 4, 5>::run(v, s); } };
 template <> struct Bfly<25> { static QEB_HD void run(cplx* v, double s) { BflyComp<25, 5, 5>::run(v, s); } };
+template <> struct Bfly<27> { static QEB_HD void run(cplx* v, double s) { BflyComp<27, 3, 9>::run(v, s); } };
 
 // twiddle exp(sgn*2*pi*i*j/N) from the +sign table
 QEB_HD cplx twid(const cplx* tw, int j, double sgn)
@@ -229,6 +231,7 @@ QEB_HD void fft_pass_r(int tid, int nthr, int nl, const FastDiv& divNl, const Pa
 
 struct NoMid {
     QEB_HD cplx apply(int, int, cplx v) const { return v; }
+    QEB_HD double fetch(int, int) const { return 1.0; }
 };
 
 // Radix dispatch (warp-uniform switch).
@@ -245,6 +248,10 @@ QEB_HD void fft_pass(int tid, int nthr, int nl, const FastDiv& divNl, const Pass
     case 8: fft_pass_r<8, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     case 9: fft_pass_r<9, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     case 10: fft_pass_r<10, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
+    case 12: fft_pass_r<12, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
+    case 15: fft_pass_r<15, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
+    case 25: fft_pass_r<25, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
+    case 27: fft_pass_r<27, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     default: break;
     }
 }

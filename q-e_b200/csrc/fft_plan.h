@@ -53,29 +53,33 @@ inline cplx exact_twiddle(int j, int n)
 }
 
 // Radix choice: as few passes as possible with radices <= maxr from
-// {10, 9, 8, 6, 5, 4, 3, 2}; large radices first (DIF order).
+// {10, 9, 8, 6, 5, 4, 3, 2}; among those the most balanced list (smallest sum
+// of squares); large radices first (DIF order). fft_static.cuh instantiates
+// the same lists for the common grid sizes.
 inline bool factorize(int n, std::vector<int>& out, int maxr = 10)
 {
     static const int cand[] = {10, 9, 8, 6, 5, 4, 3, 2};
     out.clear();
     if (n < 1) return false;
     if (n == 1) return true;
-    // dynamic programming on the number of passes
-    std::vector<int> best(n + 1, 1 << 20), pick(n + 1, 0);
+    const long BIG = 1L << 40;
+    std::vector<long> best(n + 1, BIG);  // passes * 2^20 + sum of squares
+    std::vector<int> pick(n + 1, 0);
     best[1] = 0;
     for (int m = 2; m <= n; ++m) {
         if (n % m) continue;
         for (int c : cand) {
             if (c > maxr || m % c) continue;
-            if (best[m / c] + 1 < best[m]) {
-                best[m] = best[m / c] + 1;
+            if (best[m / c] >= BIG) continue;
+            const long cost = best[m / c] + (1L << 20) + (long)c * c;
+            if (cost < best[m]) {
+                best[m] = cost;
                 pick[m] = c;
             }
         }
     }
-    if (best[n] >= (1 << 20)) return false;
+    if (best[n] >= BIG) return false;
     for (int m = n; m > 1; m /= pick[m]) out.push_back(pick[m]);
-    // largest radix first
     for (size_t i = 0; i < out.size(); ++i)
         for (size_t k = i + 1; k < out.size(); ++k)
             if (out[k] > out[i]) {
@@ -86,10 +90,27 @@ inline bool factorize(int n, std::vector<int>& out, int maxr = 10)
     return (int)out.size() <= QEB_MAXPASS;
 }
 
+// Lengths with a compile-time plan in fft_static.cuh use its (large, in-register) radix list, so that
+// the fast kernels and the generic fallback share one twiddle/digit-reversal table per length.
+inline bool preferred_factors(int n, std::vector<int>& out)
+{
+    switch (n) {
+    case 15: out = {15}; return true;
+    case 25: out = {25}; return true;
+    case 27: out = {27}; return true;
+    case 64: out = {8, 8}; return true;
+    case 125: out = {25, 5}; return true;
+    case 135: out = {15, 9}; return true;
+    case 144: out = {12, 12}; return true;
+    case 200: out = {25, 8}; return true;
+    default: return false;
+    }
+}
+
 inline bool make_host_plan(int n, HostPlan& hp, int maxr = 10)
 {
     hp.n = n;
-    if (!factorize(n, hp.r, maxr)) return false;
+    if (!(maxr >= 10 && preferred_factors(n, hp.r)) && !factorize(n, hp.r, maxr)) return false;
     if (hp.r.empty()) hp.r.push_back(1);  // n == 1: not used by the kernels
     hp.L.clear();
     int L = n;

@@ -1,0 +1,115 @@
+// Compile-time FFT plans and the warp-mapped radix pass used by the fast V_loc
+// kernels (vloc_fast.cuh). Same algorithm as fft_core.cuh (in-place DIF/DIT
+// passes over positions base + A*b), but
+//   * the length and the radix list are template parameters, so every stride,
+//     sub-length and division is a constant and the pass list is unrolled;
+//   * the work mapping is "one line per lane, one butterfly index per warp":
+//     lane l owns line l of the tile (tiles have <= 32 lines), the warps stride
+//     over the N/R butterfly indices j, so (blk, a), the twiddle addresses and
+//     all table look-ups are warp-uniform and the shared-memory accesses
+//     S[pos*32 + lane] are conflict-free.
+#pragma once
+#include "fft_core.cuh"
+
+namespace qeb {
+
+template <int N_, int... Rs>
+struct SPlan {
+    static constexpr int N = N_;
+    static constexpr int NP = (int)sizeof...(Rs);
+    QEB_HD static constexpr int r(int p)
+    {
+        constexpr int a[sizeof...(Rs)] = {Rs...};
+        return a[p];
+    }
+    QEB_HD static constexpr int L(int p)
+    {
+        int l = N_;
+        for (int i = 0; i < p; ++i) l /= r(i);
+        return l;
+    }
+    // does a runtime plan (host factorisation) describe the same pass list?
+    static bool matches(const FftPlan& pl)
+    {
+        if (pl.n != N_ || pl.npass != NP) return false;
+        for (int p = 0; p < NP; ++p)
+            if (pl.r[p] != r(p)) return false;
+        return true;
+    }
+};
+
+constexpr int QEB_TL = 32;  // lines per tile = lanes
+
+// twiddle from a table that the fast kernels stage in shared memory (plain load: LDS once inlined)
+QEB_HD cplx stw(const cplx* tw, int j, double sgn) { return mk(tw[j].x, sgn * tw[j].y); }
+
+// One radix pass P of plan PL over the tile; see fft_core.cuh::fft_pass_r for the math.
+template <class PL, int P, bool DIT, bool FUSE2, class Src, class Dst, class Mid>
+QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double sgn, Src& src, Dst& dst, Mid& mid)
+{
+    constexpr int R = PL::r(P);
+    constexpr int L = PL::L(P);
+    constexpr int A = L / R;
+    constexpr int NB = PL::N / L;
+    constexpr int NJ = PL::N / R;
+    if (lane >= nl) return;
+    for (int j = warp; j < NJ; j += nwarps) {
+        const int blk = j / A;
+        const int a = j - blk * A;
+        const int base = blk * L + a;
+        cplx v[R];
+        double f[FUSE2 ? R : 1];
+        if (FUSE2) {  // issue the loads of the pointwise factor first: they overlap the tile loads and the butterfly
+#pragma unroll
+            for (int d = 0; d < R; ++d) f[d] = mid.fetch(lane, base + d);
+        }
+#pragma unroll
+        for (int b = 0; b < R; ++b) v[b] = src.load(lane, base + A * b);
+        if (DIT && A > 1) {
+            const int st = a * NB;
+#pragma unroll
+            for (int b = 1; b < R; ++b) v[b] = cmul(v[b], stw(tw, st * b, sgn));
+        }
+        Bfly<R>::run(v, sgn);
+        if (FUSE2) {
+#pragma unroll
+            for (int d = 0; d < R; ++d) v[d] = scal(v[d], f[d]);
+            Bfly<R>::run(v, -sgn);
+        }
+        if (!DIT && !FUSE2 && A > 1) {
+            const int st = a * NB;
+#pragma unroll
+            for (int d = 1; d < R; ++d) v[d] = cmul(v[d], stw(tw, st * d, sgn));
+        }
+#pragma unroll
+        for (int d = 0; d < R; ++d) dst.store(lane, base + A * d, v[d]);
+    }
+}
+
+// run pass number `p` (runtime, warp-uniform) of plan PL: expands to a switch over the NP passes
+template <class PL, bool DIT, bool FUSE2, int P = 0>
+struct SPassSel {
+    template <class Src, class Dst, class Mid>
+    QEB_HD static void run(int p, int warp, int nwarps, int lane, int nl, const cplx* tw, double sgn, Src& src, Dst& dst,
+                           Mid& mid)
+    {
+        if (p == P)
+            spass<PL, P, DIT, FUSE2>(warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
+        else if constexpr (P + 1 < PL::NP)
+            SPassSel<PL, DIT, FUSE2, P + 1>::run(p, warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
+    }
+};
+
+// the static plans that are instantiated (BASELINE grids 25, 27, 64, 125, 135, 144, 200 + common small sizes);
+// DIF order, identical to fft_plan.h::preferred_factors (large in-register radices: at most one
+// shared-memory exchange per transform)
+using SP15 = SPlan<15, 15>;
+using SP25 = SPlan<25, 25>;
+using SP27 = SPlan<27, 27>;
+using SP64 = SPlan<64, 8, 8>;
+using SP125 = SPlan<125, 25, 5>;
+using SP135 = SPlan<135, 15, 9>;
+using SP144 = SPlan<144, 12, 12>;
+using SP200 = SPlan<200, 25, 8>;
+
+}  // namespace qeb

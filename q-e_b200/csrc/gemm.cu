@@ -25,6 +25,12 @@ __device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b)
                  : "d"(a), "d"(b));
 }
 
+// sign flip on the integer pipe: an FP64 negation would be a DADD that competes with DMMA for the FP64 datapath
+__device__ __forceinline__ double flip_sign(double x, unsigned mask)
+{
+    return __hiloint2double(__double2hiint(x) ^ (int)mask, __double2loint(x));
+}
+
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, bool valid)
 {
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
@@ -116,12 +122,14 @@ k_calbec(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi, i
 #pragma unroll
             for (int mi = 0; mi < 4; ++mi) a[mi] = Aw[(size_t)mi * 8 * CB_LDK + kk];
             if (CPLX) {
+                // Re: B = psi_real[k]; Im: B = (J psi)[k] = (Im, -Re)[k&1], read from the neighbouring double
                 const double* Bw = Bs + (size_t)(wn * 32 + r) * CB_LDK + (k & 2);
+                const int sel = k & 1;
+                const unsigned smask = sel ? 0x80000000u : 0u;
 #pragma unroll
                 for (int nj = 0; nj < 4; ++nj) {
-                    const double2 bb = *reinterpret_cast<const double2*>(Bw + (size_t)nj * 8 * CB_LDK + kk);
-                    const double bre = (k & 1) ? bb.y : bb.x;
-                    const double bim = (k & 1) ? -bb.x : bb.y;
+                    const double bre = Bw[(size_t)nj * 8 * CB_LDK + kk + sel];
+                    const double bim = flip_sign(Bw[(size_t)nj * 8 * CB_LDK + kk + (sel ^ 1)], smask);
 #pragma unroll
                     for (int mi = 0; mi < 4; ++mi) {
                         dmma(acc[mi][nj][0], acc[mi][nj][1], a[mi], bre);
@@ -323,11 +331,12 @@ k_addvus(const cplx* __restrict__ vkb, int npwx, const void* __restrict__ ps_, i
             for (int mi = 0; mi < 4; ++mi) a[mi] = Aw[(size_t)mi * 8 * C::LDK + kk];
             if (CPLX) {
                 // K index (i, c'): i = kk/2 + (k>>1), c' = k&1 ; N index (g, c): g = .. + (r>>1), c = r&1
-                const cplx* Vw = Vs + (size_t)(kk / 2 + (k >> 1)) * AV_LDV + wn * 32 + (r >> 1);
+                // [vr -vi; vi vr]: element (c = r&1, c' = k&1) is the double at offset c^c', negated for (c=0,c'=1)
+                const double* Vw = reinterpret_cast<const double*>(Vs + (size_t)(kk / 2 + (k >> 1)) * AV_LDV + wn * 32 + (r >> 1)) + ((r ^ k) & 1);
+                const unsigned smask = (!(r & 1) && (k & 1)) ? 0x80000000u : 0u;
 #pragma unroll
                 for (int nj = 0; nj < 8; ++nj) {
-                    const double2 v = *reinterpret_cast<const double2*>(Vw + nj * 4);
-                    const double b = (r & 1) ? ((k & 1) ? v.x : v.y) : ((k & 1) ? -v.y : v.x);
+                    const double b = flip_sign(Vw[nj * 8], smask);
 #pragma unroll
                     for (int mi = 0; mi < 4; ++mi) dmma(acc[mi][nj][0], acc[mi][nj][1], a[mi], b);
                 }

@@ -2,10 +2,10 @@
 // phases of vloc_kernels.cuh. See that file for the algorithm and the
 // reference lines it replaces.
 #include "vloc.h"
+#include "vloc_fast_inst.cuh"
 
 namespace qeb {
 
-#define QEB_SMEM extern __shared__ __align__(16) unsigned char smem_raw[]; cplx* smem = reinterpret_cast<cplx*>(smem_raw)
 
 __global__ void __launch_bounds__(256) k_vloc_zinv(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
 {
@@ -57,6 +57,51 @@ __global__ void __launch_bounds__(256) k_vloc_xfus(const __grid_constant__ VlocT
     }
 }
 
+
+
+// ---- fast variants (vloc_fast_inst.cuh, instantiated in vloc_fast_<N>.cu) ----
+#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200)
+#define X(PL) extern template struct FastLaunch<PL>;
+QEB_FOR_PLANS(X)
+#undef X
+
+static bool launch_z(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
+{
+    if (t.TZ > QEB_TL || env_int("QEB_GENERIC", 0)) return false;
+#define X(PL)                                        \
+    if (PL::matches(t.pz)) {                         \
+        FastLaunch<PL>::z(inv, t, io, cfg, nboxes, st); \
+        return true;                                 \
+    }
+    QEB_FOR_PLANS(X)
+#undef X
+    return false;
+}
+static bool launch_y(bool inv, const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
+{
+    if (t.TY > QEB_TL || env_int("QEB_GENERIC", 0)) return false;
+#define X(PL)                                    \
+    if (PL::matches(t.py)) {                     \
+        FastLaunch<PL>::y(inv, t, cfg, nboxes, st); \
+        return true;                             \
+    }
+    QEB_FOR_PLANS(X)
+#undef X
+    return false;
+}
+static bool launch_x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
+{
+    if (t.TX > QEB_TL || env_int("QEB_GENERIC", 0)) return false;
+#define X(PL)                               \
+    if (PL::matches(t.px)) {                \
+        FastLaunch<PL>::x(t, cfg, nboxes, st); \
+        return true;                        \
+    }
+    QEB_FOR_PLANS(X)
+#undef X
+    return false;
+}
+
 __global__ void k_prepare_v(const double* __restrict__ v, double* __restrict__ vp, const int* __restrict__ rev_x,
                             int nr1, int nr2, int nr3, double scale)
 {
@@ -86,18 +131,26 @@ cudaError_t vloc_init_attrs(size_t max_smem)
     if ((e = cudaFuncSetAttribute(k_vloc_yinv, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
     if ((e = cudaFuncSetAttribute(k_vloc_yfwd, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
     if ((e = cudaFuncSetAttribute(k_vloc_xfus, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
-    return cudaSuccess;
+#define X(PL) FastLaunch<PL>::attrs(s);
+    QEB_FOR_PLANS(X)
+#undef X
+    return cudaGetLastError();
 }
 
 cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
                               cudaStream_t st)
 {
     if (nboxes <= 0) return cudaSuccess;
-    k_vloc_zinv<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
-    k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
-    k_vloc_xfus<<<dim3(t.ntx, nboxes), cfg.threads_x, cfg.smem_x, st>>>(t);
-    k_vloc_yfwd<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
-    k_vloc_zfwd<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
+    if (!launch_z(true, t, io, cfg, nboxes, st))
+        k_vloc_zinv<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
+    if (!launch_y(true, t, cfg, nboxes, st))
+        k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
+    if (!launch_x(t, cfg, nboxes, st))
+        k_vloc_xfus<<<dim3(t.ntx, nboxes), cfg.threads_x, cfg.smem_x, st>>>(t);
+    if (!launch_y(false, t, cfg, nboxes, st))
+        k_vloc_yfwd<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
+    if (!launch_z(false, t, io, cfg, nboxes, st))
+        k_vloc_zfwd<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
     return cudaGetLastError();
 }
 

@@ -1,0 +1,181 @@
+// Fast (compile-time plan, warp-mapped) variants of the five V_loc passes of
+// vloc_kernels.cuh. Same data flow, tables, intermediates and phase lists; the
+// FFT length/radix list of the pass direction is a template parameter (SPlan)
+// and tiles have at most 32 lines (one per lane). Selected by vloc.cu when the
+// grid dimension has an instantiated static plan, otherwise the generic
+// kernels run. `tw` is the twiddle table of the pass direction (the kernels
+// stage it in shared memory). Executed on the CPU by tests/emul like the
+// generic phases.
+#pragma once
+#include "fft_static.cuh"
+#include "vloc_kernels.cuh"
+
+namespace qeb {
+
+// small per-CTA tables the fast kernels stage in shared memory (in the CPU emulation they point at the
+// global tables): twiddles of the pass direction, the x/y pruning map, the digit-reversal table, the
+// stick list of the z group
+struct FastTabs {
+    const cplx* tw;
+    const int* map;     // x pass: xmap[nr1]; y passes: ymap row of the plane [nr2]
+    const int* rev;     // y passes: rev_y[nr2]; z passes: rev_z[nr3]
+    const int* sticks;  // z passes: stick ids of the group [TZ]
+};
+
+struct LaneTile {  // S[pos*ld + lane]
+    cplx* s;
+    int ld;
+    QEB_HD cplx load(int lane, int pos) const { return s[pos * ld + lane]; }
+    QEB_HD void store(int lane, int pos, cplx v) const { s[pos * ld + lane] = v; }
+};
+
+// ---------------------------------------------------------------------------
+// P1 fast: scatter + z inverse
+// ---------------------------------------------------------------------------
+template <class PL>
+QEB_HD void zinv_fast_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem,
+                                const FastTabs& ft)
+{
+    if (ph < 2) {  // zero + scatter: identical to the generic kernel
+        zinv_scatter_phase(ph, tid, nthr, t, io, grp, box, smem);
+        return;
+    }
+    const int p = ph - 2;
+    const int warp = tid / QEB_TL, lane = tid % QEB_TL, nwarps = nthr / QEB_TL;
+    const int nl = t.grp_nl[grp];
+    LaneTile s{smem, t.TZ};
+    NoMid nm;
+    if (p == PL::NP - 1) {
+        G1Dst d{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.nst};
+        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, d, nm);
+    } else {
+        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, s, nm);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// P5 fast: z forward + gather
+// ---------------------------------------------------------------------------
+template <class PL>
+QEB_HD void zfwd_fast_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem,
+                                const FastTabs& ft)
+{
+    constexpr int np = PL::NP;
+    if (ph >= np) {  // gather: identical to the generic kernel
+        zfwd_gather_phase(tid, nthr, t, io, grp, box, smem);
+        return;
+    }
+    const int p = np - 1 - ph;
+    const int warp = tid / QEB_TL, lane = tid % QEB_TL, nwarps = nthr / QEB_TL;
+    const int nl = t.grp_nl[grp];
+    LaneTile s{smem, t.TZ};
+    NoMid nm;
+    if (ph == 0) {
+        G1Dst g{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.nst};
+        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, g, s, nm);
+    } else {
+        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, s, s, nm);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// P2 / P4 fast: y passes
+// ---------------------------------------------------------------------------
+template <class PL>
+QEB_HD void yinv_fast_phase(int ph, int tid, int nthr, const VlocTables& t, int ztile, int xa, int box, cplx* smem,
+                                const FastTabs& ft)
+{
+    if (ph == 0) {
+        yinv_load_phase(tid, nthr, t, ztile, xa, box, smem);  // G1 slab -> compact rows
+        return;
+    }
+    constexpr int np = PL::NP;
+    const int TY = t.TY, ldc = TY + 1;
+    const int z0 = ztile * TY;
+    const int nl = (t.nr3 - z0) < TY ? (t.nr3 - z0) : TY;
+    cplx* C = smem;
+    cplx* W = smem + (size_t)t.nsmax * ldc;
+    const int p = ph - 1;
+    const int warp = tid / QEB_TL, lane = tid % QEB_TL, nwarps = nthr / QEB_TL;
+    LaneTile w{W, TY};
+    NoMid nm;
+    cplx* g2 = t.g2 + (size_t)box * t.g2_box + (size_t)xa * t.npos;
+    G2YDst gd{g2, ft.rev, t.nr3, z0};
+    YSrcCompact cs{C, ft.map, ldc};
+    if (np == 1)
+        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, cs, gd, nm);
+    else if (p == 0)
+        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, cs, w, nm);
+    else if (p == np - 1)
+        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, w, gd, nm);
+    else
+        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, w, w, nm);
+}
+
+template <class PL>
+QEB_HD void yfwd_fast_phase(int ph, int tid, int nthr, const VlocTables& t, int ztile, int xa, int box, cplx* smem,
+                                const FastTabs& ft)
+{
+    constexpr int np = PL::NP;
+    if (ph >= np) {
+        yfwd_store_phase(tid, nthr, t, ztile, xa, box, smem);  // compact rows -> G1 slab
+        return;
+    }
+    const int TY = t.TY, ldc = TY + 1;
+    const int z0 = ztile * TY;
+    const int nl = (t.nr3 - z0) < TY ? (t.nr3 - z0) : TY;
+    cplx* C = smem;
+    cplx* W = smem + (size_t)t.nsmax * ldc;
+    const int p = np - 1 - ph;
+    const int warp = tid / QEB_TL, lane = tid % QEB_TL, nwarps = nthr / QEB_TL;
+    LaneTile w{W, TY};
+    NoMid nm;
+    cplx* g2 = t.g2 + (size_t)box * t.g2_box + (size_t)xa * t.npos;
+    G2YDst gs{g2, ft.rev, t.nr3, z0};
+    YDstCompact cd{C, ft.map, ldc};
+    if (np == 1)
+        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, gs, cd, nm);
+    else if (ph == 0)
+        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, gs, w, nm);
+    else if (p == 0)
+        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, w, cd, nm);
+    else
+        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, w, w, nm);
+}
+
+// ---------------------------------------------------------------------------
+// P3 fast: fused x inverse * V * x forward
+// ---------------------------------------------------------------------------
+template <class PL>
+QEB_HD void xfus_fast_phase(int ph, int tid, int nthr, const VlocTables& t, int tile, int box, cplx* smem,
+                                const FastTabs& ft)
+{
+    constexpr int np = PL::NP;
+    const int TX = t.TX;
+    const int p0 = tile * TX;
+    const int nl = (t.npos - p0) < TX ? (t.npos - p0) : TX;
+    const int warp = tid / QEB_TL, lane = tid % QEB_TL, nwarps = nthr / QEB_TL;
+    LaneTile w{smem, TX};
+    G2XSrc g{t.g2 + (size_t)box * t.g2_box, ft.map, t.npos, p0};
+    VMid vm{t.vp, t.npos, p0};
+    NoMid nm;
+    if (ph < np - 1) {
+        if (ph == 0)
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, g, w, nm);
+        else
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, w, w, nm);
+    } else if (ph == np - 1) {
+        if (np == 1)
+            SPassSel<PL, false, true>::run(np - 1, warp, nwarps, lane, nl, ft.tw, +1.0, g, g, vm);
+        else
+            SPassSel<PL, false, true>::run(np - 1, warp, nwarps, lane, nl, ft.tw, +1.0, w, w, vm);
+    } else {
+        const int p = 2 * np - 2 - ph;
+        if (p == 0)
+            SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, w, g, nm);
+        else
+            SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, w, w, nm);
+    }
+}
+
+}  // namespace qeb

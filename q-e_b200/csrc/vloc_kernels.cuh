@@ -79,10 +79,10 @@ struct G1Dst {  // last z-DIF pass: position -> z = rev[pos], line -> stick
 
 QEB_HD int zinv_nphase(const VlocTables& t) { return 2 + t.pz.npass; }
 
-QEB_HD void zinv_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem)
+// phases 0 (zero the tile) and 1 (scatter psi into the sticks), shared with the fast kernels
+QEB_HD void zinv_scatter_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem)
 {
     const int TZ = t.TZ;
-    const int nl = t.grp_nl[grp];
     if (ph == 0) {
         const int tot = t.nr3 * TZ;
         for (int i = tid; i < tot; i += nthr) smem[i] = mk(0.0, 0.0);
@@ -117,6 +117,16 @@ QEB_HD void zinv_phase(int ph, int tid, int nthr, const VlocTables& t, const Vlo
         }
         return;
     }
+}
+
+QEB_HD void zinv_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem)
+{
+    const int TZ = t.TZ;
+    const int nl = t.grp_nl[grp];
+    if (ph < 2) {
+        zinv_scatter_phase(ph, tid, nthr, t, io, grp, box, smem);
+        return;
+    }
     const int p = ph - 2;
     const FastDiv dnl = t.grp_div[grp];
     const PassDesc pd = pass_of(t.pz, p);
@@ -134,6 +144,7 @@ QEB_HD void zinv_phase(int ph, int tid, int nthr, const VlocTables& t, const Vlo
 // P5: z forward + gather.  block = (group, box).  smem: nr3*TZ
 // ---------------------------------------------------------------------------
 QEB_HD int zfwd_nphase(const VlocTables& t) { return 1 + t.pz.npass; }
+QEB_HD void zfwd_gather_phase(int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem);
 
 QEB_HD void zfwd_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem)
 {
@@ -154,7 +165,12 @@ QEB_HD void zfwd_phase(int ph, int tid, int nthr, const VlocTables& t, const Vlo
         }
         return;
     }
-    // gather (the 1/N scaling is folded into vp)
+    zfwd_gather_phase(tid, nthr, t, io, grp, box, smem);
+}
+
+// gather (the 1/N scaling is folded into vp) + kinetic term; shared with the fast kernels
+QEB_HD void zfwd_gather_phase(int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem)
+{
     const int c0 = t.grp_coef_off[grp], c1 = t.grp_coef_off[grp + 1];
     if (!io.gamma) {
         const size_t off = (size_t)(io.band0 + box) * io.lda;
@@ -240,6 +256,36 @@ struct YDstCompact {  // last y-DIT pass: natural y -> stick row (others dropped
 
 QEB_HD int ypass_nphase(const VlocTables& t) { return 1 + t.py.npass; }
 
+// G1[box][z0+zl][s0+s] -> C[s][zl], lanes along s (shared with the fast kernels)
+QEB_HD void yinv_load_phase(int tid, int nthr, const VlocTables& t, int ztile, int xa, int box, cplx* smem)
+{
+    const int TY = t.TY, ldc = TY + 1;
+    const int z0 = ztile * TY;
+    const int nl = (t.nr3 - z0) < TY ? (t.nr3 - z0) : TY;
+    const int ns = t.plane_ns[xa], s0 = t.plane_s0[xa];
+    cplx* C = smem;
+    const cplx* g1 = t.g1 + (size_t)box * t.g1_box;
+    const int lanes = nthr < 32 ? nthr : 32;
+    const int nw = nthr / lanes, wid = tid / lanes, ln = tid % lanes;
+    for (int zl = wid; zl < nl; zl += nw)
+        for (int s = ln; s < ns; s += lanes) C[s * ldc + zl] = g1[(size_t)(z0 + zl) * t.nst + s0 + s];
+}
+
+// C[s][zl] -> G1[box][z0+zl][s0+s] (shared with the fast kernels)
+QEB_HD void yfwd_store_phase(int tid, int nthr, const VlocTables& t, int ztile, int xa, int box, cplx* smem)
+{
+    const int TY = t.TY, ldc = TY + 1;
+    const int z0 = ztile * TY;
+    const int nl = (t.nr3 - z0) < TY ? (t.nr3 - z0) : TY;
+    const int ns = t.plane_ns[xa], s0 = t.plane_s0[xa];
+    const cplx* C = smem;
+    cplx* g1 = t.g1 + (size_t)box * t.g1_box;
+    const int lanes = nthr < 32 ? nthr : 32;
+    const int nw = nthr / lanes, wid = tid / lanes, ln = tid % lanes;
+    for (int zl = wid; zl < nl; zl += nw)
+        for (int s = ln; s < ns; s += lanes) g1[(size_t)(z0 + zl) * t.nst + s0 + s] = C[s * ldc + zl];
+}
+
 QEB_HD void yinv_phase(int ph, int tid, int nthr, const VlocTables& t, int ztile, int xa, int box, cplx* smem)
 {
     const int TY = t.TY, ldc = TY + 1;
@@ -250,12 +296,7 @@ QEB_HD void yinv_phase(int ph, int tid, int nthr, const VlocTables& t, int ztile
     cplx* W = smem + (size_t)t.nsmax * ldc;
     const int np = t.py.npass;
     if (ph == 0) {
-        // G1[box][z0+zl][s0+s] -> C[s][zl], lanes along s
-        const cplx* g1 = t.g1 + (size_t)box * t.g1_box;
-        const int lanes = nthr < 32 ? nthr : 32;
-        const int nw = nthr / lanes, wid = tid / lanes, ln = tid % lanes;
-        for (int zl = wid; zl < nl; zl += nw)
-            for (int s = ln; s < ns; s += lanes) C[s * ldc + zl] = g1[(size_t)(z0 + zl) * t.nst + s0 + s];
+        yinv_load_phase(tid, nthr, t, ztile, xa, box, smem);
         return;
     }
     const int p = ph - 1;
@@ -309,12 +350,7 @@ QEB_HD void yfwd_phase(int ph, int tid, int nthr, const VlocTables& t, int ztile
         }
         return;
     }
-    // C[s][zl] -> G1[box][z0+zl][s0+s]
-    cplx* g1 = t.g1 + (size_t)box * t.g1_box;
-    const int lanes = nthr < 32 ? nthr : 32;
-    const int nw = nthr / lanes, wid = tid / lanes, ln = tid % lanes;
-    for (int zl = wid; zl < nl; zl += nw)
-        for (int s = ln; s < ns; s += lanes) g1[(size_t)(z0 + zl) * t.nst + s0 + s] = C[s * ldc + zl];
+    yfwd_store_phase(tid, nthr, t, ztile, xa, box, smem);
 }
 
 // ---------------------------------------------------------------------------
@@ -338,13 +374,17 @@ struct G2XSrc {  // natural x -> active plane (pruned); lines = (y,z) positions
 struct VMid {
     const double* vp;
     int npos, p0;
-    QEB_HD cplx apply(int line, int xpos, cplx v) const
+    QEB_HD double fetch(int line, int xpos) const
     {
 #if defined(__CUDA_ARCH__)
-        const double s = __ldg(vp + (size_t)xpos * npos + p0 + line);
+        return __ldg(vp + (size_t)xpos * npos + p0 + line);
 #else
-        const double s = vp[(size_t)xpos * npos + p0 + line];
+        return vp[(size_t)xpos * npos + p0 + line];
 #endif
+    }
+    QEB_HD cplx apply(int line, int xpos, cplx v) const
+    {
+        const double s = fetch(line, xpos);
         return mk(v.x * s, v.y * s);
     }
 };

@@ -110,9 +110,13 @@ inline std::string build_vloc_tables(int nr1, int nr2, int nr3, int npw, const i
         T.TZ = std::max(1, std::min(tz, std::max(T.nst, T.gamma ? 2 : 1)));
         if (T.gamma && T.TZ < 2) T.TZ = 2;
         T.smem_z = (size_t)nr3 * T.TZ * 16;
-        int ty_hi = 40;
+        // y tiles: at most 32 z-lines (one per lane in the fast kernels), evenly sized
+        int ty_hi = 32;
         while (ty_hi > 8 && ((size_t)nr2 * ty_hi + (size_t)T.nsmax * (ty_hi + 1)) * 16 > smem_cap) ty_hi -= 2;
-        T.TY = pick_tile(nr3, std::max(4, ty_hi / 2), ty_hi);
+        {
+            const int nt = (nr3 + ty_hi - 1) / ty_hi;
+            T.TY = (nr3 + nt - 1) / nt;
+        }
         T.nty = (nr3 + T.TY - 1) / T.TY;
         T.smem_y = ((size_t)nr2 * T.TY + (size_t)T.nsmax * (T.TY + 1)) * 16;
         int tx_hi = 32;

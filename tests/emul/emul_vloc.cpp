@@ -7,6 +7,7 @@
 #include <vector>
 #include "vloc_setup.h"
 #include "fullfft_kernels.cuh"
+#include "vloc_fast.cuh"
 
 using namespace qeb;
 
@@ -45,6 +46,39 @@ extern "C" int emul_fft1d(int n, int sign, int nlines, const double* in, double*
             for (int i = 0; i < n; ++i) co[(size_t)l * n + i] = s[(size_t)i * nlines + l];
     }
     return 0;
+}
+
+#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200)
+typedef void (*zfn)(int, int, int, const VlocTables&, const VlocIO&, int, int, cplx*, const FastTabs&);
+typedef void (*yfn)(int, int, int, const VlocTables&, int, int, int, cplx*, const FastTabs&);
+typedef void (*xfn)(int, int, int, const VlocTables&, int, int, cplx*, const FastTabs&);
+static int g_fast = 0;  // set by emul_set_fast: run the compile-time-plan phase functions when a plan matches
+extern "C" void emul_set_fast(int f) { g_fast = f; }
+static void zinv_g(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int g, int b, cplx* s, const FastTabs&) { zinv_phase(ph, tid, nthr, t, io, g, b, s); }
+static void zfwd_g(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int g, int b, cplx* s, const FastTabs&) { zfwd_phase(ph, tid, nthr, t, io, g, b, s); }
+static void yinv_g(int ph, int tid, int nthr, const VlocTables& t, int z, int x, int b, cplx* s, const FastTabs&) { yinv_phase(ph, tid, nthr, t, z, x, b, s); }
+static void yfwd_g(int ph, int tid, int nthr, const VlocTables& t, int z, int x, int b, cplx* s, const FastTabs&) { yfwd_phase(ph, tid, nthr, t, z, x, b, s); }
+static void xfus_g(int ph, int tid, int nthr, const VlocTables& t, int tile, int b, cplx* s, const FastTabs&) { xfus_phase(ph, tid, nthr, t, tile, b, s); }
+static zfn pick_z(const FftPlan& pl, bool inv)
+{
+#define X(PL) if (g_fast && PL::matches(pl)) return inv ? (zfn)zinv_fast_phase<PL> : (zfn)zfwd_fast_phase<PL>;
+    QEB_FOR_PLANS(X)
+#undef X
+    return inv ? zinv_g : zfwd_g;
+}
+static yfn pick_y(const FftPlan& pl, bool inv)
+{
+#define X(PL) if (g_fast && PL::matches(pl)) return inv ? (yfn)yinv_fast_phase<PL> : (yfn)yfwd_fast_phase<PL>;
+    QEB_FOR_PLANS(X)
+#undef X
+    return inv ? yinv_g : yfwd_g;
+}
+static xfn pick_x(const FftPlan& pl)
+{
+#define X(PL) if (g_fast && PL::matches(pl)) return (xfn)xfus_fast_phase<PL>;
+    QEB_FOR_PLANS(X)
+#undef X
+    return xfus_g;
 }
 
 extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, const int* nlm, const int* igk, int ngm,
@@ -102,29 +136,29 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
                 for (int ph = 0; ph < zinv_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) zinv_phase(ph, tid, nthr, t, io, g, box, smem.data());
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
             }
             for (int xa = 0; xa < H.nxw; ++xa)
                 for (int zt = 0; zt < H.nty; ++zt) {
                     for (auto& x : smem) x = nanv;
                     for (int ph = 0; ph < ypass_nphase(t); ++ph)
-                        for (int tid = 0; tid < nthr; ++tid) yinv_phase(ph, tid, nthr, t, zt, xa, box, smem.data());
+                        for (int tid = 0; tid < nthr; ++tid) pick_y(t.py, true)(ph, tid, nthr, t, zt, xa, box, smem.data(), FastTabs{t.py.tw, t.ymap + (size_t)xa * t.nr2, t.py.rev, nullptr});
                 }
             for (int tile = 0; tile < H.ntx; ++tile) {
                 for (auto& x : smem) x = nanv;
                 for (int ph = 0; ph < xfus_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) xfus_phase(ph, tid, nthr, t, tile, box, smem.data());
+                    for (int tid = 0; tid < nthr; ++tid) pick_x(t.px)(ph, tid, nthr, t, tile, box, smem.data(), FastTabs{t.px.tw, t.xmap, nullptr, nullptr});
             }
             for (int xa = 0; xa < H.nxw; ++xa)
                 for (int zt = 0; zt < H.nty; ++zt) {
                     for (auto& x : smem) x = nanv;
                     for (int ph = 0; ph < ypass_nphase(t); ++ph)
-                        for (int tid = 0; tid < nthr; ++tid) yfwd_phase(ph, tid, nthr, t, zt, xa, box, smem.data());
+                        for (int tid = 0; tid < nthr; ++tid) pick_y(t.py, false)(ph, tid, nthr, t, zt, xa, box, smem.data(), FastTabs{t.py.tw, t.ymap + (size_t)xa * t.nr2, t.py.rev, nullptr});
                 }
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
                 for (int ph = 0; ph < zfwd_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) zfwd_phase(ph, tid, nthr, t, io, g, box, smem.data());
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, false)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
             }
         }
     }

@@ -24,6 +24,7 @@ def emul():
     L.emul_fft1d.argtypes = [I, I, I, P, P, I, I]
     L.emul_vloc.argtypes = [I, I, I, I, P, P, P, I, I, I, P, P, P, P, I, I]
     L.emul_fullfft.argtypes = [I, I, I, I, I, P, I]
+    L.emul_set_fast.argtypes = [I]
     return L
 
 
@@ -65,7 +66,10 @@ def test_radix_passes_small_radices_only(emul, maxr):
 
 @pytest.mark.parametrize("name", ["si2_small", "ortho_small", "si2_small_gamma", "ortho_small_gamma", "si2", "al4"])
 @pytest.mark.parametrize("m,batch", [(1, 1), (3, 2), (4, 3)])
-def test_vloc_phases_match_oracle(emul, name, m, batch):
+@pytest.mark.parametrize("fast", [0, 1])
+def test_vloc_phases_match_oracle(emul, name, m, batch, fast):
+    """fast=1: the compile-time-plan, warp-mapped phase functions (vloc_fast.cuh) where a static plan exists"""
+    emul.emul_set_fast(fast)
     d = D.config_descriptor(name)
     inp = R.synthetic_inputs(d, m, [4, 4], seed=m)
     lda, n = inp["lda"], inp["n"]
@@ -82,7 +86,7 @@ def test_vloc_phases_match_oracle(emul, name, m, batch):
         out = h0.copy()
         g2 = np.ascontiguousarray(d.g2kin) if kin else None
         rc = emul.emul_vloc(d.nr1, d.nr2, d.nr3, n, p(nl_), p(nlm), p(igk), d.ngm, lda, m, p(inp["psi"]),
-                            p(inp["vrs"]), p(g2), p(out), 37, batch)
+                            p(inp["vrs"]), p(g2), p(out), 96 if fast else 37, batch)
         assert rc == 0
         assert np.abs(out[:, :n] - ref[:, :n]).max() / np.abs(ref[:, :n]).max() < 1e-13
 
@@ -98,3 +102,23 @@ def test_fullbox_fft_phases(emul, shape):
     assert np.abs(g - ref).max() / np.abs(ref).max() < 1e-13
     assert emul.emul_fullfft(nr1, nr2, nr3, 2, -1, p(g), 19) == 0
     assert np.abs(g - f).max() / np.abs(f).max() < 1e-13
+
+
+@pytest.mark.parametrize("name,m", [("ausurf112", 1), ("h2o64", 2), ("si512", 1)])
+def test_vloc_fast_phases_full_baseline_grids(emul, name, m):
+    """BASELINE grids (125x64x200 k, 135^3 and 144^3 Gamma) through the compile-time-plan phase functions."""
+    emul.emul_set_fast(1)
+    d = D.config_descriptor(name)
+    inp = R.synthetic_inputs(d, m, [4, 4], seed=1)
+    lda, n = inp["lda"], inp["n"]
+    ref = np.zeros((m, lda), complex)
+    (R.vloc_psi_gamma if d.gamma_only else R.vloc_psi_k)(d, lda, n, m, inp["psi"], inp["vrs"], ref)
+    out = np.zeros((m, lda), complex)
+    nl_ = np.ascontiguousarray(d.nl, dtype=np.int32)
+    nlm = np.ascontiguousarray(d.nlm, dtype=np.int32) if d.gamma_only else None
+    igk = None if d.gamma_only else np.ascontiguousarray(d.igk, dtype=np.int32)
+    rc = emul.emul_vloc(d.nr1, d.nr2, d.nr3, n, p(nl_), p(nlm), p(igk), d.ngm, lda, m, p(inp["psi"]), p(inp["vrs"]),
+                        None, p(out), 160, 2)
+    assert rc == 0
+    assert np.abs(out[:, :n] - ref[:, :n]).max() / np.abs(ref[:, :n]).max() < 1e-13
+    emul.emul_set_fast(0)
