@@ -1,0 +1,322 @@
+!
+! qeb200_shim.f90 - ISO_C_BINDING shim between PWscf and libqeb200 (include/qeb200.h).
+!
+! Drop-in use: compile this file into PW/src (see INTEGRATION.md) and pass
+! h_psi_qeb to the solvers where c_bands.f90 passes h_psi / h_psi_gpu
+! (PW/src/c_bands.f90:253-254,557,573,850,866), or rename it to h_psi to
+! replace the symbol for every caller. The argument list is the reference's
+! (PW/src/h_psi.f90:9): all arguments by reference, psi/hpsi contiguous
+! COMPLEX(DP)(lda*npol, m).
+!
+! Not compiled in this repository's CI: neither the build image nor the GPU
+! box has a Fortran compiler. The same call sequence is exercised through the
+! Python mirror q-e_b200/hpsi.py by tests/test_gpu_parity.py.
+!
+MODULE qeb200_c
+  USE, INTRINSIC :: ISO_C_BINDING
+  IMPLICIT NONE
+  INTEGER(C_INT), PARAMETER :: QEB_FFT_RHO = 0, QEB_FFT_WAVE = 1
+  INTERFACE
+    INTEGER(C_INT) FUNCTION qeb_create(ctx, device, stream) BIND(C, name='qeb_create')
+      IMPORT; TYPE(C_PTR) :: ctx; INTEGER(C_INT), VALUE :: device; TYPE(C_PTR), VALUE :: stream
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_destroy(ctx) BIND(C, name='qeb_destroy')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    TYPE(C_PTR) FUNCTION qeb_last_error(ctx) BIND(C, name='qeb_last_error')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_grid(ctx, nr1, nr2, nr3, nr1x, nr2x, nr3x, ngm, nl, nlm, gamma_only) &
+        BIND(C, name='qeb_set_grid')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, nl, nlm
+      INTEGER(C_INT), VALUE :: nr1, nr2, nr3, nr1x, nr2x, nr3x, ngm, gamma_only
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_kpoint(ctx, npw, npwx, igk, g2kin, vkb, nkb, gstart) BIND(C, name='qeb_set_kpoint')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, igk, g2kin, vkb
+      INTEGER(C_INT), VALUE :: npw, npwx, nkb, gstart
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_vloc(ctx, vrs) BIND(C, name='qeb_set_vloc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, vrs
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_nonlocal(ctx, nat, nhm, nh_of_atom, ofsbeta, deeq) BIND(C, name='qeb_set_nonlocal')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, nh_of_atom, ofsbeta, deeq
+      INTEGER(C_INT), VALUE :: nat, nhm
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_h_psi(ctx, lda, n, m, psi, hpsi) BIND(C, name='qeb_h_psi')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_h_psi_bgrp(ctx, lda, n, m, psi, hpsi, nbgrp, my_bgrp) BIND(C, name='qeb_h_psi_bgrp')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, hpsi; INTEGER(C_INT), VALUE :: lda, n, m, nbgrp, my_bgrp
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_vloc_psi_k(ctx, lda, n, m, psi, v, hpsi) BIND(C, name='qeb_vloc_psi_k')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, v, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_vloc_psi_gamma(ctx, lda, n, m, psi, v, hpsi) BIND(C, name='qeb_vloc_psi_gamma')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, v, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_fft(ctx, sign, kind, f, howmany) BIND(C, name='qeb_fft')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, f; INTEGER(C_INT), VALUE :: sign, kind, howmany
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_calbec(ctx, n, beta, nkb, psi, lda, m, becp) BIND(C, name='qeb_calbec')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, beta, psi, becp; INTEGER(C_INT), VALUE :: n, nkb, lda, m
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_add_vuspsi(ctx, lda, n, m, hpsi, becp) BIND(C, name='qeb_add_vuspsi')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, hpsi, becp; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_get_becp(ctx, becp, m) BIND(C, name='qeb_get_becp')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, becp; INTEGER(C_INT), VALUE :: m
+    END FUNCTION
+  END INTERFACE
+END MODULE qeb200_c
+
+!----------------------------------------------------------------------------
+MODULE qeb200_state
+  !! One context per MPI rank (= per device, Modules/mp_world.f90:94) and the
+  !! "dirty" flags that replace the reference's implicit module state.
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE qeb200_c
+  IMPLICIT NONE
+  SAVE
+  TYPE(C_PTR) :: ctx = C_NULL_PTR
+  LOGICAL :: grid_set = .FALSE.
+  INTEGER :: k_set = -1          ! current_k the context holds
+  INTEGER :: vloc_version = -1   ! bumped by qeb200_touch_vloc (call it after set_vrs, electrons.f90:1038)
+  INTEGER :: vloc_loaded = -2
+  INTEGER :: deeq_version = -1   ! bumped by qeb200_touch_deeq (call it after newd, electrons.f90:1045)
+  INTEGER :: deeq_loaded = -2
+  INTEGER :: spin_loaded = -1
+CONTAINS
+  SUBROUTINE qeb200_check(rc, routine)
+    INTEGER(C_INT), INTENT(IN) :: rc
+    CHARACTER(*), INTENT(IN) :: routine
+    CHARACTER(KIND=C_CHAR), POINTER :: s(:)
+    CHARACTER(LEN=256) :: msg
+    INTEGER :: i
+    IF (rc == 0) RETURN
+    msg = ' '
+    CALL C_F_POINTER(qeb_last_error(ctx), s, [256])
+    DO i = 1, 256
+      IF (s(i) == C_NULL_CHAR) EXIT
+      msg(i:i) = s(i)
+    END DO
+    CALL errore(routine, TRIM(msg), INT(rc))   ! UtilXlib/error_handler.f90:10 -> mp_abort
+  END SUBROUTINE
+  SUBROUTINE qeb200_touch_vloc();  vloc_version = vloc_version + 1; END SUBROUTINE
+  SUBROUTINE qeb200_touch_deeq();  deeq_version = deeq_version + 1; END SUBROUTINE
+  SUBROUTINE qeb200_touch_kpoint(); k_set = -1; END SUBROUTINE   ! after init_us_2 when atoms move
+
+  SUBROUTINE qeb200_sync_state()
+    !! Pushes whatever module state changed since the last call into the context.
+    USE fft_base,      ONLY: dffts
+    USE gvect,         ONLY: gstart
+    USE gvecs,         ONLY: ngms
+    USE klist,         ONLY: ngk, igk_k
+    USE wvfct,         ONLY: npwx, g2kin, current_k
+    USE scf,           ONLY: vrs
+    USE lsda_mod,      ONLY: current_spin
+    USE uspp,          ONLY: vkb, nkb, deeq, ofsbeta
+    USE uspp_param,    ONLY: nh, nhm
+    USE ions_base,     ONLY: nat, ityp
+    USE control_flags, ONLY: gamma_only
+    USE mp_world,      ONLY: mpime
+    INTEGER(C_INT), ALLOCATABLE, TARGET :: nh_at(:), ofs0(:)
+    INTEGER :: na, ig
+    TYPE(C_PTR) :: pnlm, pigk
+    IF (.NOT. C_ASSOCIATED(ctx)) CALL qeb200_check(qeb_create(ctx, INT(mpime, C_INT), C_NULL_PTR), 'qeb_create')
+    IF (.NOT. grid_set) THEN
+      pnlm = C_NULL_PTR
+      IF (gamma_only) pnlm = C_LOC(dffts%nlm)
+      ig = 0; IF (gamma_only) ig = 1
+      CALL qeb200_check(qeb_set_grid(ctx, dffts%nr1, dffts%nr2, dffts%nr3, dffts%nr1x, dffts%nr2x, dffts%nr3x, &
+                        ngms, C_LOC(dffts%nl), pnlm, INT(ig, C_INT)), 'qeb_set_grid')
+      grid_set = .TRUE.
+    END IF
+    IF (k_set /= current_k) THEN
+      pigk = C_NULL_PTR
+      IF (.NOT. gamma_only) pigk = C_LOC(igk_k(1, current_k))
+      CALL qeb200_check(qeb_set_kpoint(ctx, ngk(current_k), npwx, pigk, C_LOC(g2kin), C_LOC(vkb), nkb, gstart), &
+                        'qeb_set_kpoint')
+      k_set = current_k
+    END IF
+    IF (vloc_loaded /= vloc_version .OR. spin_loaded /= current_spin) THEN
+      CALL qeb200_check(qeb_set_vloc(ctx, C_LOC(vrs(1, current_spin))), 'qeb_set_vloc')
+      vloc_loaded = vloc_version
+    END IF
+    IF (nkb > 0 .AND. (deeq_loaded /= deeq_version .OR. spin_loaded /= current_spin)) THEN
+      ALLOCATE(nh_at(nat), ofs0(nat))
+      DO na = 1, nat
+        nh_at(na) = nh(ityp(na)); ofs0(na) = ofsbeta(na)     ! ofsbeta is already a 0-based offset (upflib/uspp.f90)
+      END DO
+      CALL qeb200_check(qeb_set_nonlocal(ctx, nat, nhm, C_LOC(nh_at), C_LOC(ofs0), C_LOC(deeq(1, 1, 1, current_spin))), &
+                        'qeb_set_nonlocal')
+      deeq_loaded = deeq_version
+      DEALLOCATE(nh_at, ofs0)
+    END IF
+    spin_loaded = current_spin
+  END SUBROUTINE
+END MODULE qeb200_state
+
+!----------------------------------------------------------------------------
+SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
+  !! Same interface as h_psi (PW/src/h_psi.f90:9). Branches the library does not
+  !! implement are routed to the original routine (SURVEY 8a a18).
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds,            ONLY: DP
+  USE qeb200_c
+  USE qeb200_state
+  USE becmod,           ONLY: becp
+  USE uspp,             ONLY: nkb
+  USE control_flags,    ONLY: gamma_only
+  USE noncollin_module, ONLY: npol, noncolin
+  USE realus,           ONLY: real_space
+  USE fft_base,         ONLY: dffts
+  USE ldaU,             ONLY: lda_plus_u
+  USE bp,               ONLY: lelfield
+  USE xc_lib,           ONLY: exx_is_active, xclib_dft_is
+  USE mp_bands,         ONLY: use_bgrp_in_hpsi, inter_bgrp_comm, nbgrp, my_bgrp_id
+  USE mp,               ONLY: mp_allgather, mp_size, mp_type_create_column_section, mp_type_free
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n, m
+  COMPLEX(DP), INTENT(IN), TARGET :: psi(lda*npol, m)
+  COMPLEX(DP), INTENT(OUT), TARGET :: hpsi(lda*npol, m)
+  INTEGER :: m_start, m_end, column_type
+  INTEGER, ALLOCATABLE :: recv_counts(:), displs(:)
+  !
+  IF (noncolin .OR. real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. &
+      exx_is_active() .OR. xclib_dft_is('meta') .OR. dffts%lpara) THEN
+    CALL h_psi(lda, n, m, psi, hpsi)      ! original Fortran path
+    RETURN
+  END IF
+  CALL start_clock('h_psi')
+  CALL qeb200_sync_state()
+  IF (use_bgrp_in_hpsi .AND. nbgrp > 1 .AND. m > 1) THEN
+    ! band groups, h_psi.f90:53-67: own columns on this rank's GPU, then the reference's own all-gather
+    ALLOCATE(recv_counts(mp_size(inter_bgrp_comm)), displs(mp_size(inter_bgrp_comm)))
+    CALL divide_all(inter_bgrp_comm, m, m_start, m_end, recv_counts, displs)
+    CALL qeb200_check(qeb_h_psi_bgrp(ctx, lda, n, m, C_LOC(psi), C_LOC(hpsi), nbgrp, my_bgrp_id), 'h_psi')
+    CALL mp_type_create_column_section(hpsi(1, 1), 0, lda*npol, lda*npol, column_type)
+    CALL mp_allgather(hpsi, column_type, recv_counts, displs, inter_bgrp_comm)
+    CALL mp_type_free(column_type)
+    DEALLOCATE(recv_counts, displs)
+  ELSE
+    CALL qeb200_check(qeb_h_psi(ctx, lda, n, m, C_LOC(psi), C_LOC(hpsi)), 'h_psi')
+  END IF
+  ! side effect callers rely on (s_psi.f90:15,132,157): becmod::becp = <beta|psi> of these m columns
+  IF (nkb > 0) THEN
+    IF (gamma_only) THEN
+      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%r), m), 'h_psi')
+    ELSE
+      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%k), m), 'h_psi')
+    END IF
+  END IF
+  CALL stop_clock('h_psi')
+END SUBROUTINE h_psi_qeb
+
+!----------------------------------------------------------------------------
+SUBROUTINE vloc_psi_k_qeb(lda, n, m, psi, v, hpsi)
+  !! vloc_psi_k (PW/src/vloc_psi_acc.f90:148): hpsi (INOUT) += V_loc psi
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds, ONLY: DP
+  USE qeb200_c; USE qeb200_state
+  USE fft_base, ONLY: dffts
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n, m
+  COMPLEX(DP), INTENT(IN), TARGET :: psi(lda, m)
+  COMPLEX(DP), INTENT(INOUT), TARGET :: hpsi(lda, m)
+  REAL(DP), INTENT(IN), TARGET :: v(dffts%nnr)
+  CALL qeb200_sync_state()
+  CALL qeb200_check(qeb_vloc_psi_k(ctx, lda, n, m, C_LOC(psi), C_LOC(v), C_LOC(hpsi)), 'vloc_psi_k')
+  vloc_loaded = -2   ! the context now holds v, not vrs(:,current_spin)
+END SUBROUTINE
+
+SUBROUTINE vloc_psi_gamma_qeb(lda, n, m, psi, v, hpsi)
+  !! vloc_psi_gamma (PW/src/vloc_psi_acc.f90:9)
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds, ONLY: DP
+  USE qeb200_c; USE qeb200_state
+  USE fft_base, ONLY: dffts
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n, m
+  COMPLEX(DP), INTENT(IN), TARGET :: psi(lda, m)
+  COMPLEX(DP), INTENT(INOUT), TARGET :: hpsi(lda, m)
+  REAL(DP), INTENT(IN), TARGET :: v(dffts%nnr)
+  CALL qeb200_sync_state()
+  CALL qeb200_check(qeb_vloc_psi_gamma(ctx, lda, n, m, C_LOC(psi), C_LOC(v), C_LOC(hpsi)), 'vloc_psi_gamma')
+  vloc_loaded = -2
+END SUBROUTINE
+
+!----------------------------------------------------------------------------
+MODULE qeb200_becmod
+  !! Specific procedures to add to the generic calbec of Modules/becmod.f90:40-53
+  !! (k and Gamma array forms; the bec_type form dispatches on gamma_only like
+  !! calbec_bec_type, becmod.f90:138-172) and the add_vuspsi replacement.
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds, ONLY: DP
+  USE qeb200_c; USE qeb200_state
+  IMPLICIT NONE
+CONTAINS
+  SUBROUTINE calbec_k_qeb(npw, beta, psi, betapsi, nbnd)
+    INTEGER, INTENT(IN) :: npw
+    COMPLEX(DP), INTENT(IN), TARGET :: beta(:,:), psi(:,:)
+    COMPLEX(DP), INTENT(OUT), TARGET :: betapsi(:,:)
+    INTEGER, OPTIONAL, INTENT(IN) :: nbnd
+    INTEGER :: m
+    m = SIZE(psi, 2); IF (PRESENT(nbnd)) m = nbnd
+    CALL qeb200_sync_state()
+    CALL qeb200_check(qeb_calbec(ctx, npw, C_LOC(beta), SIZE(beta, 2), C_LOC(psi), SIZE(psi, 1), m, C_LOC(betapsi)), 'calbec')
+  END SUBROUTINE
+  SUBROUTINE calbec_gamma_qeb(npw, beta, psi, betapsi, nbnd)
+    INTEGER, INTENT(IN) :: npw
+    COMPLEX(DP), INTENT(IN), TARGET :: beta(:,:), psi(:,:)
+    REAL(DP), INTENT(OUT), TARGET :: betapsi(:,:)
+    INTEGER, OPTIONAL, INTENT(IN) :: nbnd
+    INTEGER :: m
+    m = SIZE(psi, 2); IF (PRESENT(nbnd)) m = nbnd
+    CALL qeb200_sync_state()
+    CALL qeb200_check(qeb_calbec(ctx, npw, C_LOC(beta), SIZE(beta, 2), C_LOC(psi), SIZE(psi, 1), m, C_LOC(betapsi)), 'calbec')
+  END SUBROUTINE
+  SUBROUTINE add_vuspsi_qeb(lda, n, m, hpsi)
+    !! add_vuspsi (PW/src/add_vuspsi.f90:10): hpsi += vkb * (D becp), becp = becmod::becp
+    USE becmod, ONLY: becp
+    USE control_flags, ONLY: gamma_only
+    INTEGER, INTENT(IN) :: lda, n, m
+    COMPLEX(DP), INTENT(INOUT), TARGET :: hpsi(lda, m)
+    CALL qeb200_sync_state()
+    IF (gamma_only) THEN
+      CALL qeb200_check(qeb_add_vuspsi(ctx, lda, n, m, C_LOC(hpsi), C_LOC(becp%r)), 'add_vuspsi')
+    ELSE
+      CALL qeb200_check(qeb_add_vuspsi(ctx, lda, n, m, C_LOC(hpsi), C_LOC(becp%k)), 'add_vuspsi')
+    END IF
+  END SUBROUTINE
+END MODULE qeb200_becmod
+
+!----------------------------------------------------------------------------
+SUBROUTINE invfft_qeb(fft_kind, f, howmany)
+  !! invfft(fft_kind, f, dffts, howmany) (FFTXlib/src/fft_interfaces.f90:19-47) for the serial smooth grid
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds, ONLY: DP
+  USE qeb200_c; USE qeb200_state
+  IMPLICIT NONE
+  CHARACTER(LEN=*), INTENT(IN) :: fft_kind
+  COMPLEX(DP), INTENT(INOUT), TARGET :: f(*)
+  INTEGER, INTENT(IN) :: howmany
+  INTEGER(C_INT) :: kind
+  kind = QEB_FFT_RHO; IF (fft_kind == 'Wave') kind = QEB_FFT_WAVE
+  CALL qeb200_sync_state()
+  CALL qeb200_check(qeb_fft(ctx, 1_C_INT, kind, C_LOC(f), howmany), 'invfft')
+END SUBROUTINE
+
+SUBROUTINE fwfft_qeb(fft_kind, f, howmany)
+  !! fwfft(fft_kind, f, dffts, howmany) (FFTXlib/src/fft_interfaces.f90:49-80)
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds, ONLY: DP
+  USE qeb200_c; USE qeb200_state
+  IMPLICIT NONE
+  CHARACTER(LEN=*), INTENT(IN) :: fft_kind
+  COMPLEX(DP), INTENT(INOUT), TARGET :: f(*)
+  INTEGER, INTENT(IN) :: howmany
+  INTEGER(C_INT) :: kind
+  kind = QEB_FFT_RHO; IF (fft_kind == 'Wave') kind = QEB_FFT_WAVE
+  CALL qeb200_sync_state()
+  CALL qeb200_check(qeb_fft(ctx, -1_C_INT, kind, C_LOC(f), howmany), 'fwfft')
+END SUBROUTINE
