@@ -305,12 +305,29 @@ def run_ours(args):
     nbatches = -(-boxes // st["batch"])
     vloc_bytes = st["vloc_bytes_per_band"] * mm
     achieved = vloc_bytes / (ms_vloc * 1e-3) / 1e9
-    # per launch of the dominant V_loc kernel family: 5 pass kernels per batch
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "V_loc pass pipeline (5 kernels/batch: zinv,yinv,xfus,yfwd,zfwd)",
-                "algorithmic_bytes_per_band": st["vloc_bytes_per_band"], "ms_vloc_section": ms_vloc,
-                "peak_source": peak_src}
+    # V_loc pipeline (5 pass kernels per batch of boxes) against the HBM roofline
+    roofline_vloc = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "V_loc pass pipeline (5 kernels/batch: zinv,yinv,xfus,yfwd,zfwd)",
+                     "algorithmic_bytes_per_band": st["vloc_bytes_per_band"], "ms_vloc_section": ms_vloc,
+                     "peak_source": peak_src}
     gemm_tf = st["gemm_flops_per_band"] * mm / (ms_nl * 1e-3) / 1e12 if ms_nl > 0 else None
+    # FP64 tensor (DMMA) ceiling: 148 SMs x 64 FMA/clk x SM clock; cuBLAS DGEMM timed beside it as the empirical ceiling
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    fp64_peak = torch.cuda.get_device_properties(dev).multi_processor_count * 64 * 2 * sm_mhz * 1e6 / 1e12
+    a64 = torch.randn((4096, 4096), device=dev, dtype=torch.float64)
+    ms_dgemm = time_section(lambda: torch.matmul(a64, a64), reps=5)
+    dgemm_tf = 2 * 4096 ** 3 / (ms_dgemm * 1e-3) / 1e12
+    del a64
+    roofline_gemm = None
+    if ms_nl > 0:
+        roofline_gemm = {"bound": "tensor", "achieved": gemm_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": gemm_tf / fp64_peak, "traffic": None,
+                         "kernel": "projector GEMMs k_calbec + k_addvus (FP64 DMMA.8x8x4)",
+                         "algorithmic_flops_per_band": st["gemm_flops_per_band"], "ms_projector_section": ms_nl,
+                         "peak_source": "148 SMs x 64 FP64 FMA/clk x %.0f MHz (FP64 tensor = FP64 vector rate on B200); "
+                                        "cuBLAS DGEMM 4096^3 in this run: %.1f TFLOP/s" % (sm_mhz, dgemm_tf)}
+    # `roofline` = the kernel family with the largest share of the step
+    roofline = roofline_gemm if (roofline_gemm and ms_nl >= ms_vloc) else roofline_vloc
     launches_step = nbatches * 5 + (4 if nkb else 0) + 1
 
     # ---- end to end through the public API with HOST (pinned) buffers ----
@@ -347,7 +364,9 @@ def run_ours(args):
                        "nkb": nkb, "gamma_only": bool(d.gamma_only), "parallelism": ("k-pools" if pools else "band-groups") + f" x{world}",
                        "vloc_batch_boxes": st["batch"], "l2": "inputs larger than L2 (psi+hpsi+vkb = %.1f GB)" % ((2 * m_total * lda * 16 + nkb * lda * 16) / 1e9)},
             "roofline": roofline,
-            "projectors": {"ms": ms_nl, "tflops_fp64": gemm_tf},
+            "roofline_vloc": roofline_vloc,
+            "roofline_projectors": roofline_gemm,
+            "sections_ms": {"vloc": ms_vloc, "projectors": ms_nl},
             "gpu_launches": launches_step * args.steps,
             "clocks": clocks,
         }

@@ -47,6 +47,12 @@ int qeb_set_batch(qeb_ctx* ctx, int nboxes);
  * stream (for callers that own the stream, e.g. the benchmark). */
 int qeb_set_async(qeb_ctx* ctx, int async);
 
+/* Host-buffer pipeline of qeb_h_psi: when psi and hpsi are HOST arrays with at least min_cols columns, the call is
+ * split into chunks of chunk_cols columns (0 = automatic, about m/8 rounded to 64) whose H2D copy, kernels and D2H
+ * copy overlap on three streams; the caller's arrays are page-locked once (cudaHostRegister) unless the
+ * environment variable QEB_NO_HOSTREG is set. Columns are independent (h_psi.f90:53-67), results are unchanged. */
+int qeb_set_pipeline(qeb_ctx* ctx, int chunk_cols, int min_cols);
+
 /* ---- state setters ----------------------------------------------------- */
 /* FFT grid + G-vector maps of dffts (serial descriptor):
  *   fft_type_descriptor nr1,nr2,nr3,nr1x,nr2x,nr3x,nnr   FFTXlib/src/fft_types.f90:35-185

@@ -46,6 +46,32 @@ def _compile(nvcc, src, obj):
     return obj
 
 
+def build_variant(tag: str, defines: list[str], verbose: bool = True) -> str:
+    """Tuning aid: builds q-e_b200/libqeb200_<tag>.so with extra -D defines (select it with QEB_LIB=<path>)."""
+    nvcc = _nvcc()
+    bdir = os.path.join(BUILD, "variant_" + tag)
+    os.makedirs(bdir, exist_ok=True)
+    srcs = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+    flags = [*NVCC_FLAGS, *[f"-D{d}" for d in defines]]
+
+    def one(src):
+        obj = os.path.join(bdir, src.replace(".cu", ".o"))
+        r = subprocess.run([nvcc, *flags, "-I", CSRC, "-c", os.path.join(CSRC, src), "-o", obj], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+        return obj
+
+    with cf.ThreadPoolExecutor(max_workers=8) as ex:
+        objs = list(ex.map(one, srcs))
+    out = os.path.join(HERE, f"libqeb200_{tag}.so")
+    r = subprocess.run([nvcc, "-shared", "-o", out, *objs, "-gencode", "arch=compute_100a,code=sm_100a"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    if verbose:
+        print("built", out)
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     srcs = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
@@ -73,4 +99,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    build(force="--force" in sys.argv, verbose=True)
+    if "--variant" in sys.argv:
+        i = sys.argv.index("--variant")
+        build_variant(sys.argv[i + 1], sys.argv[i + 2:])
+    else:
+        build(force="--force" in sys.argv, verbose=True)

@@ -4,6 +4,7 @@
 // the reference's order (PW/src/h_psi.f90:138-147 kinetic, :180/:220 V_loc,
 // :229-236 nonlocal, :294-295 Gamma fix).
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -80,6 +81,11 @@ struct qeb_ctx {
     VlocLaunchCfg cfg;
     int batch_user = 0, batch = 1;
     DevBuf g1_d, g2_d;
+    // batches are dealt round-robin to vloc_nstreams streams (each with its own G1/G2 slice), so that the
+    // latency-bound z passes of one batch overlap the FP64-heavy x pass of another
+    int vloc_nstreams = 2;
+    cudaStream_t vstream[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t vev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // potential
     bool have_v = false;
     DevBuf v_d, vp_d;
@@ -97,6 +103,14 @@ struct qeb_ctx {
     int becp_m = 0;
     // staging
     DevBuf psi_stage, hpsi_stage, beta_stage, misc_stage;
+    // host-buffer pipeline (qeb_h_psi with host psi/hpsi): copy-in / copy-out streams, per-chunk events and the
+    // caller's arrays page-locked once (the Davidson work arrays are re-used call after call)
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    std::vector<cudaEvent_t> ev;
+    struct HostReg { const char* p; size_t bytes; };
+    std::vector<HostReg> hostreg;
+    int pipeline_chunk = 0;  // 0 = automatic
+    int pipeline_min_cols = 128;
     // nccl
     void* nccl = nullptr;
     int nranks = 1, rank = 0;
@@ -167,6 +181,18 @@ int qeb_create(qeb_ctx** out, int device, void* stream)
         return 6;
     }
     if (const char* e = getenv("QEB_BATCH")) c->batch_user = atoi(e);
+    if (const char* e = getenv("QEB_VLOC_STREAMS")) c->vloc_nstreams = std::max(1, std::min(4, atoi(e)));
+    for (int i = 1; i < c->vloc_nstreams; ++i)
+        if (cudaStreamCreateWithFlags(&c->vstream[i], cudaStreamNonBlocking) != cudaSuccess) {
+            delete c;
+            return 7;
+        }
+    for (int i = 0; i < 5; ++i)
+        if (cudaEventCreateWithFlags(&c->vev[i], cudaEventDisableTiming) != cudaSuccess) {
+            delete c;
+            return 7;
+        }
+    if (const char* e = getenv("QEB_PIPELINE_CHUNK")) c->pipeline_chunk = atoi(e);
     *out = c;
     return 0;
 }
@@ -180,6 +206,14 @@ int qeb_destroy(qeb_ctx* c)
                       &c->revx_d, &c->full_plan_d, &c->nlint_d, &c->deeq_d, &c->becp_d, &c->ps_d, &c->part_d,
                       &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage};
     for (DevBuf* b : bufs) b->release();
+    for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
+    for (int i = 0; i < 5; ++i)
+        if (c->vev[i]) cudaEventDestroy(c->vev[i]);
+    for (int i = 1; i < 4; ++i)
+        if (c->vstream[i]) cudaStreamDestroy(c->vstream[i]);
+    for (auto& r : c->hostreg) cudaHostUnregister((void*)r.p);
+    if (c->s_in) cudaStreamDestroy(c->s_in);
+    if (c->s_out) cudaStreamDestroy(c->s_out);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
     return 0;
@@ -192,6 +226,14 @@ int qeb_set_batch(qeb_ctx* c, int nboxes)
     if (!c || nboxes < 0) return 1;
     c->batch_user = nboxes;
     c->have_k = false;  // workspaces are re-sized by the next qeb_set_kpoint
+    return 0;
+}
+
+int qeb_set_pipeline(qeb_ctx* c, int chunk_cols, int min_cols)
+{
+    if (!c || chunk_cols < 0 || min_cols < 1) return 1;
+    c->pipeline_chunk = chunk_cols;
+    c->pipeline_min_cols = min_cols;
     return 0;
 }
 
@@ -319,14 +361,15 @@ static int upload_tables(qeb_ctx* c)
     t.g2_box = (size_t)H.nxw * t.npos;
     int nb = c->batch_user;
     if (nb <= 0) {
-        const size_t target = (size_t)56 << 20;  // keep the batch's G2 planes L2-resident
+        // keep the G2 planes of the batches in flight L2-resident
+        const size_t target = ((size_t)56 << 20) / c->vloc_nstreams;
         nb = (int)(target / (t.g2_box * 16 + 1));
         if (nb < 1) nb = 1;
         if (nb > 64) nb = 64;
     }
     c->batch = nb;
-    QEB_CUDA(c, c->g1_d.ensure(t.g1_box * 16 * nb));
-    QEB_CUDA(c, c->g2_d.ensure(t.g2_box * 16 * nb));
+    QEB_CUDA(c, c->g1_d.ensure(t.g1_box * 16 * nb * c->vloc_nstreams));
+    QEB_CUDA(c, c->g2_d.ensure(t.g2_box * 16 * nb * c->vloc_nstreams));
     t.g1 = (cplx*)c->g1_d.p;
     t.g2 = (cplx*)c->g2_d.p;
     t.vp = (const double*)c->vp_d.p;
@@ -456,10 +499,25 @@ static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hp
     io.nbands = m;
     io.gamma = c->gamma ? 1 : 0;
     const int nboxes = c->gamma ? (m + 1) / 2 : m;
-    for (int b0 = 0; b0 < nboxes; b0 += c->batch) {
+    const int nbatches = (nboxes + c->batch - 1) / c->batch;
+    const int ns = std::min(c->vloc_nstreams, nbatches);
+    if (ns > 1) {  // fork: the side streams start after everything queued so far on the main stream
+        QEB_CUDA(c, cudaEventRecord(c->vev[0], c->stream));
+        for (int s = 1; s < ns; ++s) QEB_CUDA(c, cudaStreamWaitEvent(c->vstream[s], c->vev[0], 0));
+    }
+    int ib = 0;
+    for (int b0 = 0; b0 < nboxes; b0 += c->batch, ++ib) {
         const int nb = std::min(c->batch, nboxes - b0);
+        const int s = ib % ns;
         io.band0 = c->gamma ? 2 * b0 : b0;
-        QEB_CUDA(c, vloc_launch_batch(c->T, io, c->cfg, nb, c->stream));
+        VlocTables T = c->T;
+        T.g1 += (size_t)s * c->batch * T.g1_box;
+        T.g2 += (size_t)s * c->batch * T.g2_box;
+        QEB_CUDA(c, vloc_launch_batch(T, io, c->cfg, nb, s == 0 ? c->stream : c->vstream[s]));
+    }
+    for (int s = 1; s < ns; ++s) {  // join
+        QEB_CUDA(c, cudaEventRecord(c->vev[s], c->vstream[s]));
+        QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->vev[s], 0));
     }
     return 0;
 }
@@ -487,15 +545,18 @@ static int run_calbec(qeb_ctx* c, const cplx* beta, int npwx, int nkb, const cpl
     return 0;
 }
 
-static int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi)
+static int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi, int col0 = 0)
 {
     if (!c->have_nl) QEB_FAIL(c, 51, "add_vuspsi: qeb_set_nonlocal has not been called");
     const int nkb = c->nkb;
     if (nkb > c->nl_rows) QEB_FAIL(c, 52, "add_vuspsi: vkb has projectors not covered by ofsbeta/nh of qeb_set_nonlocal");
     const int ldps = (nkb + 1) & ~1;
-    QEB_CUDA(c, launch_apply_deeq(c->becp_d.p, nkb, m, !c->gamma, c->row_atom_d, c->ofs_d, c->nh_d,
-                                  (const double*)c->deeq_d.p, c->nhm, c->ps_d.p, ldps, c->stream));
-    QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, c->ps_d.p, ldps, n, nkb, m, !c->gamma, hpsi, lda, c->stream));
+    const size_t el = c->gamma ? 8 : 16;
+    const char* becp = (const char*)c->becp_d.p + (size_t)col0 * nkb * el;
+    char* ps = (char*)c->ps_d.p + (size_t)col0 * ldps * el;
+    QEB_CUDA(c, launch_apply_deeq(becp, nkb, m, !c->gamma, c->row_atom_d, c->ofs_d, c->nh_d,
+                                  (const double*)c->deeq_d.p, c->nhm, ps, ldps, c->stream));
+    QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, ps, ldps, n, nkb, m, !c->gamma, hpsi, lda, c->stream));
     return 0;
 }
 
@@ -507,20 +568,105 @@ static int check_call(qeb_ctx* c, int lda, int n, int m, const void* psi, const 
     return 0;
 }
 
+// columns [col0, col0+m) of a call over m_total columns; psi_d / hpsi_d point at column col0. The projections of
+// the whole call live in becp_d (column j at j*nkb): the caller runs ensure_becp(m_total) once when col0 >= 0 is
+// used with m_total > m.
 static int h_psi_cols(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool do_vloc, bool do_nl,
-                      bool kinetic)
+                      bool kinetic, int col0 = 0, int m_total = -1)
 {
     int rc;
     if (kinetic && lda > n)
         QEB_CUDA(c, cudaMemset2DAsync(hpsi_d + n, (size_t)lda * 16, 0, (size_t)(lda - n) * 16, m, c->stream));
     if (do_vloc && (rc = run_vloc(c, lda, n, m, psi_d, hpsi_d, kinetic))) return rc;
     if (do_nl && c->nkb > 0) {
-        if ((rc = ensure_becp(c, c->nkb, m))) return rc;
-        if ((rc = run_calbec(c, c->vkb_d, c->npwx, c->nkb, psi_d, lda, n, m, c->becp_d.p))) return rc;
-        c->becp_m = m;
-        if ((rc = run_addvus(c, lda, n, m, hpsi_d))) return rc;
+        if (m_total < 0 && (rc = ensure_becp(c, c->nkb, m))) return rc;
+        char* becp = (char*)c->becp_d.p + (size_t)col0 * c->nkb * (c->gamma ? 8 : 16);
+        if ((rc = run_calbec(c, c->vkb_d, c->npwx, c->nkb, psi_d, lda, n, m, becp))) return rc;
+        c->becp_m = m_total < 0 ? m : (col0 + m);
+        if ((rc = run_addvus(c, lda, n, m, hpsi_d, col0))) return rc;
     }
     if (kinetic && c->gamma && c->gstart == 2) QEB_CUDA(c, launch_zero_im_g0(hpsi_d, lda, m, c->stream));
+    return 0;
+}
+
+// Page-locks the caller's host array once so that its chunks can be copied asynchronously (pageable memory would
+// serialise the copies with the kernels). Ranges are remembered; already pinned memory is left alone.
+static void pin_host_range(qeb_ctx* c, const void* p, size_t bytes)
+{
+    if (bytes < ((size_t)1 << 20) || getenv("QEB_NO_HOSTREG")) return;  // small copies do not need the overlap
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost) return;  // pinned already
+    cudaGetLastError();
+    const char* b = (const char*)p;
+    for (auto& r : c->hostreg)
+        if (b >= r.p && b + bytes <= r.p + r.bytes) return;
+    // drop registrations this range overlaps (the caller re-allocated)
+    for (size_t i = 0; i < c->hostreg.size();) {
+        auto& r = c->hostreg[i];
+        if (b < r.p + r.bytes && r.p < b + bytes) {
+            cudaHostUnregister((void*)r.p);
+            c->hostreg.erase(c->hostreg.begin() + i);
+        } else {
+            ++i;
+        }
+    }
+    if (c->hostreg.size() >= 8) {
+        cudaHostUnregister((void*)c->hostreg.front().p);
+        c->hostreg.erase(c->hostreg.begin());
+    }
+    if (cudaHostRegister((void*)p, bytes, cudaHostRegisterDefault) == cudaSuccess)
+        c->hostreg.push_back({b, bytes});
+    else
+        cudaGetLastError();  // not fatal: the copies just do not overlap
+}
+
+// h_psi with HOST psi and hpsi: column chunks flow through three streams, so the H2D copy of chunk i+1 and the D2H
+// copy of chunk i-1 overlap the kernels of chunk i. Every column is independent in h_psi (h_psi.f90:53-67 splits
+// columns the same way over band groups), so the result is the one of the single call.
+static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
+{
+    int rc;
+    const size_t col = (size_t)lda * 16;
+    int mc = c->pipeline_chunk;
+    if (mc <= 0) {
+        mc = ((m + 7) / 8 + 63) / 64 * 64;  // ~8 chunks, whole GEMM band tiles
+        if (mc < 64) mc = 64;
+    }
+    if (mc > m) mc = m;
+    if (mc & 1) ++mc;  // Gamma: band pairs stay together
+    const int nch = (m + mc - 1) / mc;
+    if (!c->s_in) QEB_CUDA(c, cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+    if (!c->s_out) QEB_CUDA(c, cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+    while ((int)c->ev.size() < 2 * nch) {
+        cudaEvent_t e;
+        QEB_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c->ev.push_back(e);
+    }
+    QEB_CUDA(c, c->psi_stage.ensure(col * m));
+    QEB_CUDA(c, c->hpsi_stage.ensure(col * m));
+    pin_host_range(c, psi, col * m);
+    pin_host_range(c, hpsi, col * m);
+    if (c->nkb > 0 && (rc = ensure_becp(c, c->nkb, m))) return rc;
+    // the staging buffers may still be read by work queued earlier on the compute stream (async callers)
+    QEB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+    QEB_CUDA(c, cudaStreamWaitEvent(c->s_in, c->ev[0], 0));
+    const char* ph = (const char*)psi;
+    char* hh = (char*)hpsi;
+    char* pd = (char*)c->psi_stage.p;
+    char* hd = (char*)c->hpsi_stage.p;
+    for (int i = 0; i < nch; ++i) {
+        const int c0 = i * mc, mm = std::min(mc, m - c0);
+        QEB_CUDA(c, cudaMemcpyAsync(pd + col * c0, ph + col * c0, col * mm, cudaMemcpyHostToDevice, c->s_in));
+        QEB_CUDA(c, cudaEventRecord(c->ev[2 * i], c->s_in));
+        QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev[2 * i], 0));
+        if ((rc = h_psi_cols(c, lda, n, mm, (const cplx*)(pd + col * c0), (cplx*)(hd + col * c0), true, true, true, c0, m)))
+            return rc;
+        QEB_CUDA(c, cudaEventRecord(c->ev[2 * i + 1], c->stream));
+        QEB_CUDA(c, cudaStreamWaitEvent(c->s_out, c->ev[2 * i + 1], 0));
+        QEB_CUDA(c, cudaMemcpyAsync(hh + col * c0, hd + col * c0, col * mm, cudaMemcpyDeviceToHost, c->s_out));
+    }
+    QEB_CUDA(c, cudaStreamSynchronize(c->s_out));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
     return 0;
 }
 
@@ -532,9 +678,11 @@ int qeb_h_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
     if (rc) return rc;
     if (m == 0) return 0;
     const size_t bytes = (size_t)lda * m * 16;
+    const bool out_dev = is_device_ptr(hpsi);
+    if (!out_dev && !is_device_ptr(psi) && m >= c->pipeline_min_cols && (bytes >= ((size_t)8 << 20) || c->pipeline_chunk > 0))
+        return h_psi_host_pipeline(c, lda, n, m, psi, hpsi);
     const void* psi_d;
     if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
-    const bool out_dev = is_device_ptr(hpsi);
     cplx* hpsi_d = (cplx*)hpsi;
     if (!out_dev) {
         QEB_CUDA(c, c->hpsi_stage.ensure(bytes));

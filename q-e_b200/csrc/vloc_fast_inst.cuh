@@ -8,11 +8,14 @@
 
 namespace qeb {
 
+#ifndef QEB_FAST_MAXTHREADS
+#define QEB_FAST_MAXTHREADS 512
+#endif
 #define QEB_SMEM extern __shared__ __align__(16) unsigned char smem_raw[]; cplx* smem = reinterpret_cast<cplx*>(smem_raw)
 
 // ---- fast variants: compile-time plan of the pass direction, warp-mapped work ----
 template <class PL>
-__global__ void __launch_bounds__(512) k_vloc_zinv_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_zinv_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
 {
     QEB_SMEM;
     cplx* twS = smem + ((size_t)t.nr3 * t.TZ);
@@ -28,7 +31,7 @@ __global__ void __launch_bounds__(512) k_vloc_zinv_f(const __grid_constant__ Vlo
     }
 }
 template <class PL>
-__global__ void __launch_bounds__(512) k_vloc_zfwd_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_zfwd_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
 {
     QEB_SMEM;
     cplx* twS = smem + ((size_t)t.nr3 * t.TZ);
@@ -44,7 +47,7 @@ __global__ void __launch_bounds__(512) k_vloc_zfwd_f(const __grid_constant__ Vlo
     }
 }
 template <class PL>
-__global__ void __launch_bounds__(512) k_vloc_yinv_f(const __grid_constant__ VlocTables t)
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_yinv_f(const __grid_constant__ VlocTables t)
 {
     QEB_SMEM;
     cplx* twS = smem + ((size_t)t.nsmax * (t.TY + 1) + (size_t)t.nr2 * t.TY);
@@ -62,7 +65,7 @@ __global__ void __launch_bounds__(512) k_vloc_yinv_f(const __grid_constant__ Vlo
     }
 }
 template <class PL>
-__global__ void __launch_bounds__(512) k_vloc_yfwd_f(const __grid_constant__ VlocTables t)
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_yfwd_f(const __grid_constant__ VlocTables t)
 {
     QEB_SMEM;
     cplx* twS = smem + ((size_t)t.nsmax * (t.TY + 1) + (size_t)t.nr2 * t.TY);
@@ -80,7 +83,7 @@ __global__ void __launch_bounds__(512) k_vloc_yfwd_f(const __grid_constant__ Vlo
     }
 }
 template <class PL>
-__global__ void __launch_bounds__(512) k_vloc_xfus_f(const __grid_constant__ VlocTables t)
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xfus_f(const __grid_constant__ VlocTables t)
 {
     QEB_SMEM;
     cplx* twS = smem + ((size_t)t.nr1 * t.TX);

@@ -24,7 +24,8 @@ class QebError(RuntimeError):
 
 
 def lib_path() -> str:
-    return os.path.join(_HERE, "libqeb200.so")
+    # QEB_LIB selects another build of the same library (kernel-tuning variants, q-e_b200/build.py --variant)
+    return os.environ.get("QEB_LIB") or os.path.join(_HERE, "libqeb200.so")
 
 
 def load_library():
@@ -44,6 +45,7 @@ def load_library():
     L.qeb_version.restype = ctypes.c_char_p
     L.qeb_set_batch.argtypes = [P, I]
     L.qeb_set_async.argtypes = [P, I]
+    L.qeb_set_pipeline.argtypes = [P, I, I]
     L.qeb_set_grid.argtypes = [P, I, I, I, I, I, I, I, P, P, I]
     L.qeb_set_kpoint.argtypes = [P, I, I, P, P, P, I, I]
     L.qeb_set_vloc.argtypes = [P, P]
@@ -61,7 +63,7 @@ def load_library():
     L.qeb_get_stats.argtypes = [P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
                                 ctypes.POINTER(I), ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_nonlocal_only.argtypes = [P, I, I, I, P, P]
-    for name in ("qeb_create", "qeb_destroy", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
+    for name in ("qeb_create", "qeb_destroy", "qeb_set_pipeline", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
                  "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
                  "qeb_get_stats", "qeb_nonlocal_only"):
@@ -134,6 +136,9 @@ class HPsi:
     # -- state setters ------------------------------------------------------
     def set_batch(self, nboxes: int):
         self._ck(self._L.qeb_set_batch(self._h, nboxes), "qeb_set_batch")
+
+    def set_pipeline(self, chunk_cols: int = 0, min_cols: int = 128):
+        self._ck(self._L.qeb_set_pipeline(self._h, chunk_cols, min_cols), "qeb_set_pipeline")
 
     def set_async(self, flag: bool):
         self._ck(self._L.qeb_set_async(self._h, int(flag)), "qeb_set_async")

@@ -257,3 +257,25 @@ def test_hermiticity_full_size_ausurf(mods):
     lin = (torch.view_as_complex(cout)[0] - (Hm[0] + 2.0 * Hm[1])).abs().max().item() / Hm.abs().max().item()
     assert lin < 1e-12
     h.close()
+
+
+@pytest.mark.parametrize("name", ["ortho_small", "ortho_small_gamma"])
+@pytest.mark.parametrize("m,chunk", [(11, 4), (12, 6), (7, 2)])
+def test_h_psi_host_pipeline(mods, name, m, chunk):
+    """Host psi/hpsi through the chunked three-stream pipeline (qeb_set_pipeline): same result as the oracle,
+    pad rows zeroed, becp of all columns kept; pageable numpy arrays get page-locked by the library."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=11)
+    lda, n = inp["lda"], inp["n"]
+    ref, becp_ref = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    h.set_pipeline(chunk, 2)
+    for _ in range(2):  # second call re-uses the registration of the same arrays
+        out = np.full((m, lda), np.nan + 1j * np.nan)
+        h.h_psi(lda, n, m, inp["psi"], out)
+        assert relerr(out, ref) < TOL
+        assert np.all(out[:, n:] == 0)
+        assert relerr(h.get_becp(m), becp_ref) < TOL
+    h.close()
