@@ -134,6 +134,35 @@ int qeb_h_psi_bgrp(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* h
  * all-gathers the column blocks of a DEVICE hpsi itself. */
 int qeb_set_nccl(qeb_ctx* ctx, void* nccl_comm, int nranks, int rank);
 
+/* NCCL communicators by role. libnccl is bound at run time (dlopen: $QEB_NCCL_LIB, else an already loaded
+ * libnccl.so.2, else the system one), so single-GPU use needs no NCCL.
+ *   QEB_COMM_BGRP  inter_bgrp_comm: band groups (Modules/mp_bands.f90:56-123)
+ *   QEB_COMM_RG    intra_bgrp_comm = dffts%comm: the R&G group of the distributed FFT (fft_types.f90:243-254)
+ * qeb_set_nccl_comm borrows a communicator the caller created with the same libnccl; qeb_nccl_unique_id +
+ * qeb_nccl_init create one inside the library (rank 0 makes the 128-byte id, the caller broadcasts it - MPI_Bcast in
+ * a Fortran host, torch.distributed in the Python mirror - then every rank calls qeb_nccl_init). */
+#define QEB_COMM_BGRP 0
+#define QEB_COMM_RG 1
+int qeb_set_nccl_comm(qeb_ctx* ctx, int role, void* nccl_comm, int nranks, int rank);
+int qeb_nccl_unique_id(void* id128);
+int qeb_nccl_init(qeb_ctx* ctx, int role, const void* id128, int nranks, int rank);
+
+/* Slab ("R&G") distributed smooth grid: the per-rank fft_type_descriptor of a parallel run
+ * (FFTXlib/src/fft_types.f90:35-185, filled by fft_type_set :491-943; slab decomposition = QE's default,
+ * Modules/command_line_options.f90:29):
+ *   nproc, mype           dfft%nproc, dfft%mype
+ *   nr3p(nproc)           z planes per rank        nsw(nproc)  wave sticks per rank
+ *   iss(nproc)            offset of each rank's sticks in ismap (0-based, as dfft%iss)
+ *   ismap(nismap)         1-based plane position x + nr1x*(y-1)... of every stick, wave sticks first per rank
+ *   nl, nlm (ngm)         the rank's stick-major maps nl = 1 + n3 + (isind-1)*nr3x (fft_ggen.f90:77)
+ * After this call qeb_set_kpoint takes the rank's own npw/igk/g2kin/vkb rows, qeb_set_vloc the rank's z planes
+ * of vrs (nr1*nr2*nr3p(mype) values), and qeb_h_psi / qeb_vloc_psi_* / qeb_calbec / qeb_add_vuspsi work on the
+ * rank's rows: V_loc exchanges sticks <-> planes over the QEB_COMM_RG communicator (fft_scatter_2d.f90:38-266)
+ * and calbec all-reduces becp over it (becmod.f90:395-399). */
+int qeb_set_grid_dist(qeb_ctx* ctx, int nr1, int nr2, int nr3, int nproc, int mype, const int* nr3p, const int* nsw,
+                      const int* iss, const int* ismap, int nismap, int ngm, const int* nl, const int* nlm,
+                      int gamma_only);
+
 /* ---- introspection for benchmarks / tests ------------------------------ */
 /* algorithmic HBM bytes per band of the V_loc path:
  * 16*(4*nst*nr3 + 4*nxw*nr2*nr3)[/2 Gamma] + 60*npw, and the table sizes */

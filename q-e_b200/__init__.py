@@ -6,4 +6,5 @@ entry points (h_psi, vloc_psi_k/gamma, invfft/fwfft, calbec, add_vuspsi) for
 Python callers, tests and the benchmark. There is no CPU fallback: creating a
 context without a CUDA device raises.
 """
-from .hpsi import HPsi, QebError, divide_all, lib_path, load_library  # noqa: F401
+from .hpsi import (COMM_BGRP, COMM_RG, HPsi, QebError, allgather_columns, divide_all, lib_path,  # noqa: F401
+                   load_library)

@@ -11,6 +11,7 @@
 #include <string>
 #include <vector>
 #include "../../include/qeb200.h"
+#include "distfft.h"
 #include "fullfft.h"
 #include "gemm.h"
 #include "vloc.h"
@@ -111,9 +112,21 @@ struct qeb_ctx {
     std::vector<HostReg> hostreg;
     int pipeline_chunk = 0;  // 0 = automatic
     int pipeline_min_cols = 128;
-    // nccl
+    // nccl: inter_bgrp_comm (band groups) and intra_bgrp_comm (R&G distribution)
     void* nccl = nullptr;
     int nranks = 1, rank = 0;
+    bool nccl_owned = false;
+    void* nccl_rg = nullptr;
+    bool nccl_rg_owned = false;
+    // slab-distributed dffts (qeb_set_grid_dist)
+    bool dist = false;
+    DistHost DH;
+    std::vector<int> my_cols, all_cols, col_owner, col_sidx;  // wave stick columns x + nr1*y
+    HostVlocTables Hp;   // plane tables: every wave stick, the rank's own z planes
+    VlocTables Tp;
+    VlocLaunchCfg cfgp;
+    DevBuf tabp_d, planp_d, dist_tab_d, sbuf_d, rbuf_d;
+    DistDev DD;
 };
 
 #define QEB_FAIL(ctx, code, msg)   \
@@ -204,8 +217,13 @@ int qeb_destroy(qeb_ctx* c)
     cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->g2kin_d, &c->vkb_own, &c->tab_d, &c->plan_d, &c->g1_d, &c->g2_d, &c->v_d, &c->vp_d,
                       &c->revx_d, &c->full_plan_d, &c->nlint_d, &c->deeq_d, &c->becp_d, &c->ps_d, &c->part_d,
-                      &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage};
+                      &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage, &c->tabp_d, &c->planp_d,
+                      &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d};
     for (DevBuf* b : bufs) b->release();
+    if ((c->nccl_owned || c->nccl_rg_owned) && nccl_api().ok) {
+        if (c->nccl && c->nccl_owned) nccl_api().CommDestroy(c->nccl);
+        if (c->nccl_rg && c->nccl_rg_owned) nccl_api().CommDestroy(c->nccl_rg);
+    }
     for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
     for (int i = 0; i < 5; ++i)
         if (c->vev[i]) cudaEventDestroy(c->vev[i]);
@@ -244,6 +262,33 @@ int qeb_set_async(qeb_ctx* c, int async)
     return 0;
 }
 
+// plans for the x direction permutation of V and for the full-box FFT
+static int setup_full_plans(qeb_ctx* c, int nr1, int nr2, int nr3)
+{
+    HostPlan hx, hy, hz;
+    if (!make_host_plan(nr1, hx) || !make_host_plan(nr2, hy) || !make_host_plan(nr3, hz))
+        QEB_FAIL(c, 13, "qeb_set_grid: FFT dimensions must factor into 2, 3, 5 (fft_support.f90:61-120)");
+    c->nr1 = nr1;
+    c->nr2 = nr2;
+    c->nr3 = nr3;
+    const size_t ntw = (size_t)nr1 + nr2 + nr3;
+    QEB_CUDA(c, c->full_plan_d.ensure(ntw * 16 + ntw * 4));
+    cplx* tw = (cplx*)c->full_plan_d.p;
+    int* rv = (int*)(tw + ntw);
+    const HostPlan* hp[3] = {&hx, &hy, &hz};
+    FftPlan* fp[3] = {&c->fpx, &c->fpy, &c->fpz};
+    size_t off = 0;
+    for (int d = 0; d < 3; ++d) {
+        QEB_CUDA(c, cudaMemcpyAsync(tw + off, hp[d]->tw.data(), hp[d]->tw.size() * 16, cudaMemcpyHostToDevice, c->stream));
+        QEB_CUDA(c, cudaMemcpyAsync(rv + off, hp[d]->rev.data(), hp[d]->rev.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        fill_plan(*hp[d], tw + off, rv + off, *fp[d]);
+        off += hp[d]->n;
+    }
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_full = true;
+    return 0;
+}
+
 int qeb_set_grid(qeb_ctx* c, int nr1, int nr2, int nr3, int nr1x, int nr2x, int nr3x, int ngm, const int* nl,
                  const int* nlm, int gamma_only)
 {
@@ -253,46 +298,138 @@ int qeb_set_grid(qeb_ctx* c, int nr1, int nr2, int nr3, int nr1x, int nr2x, int 
     if (nr1x != nr1 || nr2x != nr2 || nr3x != nr3)
         QEB_FAIL(c, 11, "qeb_set_grid: padded leading dimensions (nr?x != nr?) are not supported");
     if (gamma_only && !nlm) QEB_FAIL(c, 12, "qeb_set_grid: gamma_only requires nlm");
-    HostPlan hx, hy, hz;
-    if (!make_host_plan(nr1, hx) || !make_host_plan(nr2, hy) || !make_host_plan(nr3, hz))
-        QEB_FAIL(c, 13, "qeb_set_grid: FFT dimensions must factor into 2, 3, 5 (fft_support.f90:61-120)");
-    c->nr1 = nr1;
-    c->nr2 = nr2;
-    c->nr3 = nr3;
+    int rc = setup_full_plans(c, nr1, nr2, nr3);
+    if (rc) return rc;
     c->ngm = ngm;
     c->gamma = gamma_only != 0;
+    c->dist = false;
     c->nl.assign(nl, nl + ngm);
     if (c->gamma)
         c->nlm.assign(nlm, nlm + ngm);
     else
         c->nlm.clear();
-    // plans for the x direction permutation of V and for the full-box FFT
-    {
-        const size_t ntw = (size_t)nr1 + nr2 + nr3;
-        QEB_CUDA(c, c->full_plan_d.ensure(ntw * 16 + ntw * 4));
-        cplx* tw = (cplx*)c->full_plan_d.p;
-        int* rv = (int*)(tw + ntw);
-        const HostPlan* hp[3] = {&hx, &hy, &hz};
-        FftPlan* fp[3] = {&c->fpx, &c->fpy, &c->fpz};
-        size_t off = 0;
-        for (int d = 0; d < 3; ++d) {
-            QEB_CUDA(c, cudaMemcpyAsync(tw + off, hp[d]->tw.data(), hp[d]->tw.size() * 16, cudaMemcpyHostToDevice, c->stream));
-            QEB_CUDA(c, cudaMemcpyAsync(rv + off, hp[d]->rev.data(), hp[d]->rev.size() * 4, cudaMemcpyHostToDevice, c->stream));
-            fill_plan(*hp[d], tw + off, rv + off, *fp[d]);
-            off += hp[d]->n;
-        }
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        c->have_full = true;
-    }
     c->have_grid = true;
     c->have_k = false;
     c->have_v = false;
     return 0;
 }
 
-static int upload_tables(qeb_ctx* c)
+static int upload_tables(qeb_ctx* c, HostVlocTables& H, DevBuf& tab_d, DevBuf& plan_d, VlocTables& t, VlocLaunchCfg& cfg);
+static int size_workspaces_dist(qeb_ctx* c);
+
+// fft_type_descriptor of a slab ("R&G") distributed dffts: FFTXlib/src/fft_types.f90:35-185 (fields), :491-943
+// (fft_type_set). nl/nlm are the rank's stick-major maps (fft_ggen.f90:77).
+int qeb_set_grid_dist(qeb_ctx* c, int nr1, int nr2, int nr3, int nproc, int mype, const int* nr3p, const int* nsw,
+                      const int* iss, const int* ismap, int nismap, int ngm, const int* nl, const int* nlm,
+                      int gamma_only)
 {
-    HostVlocTables& H = c->H;
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (nr1 < 1 || nr2 < 1 || nr3 < 1 || nproc < 1 || mype < 0 || mype >= nproc || !nr3p || !nsw || !iss || !ismap ||
+        ngm < 1 || !nl)
+        QEB_FAIL(c, 14, "qeb_set_grid_dist: bad arguments");
+    if (gamma_only && !nlm) QEB_FAIL(c, 12, "qeb_set_grid_dist: gamma_only requires nlm");
+    int rc = setup_full_plans(c, nr1, nr2, nr3);
+    if (rc) return rc;
+    const int ncol = nr1 * nr2;
+    DistHost& D = c->DH;
+    D = DistHost();
+    D.nproc = nproc;
+    D.me = mype;
+    int zsum = 0, ssum = 0;
+    for (int p = 0; p < nproc; ++p) {
+        if (nr3p[p] < 1) QEB_FAIL(c, 15, "qeb_set_grid_dist: a rank without planes (fft_types.f90:633-635)");
+        if (nsw[p] < 0 || iss[p] < 0 || iss[p] + nsw[p] > nismap) QEB_FAIL(c, 15, "qeb_set_grid_dist: bad nsw/iss");
+        D.nr3p.push_back(nr3p[p]);
+        D.i0r3p.push_back(zsum);
+        D.nsw.push_back(nsw[p]);
+        D.prefix.push_back(ssum);
+        zsum += nr3p[p];
+        ssum += nsw[p];
+    }
+    if (zsum != nr3) QEB_FAIL(c, 15, "qeb_set_grid_dist: sum(nr3p) != nr3");
+    D.nst_tot = ssum;
+    // wave stick columns rank by rank; within a rank the exchange order is (x, y) ascending, which every rank can
+    // derive from ismap alone
+    c->col_owner.assign(ncol, -1);
+    c->col_sidx.assign(ncol, -1);
+    c->all_cols.clear();
+    c->my_cols.clear();
+    for (int p = 0; p < nproc; ++p) {
+        std::vector<int> cols(ismap + iss[p], ismap + iss[p] + nsw[p]);
+        for (int& v : cols) {
+            v -= 1;
+            if (v < 0 || v >= ncol || c->col_owner[v] >= 0) QEB_FAIL(c, 16, "qeb_set_grid_dist: bad ismap");
+            c->col_owner[v] = p;
+        }
+        std::sort(cols.begin(), cols.end(), [nr1](int a, int b) {
+            const int xa = a % nr1, xb = b % nr1;
+            return xa != xb ? xa < xb : a < b;
+        });
+        for (int i = 0; i < (int)cols.size(); ++i) c->col_sidx[cols[i]] = i;
+        c->all_cols.insert(c->all_cols.end(), cols.begin(), cols.end());
+        if (p == mype) c->my_cols = cols;
+    }
+    // the rank's maps converted to box positions col + ncol*z, so that the table builder of the serial path applies
+    const int my_off = iss[mype];
+    auto conv = [&](int v) {
+        const int s = (v - 1) / nr3, z = (v - 1) % nr3;
+        if (v < 1 || my_off + s >= nismap) return 0;  // 0: invalid (only an error if igk refers to it)
+        const int col = ismap[my_off + s] - 1;
+        if (col < 0 || col >= ncol) return 0;
+        return 1 + col + ncol * z;
+    };
+    c->nl.resize(ngm);
+    for (int i = 0; i < ngm; ++i) c->nl[i] = conv(nl[i]);
+    c->nlm.clear();
+    if (gamma_only) {
+        c->nlm.resize(ngm);
+        for (int i = 0; i < ngm; ++i) c->nlm[i] = conv(nlm[i]);
+    }
+    c->ngm = ngm;
+    c->gamma = gamma_only != 0;
+    // plane tables: all wave sticks, this rank's z planes
+    std::string e = build_vloc_tables(nr1, nr2, nr3p[mype], 0, nullptr, nullptr, nullptr, 0, c->Hp, 72 * 1024,
+                                      c->all_cols.data(), (int)c->all_cols.size(), false, c->gamma);
+    if (!e.empty()) QEB_FAIL(c, 17, "qeb_set_grid_dist: " + e);
+    if (c->Hp.nst != D.nst_tot) QEB_FAIL(c, 17, "qeb_set_grid_dist: inconsistent stick count");
+    if ((rc = upload_tables(c, c->Hp, c->tabp_d, c->planp_d, c->Tp, c->cfgp))) return rc;
+    // exchange tables: owner and position-in-owner of every plane-ordered stick
+    {
+        const int nst = c->Hp.nst;
+        std::vector<int> host((size_t)2 * nst + 2 * nproc);
+        for (int sg = 0; sg < nst; ++sg) {
+            const int col = c->Hp.stick_x[sg] + nr1 * c->Hp.stick_y[sg];
+            host[sg] = c->col_owner[col];
+            host[nst + sg] = c->col_sidx[col];
+        }
+        for (int p = 0; p < nproc; ++p) {
+            host[2 * nst + p] = D.nsw[p];
+            host[2 * nst + nproc + p] = D.prefix[p];
+        }
+        QEB_CUDA(c, c->dist_tab_d.ensure(host.size() * 4 + 16));
+        QEB_CUDA(c, cudaMemcpyAsync(c->dist_tab_d.p, host.data(), host.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        const int* b = (const int*)c->dist_tab_d.p;
+        c->DD.nproc = nproc;
+        c->DD.me = mype;
+        c->DD.nz_me = nr3p[mype];
+        c->DD.nst_tot = nst;
+        c->DD.nst_me = nsw[mype];
+        c->DD.own = b;
+        c->DD.sidx = b + nst;
+        c->DD.nsw = b + 2 * nst;
+        c->DD.prefix = b + 2 * nst + nproc;
+    }
+    c->dist = true;
+    c->have_grid = true;
+    c->have_k = false;
+    c->have_v = false;
+    return 0;
+}
+
+static int upload_tables(qeb_ctx* c, HostVlocTables& H, DevBuf& tab_d, DevBuf& plan_d, VlocTables& t, VlocLaunchCfg& cfg)
+{
     // integer tables in one allocation
     std::vector<const std::vector<int>*> vs = {&H.xmap, &H.plane_s0, &H.plane_ns, &H.ymap, &H.grp_stick, &H.grp_nl,
                                                &H.grp_coef_off, &H.coef_ig, &H.coef_slot, &H.coef_slot2};
@@ -304,14 +441,13 @@ static int upload_tables(qeb_ctx* c)
     }
     const size_t div_off = tot;
     tot += H.grp_div.size() * 3;
-    QEB_CUDA(c, c->tab_d.ensure(tot * 4 + 16));
+    QEB_CUDA(c, tab_d.ensure(tot * 4 + 16));
     std::vector<int> host(tot, 0);
     for (size_t i = 0; i < vs.size(); ++i)
         if (!vs[i]->empty()) memcpy(host.data() + offs[i], vs[i]->data(), vs[i]->size() * 4);
     if (!H.grp_div.empty()) memcpy(host.data() + div_off, H.grp_div.data(), H.grp_div.size() * 12);
-    QEB_CUDA(c, cudaMemcpyAsync(c->tab_d.p, host.data(), tot * 4, cudaMemcpyHostToDevice, c->stream));
-    const int* base = (const int*)c->tab_d.p;
-    VlocTables& t = c->T;
+    QEB_CUDA(c, cudaMemcpyAsync(tab_d.p, host.data(), tot * 4, cudaMemcpyHostToDevice, c->stream));
+    const int* base = (const int*)tab_d.p;
     memset(&t, 0, sizeof(t));
     t.nr1 = H.nr1;
     t.nr2 = H.nr2;
@@ -343,21 +479,37 @@ static int upload_tables(qeb_ctx* c)
     t.nsmax = H.nsmax;
     // plans
     const size_t ntw = (size_t)H.nr1 + H.nr2 + H.nr3;
-    QEB_CUDA(c, c->plan_d.ensure(ntw * 20));
-    cplx* tw = (cplx*)c->plan_d.p;
+    QEB_CUDA(c, plan_d.ensure(ntw * 20));
+    cplx* tw = (cplx*)plan_d.p;
     int* rv = (int*)(tw + ntw);
     const HostPlan* hp[3] = {&H.px, &H.py, &H.pz};
     FftPlan* fp[3] = {&t.px, &t.py, &t.pz};
     size_t off = 0;
     for (int d = 0; d < 3; ++d) {
+        if (hp[d]->tw.empty()) continue;  // plane tables carry no z plan
         QEB_CUDA(c, cudaMemcpyAsync(tw + off, hp[d]->tw.data(), hp[d]->tw.size() * 16, cudaMemcpyHostToDevice, c->stream));
         QEB_CUDA(c, cudaMemcpyAsync(rv + off, hp[d]->rev.data(), hp[d]->rev.size() * 4, cudaMemcpyHostToDevice, c->stream));
         fill_plan(*hp[d], tw + off, rv + off, *fp[d]);
         off += hp[d]->n;
     }
     QEB_CUDA(c, cudaStreamSynchronize(c->stream));  // host vectors go out of scope
-    // workspaces
+    t.vp = (const double*)c->vp_d.p;
+    cfg.smem_z = H.smem_z;
+    cfg.smem_y = H.smem_y;
+    cfg.smem_x = H.smem_x;
+    cfg.threads_z = cfg.threads_y = cfg.threads_x = 256;
+    if (H.smem_z > c->max_smem || H.smem_y > c->max_smem || H.smem_x > c->max_smem)
+        QEB_FAIL(c, 21, "FFT dimension too large for the shared-memory pencil kernels");
+    return 0;
+}
+
+// batch size and the G1/G2 workspaces of the single-GPU path
+static int size_workspaces(qeb_ctx* c)
+{
+    HostVlocTables& H = c->H;
+    VlocTables& t = c->T;
     t.g1_box = (size_t)H.nst * H.nr3;
+    t.g1_zs = (size_t)H.nst;
     t.g2_box = (size_t)H.nxw * t.npos;
     int nb = c->batch_user;
     if (nb <= 0) {
@@ -372,13 +524,38 @@ static int upload_tables(qeb_ctx* c)
     QEB_CUDA(c, c->g2_d.ensure(t.g2_box * 16 * nb * c->vloc_nstreams));
     t.g1 = (cplx*)c->g1_d.p;
     t.g2 = (cplx*)c->g2_d.p;
-    t.vp = (const double*)c->vp_d.p;
-    c->cfg.smem_z = H.smem_z;
-    c->cfg.smem_y = H.smem_y;
-    c->cfg.smem_x = H.smem_x;
-    c->cfg.threads_z = c->cfg.threads_y = c->cfg.threads_x = 256;
-    if (H.smem_z > c->max_smem || H.smem_y > c->max_smem || H.smem_x > c->max_smem)
-        QEB_FAIL(c, 21, "FFT dimension too large for the shared-memory pencil kernels");
+    return 0;
+}
+
+// slab-distributed path: S (own sticks, all z), R (all sticks, own z, rank-blocked), G1 and G2 of the plane passes
+static int size_workspaces_dist(qeb_ctx* c)
+{
+    const DistHost& D = c->DH;
+    VlocTables& tz = c->T;
+    VlocTables& tp = c->Tp;
+    const size_t nst_me = (size_t)D.nsw[D.me], nz_me = (size_t)D.nr3p[D.me];
+    if ((size_t)c->H.nst != nst_me)
+        QEB_FAIL(c, 26, "qeb_set_kpoint: plane waves outside the rank's wave sticks (igk/nl do not match the descriptor)");
+    tp.g1_box = (size_t)tp.nst * nz_me;
+    tp.g1_zs = (size_t)tp.nst;
+    tp.g2_box = (size_t)tp.nxw * tp.npos;
+    int nb = c->batch_user;
+    if (nb <= 0) {
+        const size_t target = (size_t)48 << 20;
+        nb = (int)(target / (tp.g2_box * 16 + 1));
+        if (nb < 1) nb = 1;
+        if (nb > 64) nb = 64;
+    }
+    c->batch = nb;
+    QEB_CUDA(c, c->sbuf_d.ensure(std::max<size_t>(16, nst_me * c->nr3 * 16 * nb)));
+    QEB_CUDA(c, c->rbuf_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb)));
+    QEB_CUDA(c, c->g1_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb)));
+    QEB_CUDA(c, c->g2_d.ensure(std::max<size_t>(16, tp.g2_box * 16 * nb)));
+    tz.g1 = (cplx*)c->sbuf_d.p;
+    tz.g2 = nullptr;
+    tz.g1_box = nst_me;  // [z][box][stick]: see VlocTables::g1_zs
+    tp.g1 = (cplx*)c->g1_d.p;
+    tp.g2 = (cplx*)c->g2_d.p;
     return 0;
 }
 
@@ -396,14 +573,16 @@ int qeb_set_kpoint(qeb_ctx* c, int npw, int npwx, const int* igk, const double* 
     }
     if (!c->gamma && !igk) QEB_FAIL(c, 24, "qeb_set_kpoint: igk required for k-points");
     std::string e = build_vloc_tables(c->nr1, c->nr2, c->nr3, npw, c->nl.data(), c->gamma ? c->nlm.data() : nullptr, igk,
-                                      c->ngm, c->H, 72 * 1024);
+                                      c->ngm, c->H, 72 * 1024, c->dist ? c->my_cols.data() : nullptr,
+                                      c->dist ? (int)c->my_cols.size() : 0);
     if (!e.empty()) QEB_FAIL(c, 25, "qeb_set_kpoint: " + e);
     c->npw = npw;
     c->npwx = npwx;
     c->nkb = nkb;
     c->gstart = gstart;
-    int rc = upload_tables(c);
+    int rc = upload_tables(c, c->H, c->tab_d, c->plan_d, c->T, c->cfg);
     if (rc) return rc;
+    if ((rc = c->dist ? size_workspaces_dist(c) : size_workspaces(c))) return rc;
     QEB_CUDA(c, c->g2kin_d.ensure((size_t)npw * 8));
     QEB_CUDA(c, cudaMemcpyAsync(c->g2kin_d.p, g2kin, (size_t)npw * 8,
                                 is_device_ptr(g2kin) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
@@ -426,14 +605,17 @@ int qeb_set_kpoint(qeb_ctx* c, int npw, int npwx, const int* igk, const double* 
 
 static int prepare_v(qeb_ctx* c, const double* v)
 {
-    const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
+    // distributed: v holds the rank's own z planes (dffts%nnr points of the slab, x fastest)
+    const int nz = c->dist ? c->DH.nr3p[c->DH.me] : c->nr3;
+    const size_t nnr = (size_t)c->nr1 * c->nr2 * nz;
     const void* vd = nullptr;
     int rc = stage_in(c, v, nnr * 8, c->v_d, &vd);
     if (rc) return rc;
     QEB_CUDA(c, c->vp_d.ensure(nnr * 8));
     const double scale = 1.0 / ((double)c->nr1 * c->nr2 * c->nr3);
-    QEB_CUDA(c, vloc_prepare_v((const double*)vd, (double*)c->vp_d.p, c->fpx.rev, c->nr1, c->nr2, c->nr3, scale, c->stream));
+    QEB_CUDA(c, vloc_prepare_v((const double*)vd, (double*)c->vp_d.p, c->fpx.rev, c->nr1, c->nr2, nz, scale, c->stream));
     c->T.vp = (const double*)c->vp_d.p;
+    c->Tp.vp = (const double*)c->vp_d.p;
     c->have_v = true;
     return 0;
 }
@@ -499,6 +681,29 @@ static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hp
     io.nbands = m;
     io.gamma = c->gamma ? 1 : 0;
     const int nboxes = c->gamma ? (m + 1) / 2 : m;
+    if (c->dist) {
+        // cft_1z | fft_scatter | cft_2xy * V * cft_2xy | fft_scatter | cft_1z  (fft_parallel_2d.f90:36-204)
+        const DistHost& D = c->DH;
+        if (D.nproc > 1 && !c->nccl_rg) QEB_FAIL(c, 53, "V_loc: no NCCL communicator for the R&G group (qeb_nccl_init)");
+        cplx* S = (cplx*)c->sbuf_d.p;
+        cplx* R = (cplx*)c->rbuf_d.p;
+        for (int b0 = 0; b0 < nboxes; b0 += c->batch) {
+            const int nb = std::min(c->batch, nboxes - b0);
+            io.band0 = c->gamma ? 2 * b0 : b0;
+            VlocTables tz = c->T;
+            tz.g1_zs = (size_t)nb * tz.g1_box;
+            const char* msg = "";
+            int rc;
+            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, c->stream));
+            if ((rc = dist_exchange(D, c->nccl_rg, true, S, R, nb, c->stream, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            QEB_CUDA(c, dist_unpack(c->DD, R, c->Tp.g1, nb, c->stream));
+            QEB_CUDA(c, vloc_launch_planes(c->Tp, c->cfgp, nb, c->stream));
+            QEB_CUDA(c, dist_pack(c->DD, c->Tp.g1, R, nb, c->stream));
+            if ((rc = dist_exchange(D, c->nccl_rg, false, S, R, nb, c->stream, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            QEB_CUDA(c, vloc_launch_zpass(false, tz, io, c->cfg, nb, c->stream));
+        }
+        return 0;
+    }
     const int nbatches = (nboxes + c->batch - 1) / c->batch;
     const int ns = std::min(c->vloc_nstreams, nbatches);
     if (ns > 1) {  // fork: the side streams start after everything queued so far on the main stream
@@ -542,6 +747,14 @@ static int run_calbec(qeb_ctx* c, const cplx* beta, int npwx, int nkb, const cpl
     QEB_CUDA(c, c->part_d.ensure(calbec_workspace_bytes(nkb, m, nsplit, !c->gamma)));
     QEB_CUDA(c, launch_calbec(beta, npwx, psi, lda, n, nkb, m, !c->gamma, c->gstart, nsplit, gchunk, c->part_d.p,
                               becp_out, c->stream));
+    if (c->dist && c->DH.nproc > 1) {
+        // mp_sum(becp, intra_bgrp_comm): Modules/becmod.f90:395-399 (k), :327-331 (Gamma)
+        const NcclApi& A = nccl_api();
+        if (!A.ok || !c->nccl_rg) QEB_FAIL(c, 54, "calbec: no NCCL communicator for the R&G group (qeb_nccl_init)");
+        const int rc = A.AllReduce(becp_out, becp_out, (size_t)nkb * m * (c->gamma ? 1 : 2), kNcclDouble, kNcclSum,
+                                   c->nccl_rg, c->stream);
+        if (rc) QEB_FAIL(c, 900 + rc, std::string("ncclAllReduce(becp): ") + A.GetErrorString(rc));
+    }
     return 0;
 }
 
@@ -854,10 +1067,52 @@ int qeb_divide_all(int m, int nproc, int me, int* start, int* end)
 
 int qeb_set_nccl(qeb_ctx* c, void* comm, int nranks, int rank)
 {
-    if (!c || nranks < 1 || rank < 0 || rank >= nranks) return 1;
-    c->nccl = comm;
-    c->nranks = nranks;
-    c->rank = rank;
+    return qeb_set_nccl_comm(c, QEB_COMM_BGRP, comm, nranks, rank);
+}
+
+int qeb_set_nccl_comm(qeb_ctx* c, int role, void* comm, int nranks, int rank)
+{
+    if (!c || nranks < 1 || rank < 0 || rank >= nranks || (role != QEB_COMM_BGRP && role != QEB_COMM_RG)) return 1;
+    const NcclApi& A = nccl_api();
+    if (role == QEB_COMM_BGRP) {
+        if (c->nccl && c->nccl_owned && A.ok) A.CommDestroy(c->nccl);
+        c->nccl = comm;
+        c->nccl_owned = false;
+        c->nranks = nranks;
+        c->rank = rank;
+    } else {
+        if (c->nccl_rg && c->nccl_rg_owned && A.ok) A.CommDestroy(c->nccl_rg);
+        c->nccl_rg = comm;
+        c->nccl_rg_owned = false;
+    }
+    return 0;
+}
+
+int qeb_nccl_unique_id(void* id128)
+{
+    const NcclApi& A = nccl_api();
+    if (!A.ok || !id128) return 1;
+    return A.GetUniqueId((NcclUniqueId*)id128);
+}
+
+int qeb_nccl_init(qeb_ctx* c, int role, const void* id128, int nranks, int rank)
+{
+    if (!c) return 1;
+    if (!id128 || nranks < 1 || rank < 0 || rank >= nranks || (role != QEB_COMM_BGRP && role != QEB_COMM_RG))
+        QEB_FAIL(c, 91, "qeb_nccl_init: bad arguments");
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    const NcclApi& A = nccl_api();
+    if (!A.ok) QEB_FAIL(c, 92, std::string("qeb_nccl_init: ") + A.why);
+    NcclUniqueId id;
+    memcpy(&id, id128, sizeof(id));
+    NcclComm comm = nullptr;
+    const int rc = A.CommInitRank(&comm, nranks, id, rank);
+    if (rc) QEB_FAIL(c, 900 + rc, std::string("ncclCommInitRank: ") + A.GetErrorString(rc));
+    qeb_set_nccl_comm(c, role, comm, nranks, rank);
+    if (role == QEB_COMM_BGRP)
+        c->nccl_owned = true;
+    else
+        c->nccl_rg_owned = true;
     return 0;
 }
 
@@ -866,10 +1121,34 @@ int qeb_h_psi_bgrp(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hps
     if (!c) return 1;
     int s, e;
     if (qeb_divide_all(m, nbgrp, my_bgrp, &s, &e)) QEB_FAIL(c, 90, "qeb_h_psi_bgrp: bad band-group arguments");
-    if (e == s) return 0;
-    const char* p = (const char*)psi + (size_t)s * lda * 16;
-    char* h = (char*)hpsi + (size_t)s * lda * 16;
-    return qeb_h_psi(c, lda, n, e - s, p, h);
+    const bool gather = c->nccl && c->nranks == nbgrp && c->rank == my_bgrp && nbgrp > 1 && is_device_ptr(hpsi);
+    if (e > s) {
+        const char* p = (const char*)psi + (size_t)s * lda * 16;
+        char* h = (char*)hpsi + (size_t)s * lda * 16;
+        const bool was_async = c->async;
+        if (gather) c->async = true;  // the all-gather is queued behind the kernels; one sync at the end
+        const int rc = qeb_h_psi(c, lda, n, e - s, p, h);
+        c->async = was_async;
+        if (rc) return rc;
+    }
+    if (!gather) return 0;
+    // mp_allgather(hpsi, column_type, recv_counts, displs, inter_bgrp_comm)  (PW/src/h_psi.f90:58-63): every group
+    // sends its column block to all others; blocks may differ by one column (divide_all)
+    const NcclApi& A = nccl_api();
+    if (!A.ok) QEB_FAIL(c, 92, std::string("qeb_h_psi_bgrp: ") + A.why);
+    int rc = A.GroupStart();
+    for (int q = 0; q < nbgrp && rc == 0; ++q) {
+        if (q == my_bgrp) continue;
+        int qs, qe;
+        qeb_divide_all(m, nbgrp, q, &qs, &qe);
+        if (e > s) rc = A.Send((char*)hpsi + (size_t)s * lda * 16, (size_t)(e - s) * lda * 2, kNcclDouble, q, c->nccl, c->stream);
+        if (rc == 0 && qe > qs)
+            rc = A.Recv((char*)hpsi + (size_t)qs * lda * 16, (size_t)(qe - qs) * lda * 2, kNcclDouble, q, c->nccl, c->stream);
+    }
+    const int rc2 = A.GroupEnd();
+    if (rc == 0) rc = rc2;
+    if (rc) QEB_FAIL(c, 900 + rc, std::string("all-gather of hpsi: ") + A.GetErrorString(rc));
+    return finish(c);
 }
 
 int qeb_get_stats(qeb_ctx* c, double* vloc_bytes_per_band, double* gemm_flops_per_band, int* nst, int* nxw, int* nboxes)

@@ -1,0 +1,81 @@
+#include "distfft.h"
+
+namespace qeb {
+
+template <bool UNPACK>
+__global__ void __launch_bounds__(256) k_dist_repack(const DistDev d, const cplx* __restrict__ src, cplx* __restrict__ dst,
+                                                      int nb)
+{
+    const int sg = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sg >= d.nst_tot) return;
+    const int zl = blockIdx.y, box = blockIdx.z;
+    const int p = d.own[sg];
+    const size_t r = (size_t)nb * d.nz_me * d.prefix[p] + ((size_t)zl * nb + box) * d.nsw[p] + d.sidx[sg];
+    const size_t g = ((size_t)box * d.nz_me + zl) * d.nst_tot + sg;
+    if (UNPACK)
+        dst[g] = src[r];
+    else
+        dst[r] = src[g];
+}
+
+cudaError_t dist_unpack(const DistDev& d, const cplx* R, cplx* g1p, int nb, cudaStream_t st)
+{
+    if (d.nst_tot <= 0 || d.nz_me <= 0 || nb <= 0) return cudaSuccess;
+    dim3 grid((d.nst_tot + 255) / 256, d.nz_me, nb);
+    k_dist_repack<true><<<grid, 256, 0, st>>>(d, R, g1p, nb);
+    return cudaGetLastError();
+}
+
+cudaError_t dist_pack(const DistDev& d, const cplx* g1p, cplx* R, int nb, cudaStream_t st)
+{
+    if (d.nst_tot <= 0 || d.nz_me <= 0 || nb <= 0) return cudaSuccess;
+    dim3 grid((d.nst_tot + 255) / 256, d.nz_me, nb);
+    k_dist_repack<false><<<grid, 256, 0, st>>>(d, g1p, R, nb);
+    return cudaGetLastError();
+}
+
+int dist_exchange(const DistHost& h, NcclComm comm, bool forward, cplx* S, cplx* R, int nb, cudaStream_t st,
+                  const char** msg)
+{
+    const int me = h.me;
+    const size_t nst_me = (size_t)h.nsw[me], nz_me = (size_t)h.nr3p[me];
+    auto s_off = [&](int q) { return (size_t)h.i0r3p[q] * nb * nst_me; };       // my sticks, z range of rank q
+    auto s_cnt = [&](int q) { return (size_t)h.nr3p[q] * nb * nst_me; };
+    auto r_off = [&](int p) { return (size_t)nb * nz_me * h.prefix[p]; };       // rank p's sticks, my z range
+    auto r_cnt = [&](int p) { return nz_me * nb * (size_t)h.nsw[p]; };
+    // own block: device copy
+    if (s_cnt(me)) {
+        cudaError_t e = forward ? cudaMemcpyAsync(R + r_off(me), S + s_off(me), s_cnt(me) * 16, cudaMemcpyDeviceToDevice, st)
+                                : cudaMemcpyAsync(S + s_off(me), R + r_off(me), s_cnt(me) * 16, cudaMemcpyDeviceToDevice, st);
+        if (e != cudaSuccess) {
+            *msg = cudaGetErrorString(e);
+            return 1000 + (int)e;
+        }
+    }
+    if (h.nproc == 1) return 0;
+    const NcclApi& A = nccl_api();
+    if (!A.ok || !comm) {
+        *msg = A.ok ? "no NCCL communicator set (qeb_nccl_init / qeb_set_nccl)" : A.why;
+        return 900;
+    }
+    int rc = A.GroupStart();
+    for (int q = 0; q < h.nproc && rc == 0; ++q) {
+        if (q == me) continue;
+        if (forward) {
+            if (s_cnt(q)) rc = A.Send(S + s_off(q), 2 * s_cnt(q), kNcclDouble, q, comm, st);
+            if (rc == 0 && r_cnt(q)) rc = A.Recv(R + r_off(q), 2 * r_cnt(q), kNcclDouble, q, comm, st);
+        } else {
+            if (r_cnt(q)) rc = A.Send(R + r_off(q), 2 * r_cnt(q), kNcclDouble, q, comm, st);
+            if (rc == 0 && s_cnt(q)) rc = A.Recv(S + s_off(q), 2 * s_cnt(q), kNcclDouble, q, comm, st);
+        }
+    }
+    const int rc2 = A.GroupEnd();
+    if (rc == 0) rc = rc2;
+    if (rc != 0) {
+        *msg = A.GetErrorString(rc);
+        return 900 + rc;
+    }
+    return 0;
+}
+
+}  // namespace qeb

@@ -137,21 +137,39 @@ cudaError_t vloc_init_attrs(size_t max_smem)
     return cudaGetLastError();
 }
 
-cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
+cudaError_t vloc_launch_zpass(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
                               cudaStream_t st)
 {
-    if (nboxes <= 0) return cudaSuccess;
-    if (!launch_z(true, t, io, cfg, nboxes, st))
-        k_vloc_zinv<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
+    if (nboxes <= 0 || t.ngrp <= 0) return cudaSuccess;
+    if (!launch_z(inv, t, io, cfg, nboxes, st)) {
+        if (inv)
+            k_vloc_zinv<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
+        else
+            k_vloc_zfwd<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t vloc_launch_planes(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
+{
+    if (nboxes <= 0 || t.nxw <= 0 || t.npos <= 0) return cudaSuccess;
     if (!launch_y(true, t, cfg, nboxes, st))
         k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
     if (!launch_x(t, cfg, nboxes, st))
         k_vloc_xfus<<<dim3(t.ntx, nboxes), cfg.threads_x, cfg.smem_x, st>>>(t);
     if (!launch_y(false, t, cfg, nboxes, st))
         k_vloc_yfwd<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
-    if (!launch_z(false, t, io, cfg, nboxes, st))
-        k_vloc_zfwd<<<dim3(t.ngrp, nboxes), cfg.threads_z, cfg.smem_z, st>>>(t, io);
     return cudaGetLastError();
+}
+
+cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
+                              cudaStream_t st)
+{
+    if (nboxes <= 0) return cudaSuccess;
+    cudaError_t e;
+    if ((e = vloc_launch_zpass(true, t, io, cfg, nboxes, st)) != cudaSuccess) return e;
+    if ((e = vloc_launch_planes(t, cfg, nboxes, st)) != cudaSuccess) return e;
+    return vloc_launch_zpass(false, t, io, cfg, nboxes, st);
 }
 
 cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr1, int nr2, int nr3, double scale,

@@ -11,6 +11,11 @@ cudaError_t vloc_init_attrs(size_t max_smem);
 // one batch of nboxes boxes (bands for k, band pairs for Gamma)
 cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
                               cudaStream_t st);
+// the pieces of a batch, used separately by the slab-distributed path (an exchange sits between them):
+// z pass (inv: scatter + z inverse -> G1; !inv: G1 -> z forward + gather) and the three plane passes (y, fused x, y)
+cudaError_t vloc_launch_zpass(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
+                              cudaStream_t st);
+cudaError_t vloc_launch_planes(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st);
 // vp[xpos*npos + y*nr3 + z] = v[x = rev_x[xpos] + nr1*(y + nr2*z)] * scale
 cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr1, int nr2, int nr3, double scale,
                            cudaStream_t st);

@@ -46,7 +46,7 @@ QEB_HD void zinv_fast_phase(int ph, int tid, int nthr, const VlocTables& t, cons
     LaneTile s{smem, t.TZ};
     NoMid nm;
     if (p == PL::NP - 1) {
-        G1Dst d{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.nst};
+        G1Dst d{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.g1_zs};
         SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, d, nm);
     } else {
         SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, s, nm);
@@ -71,7 +71,7 @@ QEB_HD void zfwd_fast_phase(int ph, int tid, int nthr, const VlocTables& t, cons
     LaneTile s{smem, t.TZ};
     NoMid nm;
     if (ph == 0) {
-        G1Dst g{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.nst};
+        G1Dst g{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.g1_zs};
         SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, g, s, nm);
     } else {
         SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, s, s, nm);

@@ -51,6 +51,10 @@ struct VlocTables {
     cplx* g1;
     cplx* g2;
     size_t g1_box, g2_box;  // elements per box
+    // z passes only: element stride between consecutive z of one stick in G1 (nst when G1 is [box][z][stick]; the
+    // slab-distributed path uses [z][box][stick] = nboxes*nst with g1_box = nst, so that the z range owned by a
+    // peer rank is one contiguous block of the batch)
+    size_t g1_zs;
 };
 
 struct VlocIO {
@@ -72,9 +76,9 @@ struct G1Dst {  // last z-DIF pass: position -> z = rev[pos], line -> stick
     cplx* g1;
     const int* rev;
     const int* sticks;
-    int nst;
-    QEB_HD void store(int line, int pos, cplx v) const { g1[(size_t)rev[pos] * nst + sticks[line]] = v; }
-    QEB_HD cplx load(int line, int pos) const { return g1[(size_t)rev[pos] * nst + sticks[line]]; }
+    size_t zs;
+    QEB_HD void store(int line, int pos, cplx v) const { g1[(size_t)rev[pos] * zs + sticks[line]] = v; }
+    QEB_HD cplx load(int line, int pos) const { return g1[(size_t)rev[pos] * zs + sticks[line]]; }
 };
 
 QEB_HD int zinv_nphase(const VlocTables& t) { return 2 + t.pz.npass; }
@@ -133,7 +137,7 @@ QEB_HD void zinv_phase(int ph, int tid, int nthr, const VlocTables& t, const Vlo
     SmemTile s{smem, TZ};
     NoMid nm;
     if (p == t.pz.npass - 1) {
-        G1Dst d{t.g1 + (size_t)box * t.g1_box, t.pz.rev, t.grp_stick + (size_t)grp * TZ, t.nst};
+        G1Dst d{t.g1 + (size_t)box * t.g1_box, t.pz.rev, t.grp_stick + (size_t)grp * TZ, t.g1_zs};
         fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.pz.tw, +1.0, s, d, nm);
     } else {
         fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.pz.tw, +1.0, s, s, nm);
@@ -158,7 +162,7 @@ QEB_HD void zfwd_phase(int ph, int tid, int nthr, const VlocTables& t, const Vlo
         SmemTile s{smem, TZ};
         NoMid nm;
         if (ph == 0) {
-            G1Dst g{t.g1 + (size_t)box * t.g1_box, t.pz.rev, t.grp_stick + (size_t)grp * TZ, t.nst};
+            G1Dst g{t.g1 + (size_t)box * t.g1_box, t.pz.rev, t.grp_stick + (size_t)grp * TZ, t.g1_zs};
             fft_pass<true, false>(tid, nthr, nl, dnl, pd, t.pz.tw, -1.0, g, s, nm);
         } else {
             fft_pass<true, false>(tid, nthr, nl, dnl, pd, t.pz.tw, -1.0, s, s, nm);

@@ -48,15 +48,20 @@ inline int pick_tile(int n, int lo, int hi)
 }
 
 // nl/nlm/igk are the reference's 1-based arrays. igk == nullptr => igk(i) = i.
+// force_cols: box columns (x + nr1*y) that are sticks even if no coefficient lies on them (the slab-distributed
+// path transforms every wave stick of the descriptor, because all ranks must agree on the stick lists).
+// need_pz = false builds plane tables only (nr3 = number of local z planes, any value).
 inline std::string build_vloc_tables(int nr1, int nr2, int nr3, int npw, const int* nl, const int* nlm,
-                                     const int* igk, int ngm, HostVlocTables& T, size_t smem_cap = 72 * 1024)
+                                     const int* igk, int ngm, HostVlocTables& T, size_t smem_cap = 72 * 1024,
+                                     const int* force_cols = nullptr, int nforce = 0, bool need_pz = true,
+                                     bool gamma_flag = false)
 {
     T = HostVlocTables();
     T.nr1 = nr1;
     T.nr2 = nr2;
     T.nr3 = nr3;
-    T.gamma = nlm != nullptr;
-    if (!make_host_plan(nr1, T.px) || !make_host_plan(nr2, T.py) || !make_host_plan(nr3, T.pz))
+    T.gamma = nlm != nullptr || gamma_flag;
+    if (!make_host_plan(nr1, T.px) || !make_host_plan(nr2, T.py) || (need_pz && !make_host_plan(nr3, T.pz)))
         return "FFT dimension with a prime factor other than 2, 3, 5";
     const int ncol = nr1 * nr2;
     std::vector<int> col_stick(ncol, -1);
@@ -68,12 +73,16 @@ inline std::string build_vloc_tables(int nr1, int nr2, int nr3, int npw, const i
         if (b < 0 || b >= ncol * nr3) return "nl out of range";
         cpos[i] = b;
         col_stick[b % ncol] = -2;
-        if (T.gamma) {
+        if (nlm) {
             int bm = nlm[ig - 1] - 1;
             if (bm < 0 || bm >= ncol * nr3) return "nlm out of range";
             cneg[i] = bm;
             col_stick[bm % ncol] = -2;
         }
+    }
+    for (int i = 0; i < nforce; ++i) {
+        if (force_cols[i] < 0 || force_cols[i] >= ncol) return "stick column out of range";
+        col_stick[force_cols[i]] = -2;
     }
     // sticks ordered by (x, y); planes by x
     T.xmap.assign(nr1, -1);

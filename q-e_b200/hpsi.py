@@ -17,6 +17,8 @@ _LIB = None
 
 FFT_RHO = 0
 FFT_WAVE = 1
+COMM_BGRP = 0  # inter_bgrp_comm (band groups)
+COMM_RG = 1    # intra_bgrp_comm = dffts%comm (R&G distribution)
 
 
 class QebError(RuntimeError):
@@ -60,13 +62,18 @@ def load_library():
     L.qeb_divide_all.argtypes = [I, I, I, ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_h_psi_bgrp.argtypes = [P, I, I, I, P, P, I, I]
     L.qeb_set_nccl.argtypes = [P, P, I, I]
+    L.qeb_set_nccl_comm.argtypes = [P, I, P, I, I]
+    L.qeb_nccl_unique_id.argtypes = [P]
+    L.qeb_nccl_init.argtypes = [P, I, P, I, I]
+    L.qeb_set_grid_dist.argtypes = [P, I, I, I, I, I, P, P, P, P, I, I, P, P, I]
     L.qeb_get_stats.argtypes = [P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
                                 ctypes.POINTER(I), ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_nonlocal_only.argtypes = [P, I, I, I, P, P]
     for name in ("qeb_create", "qeb_destroy", "qeb_set_pipeline", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
                  "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
-                 "qeb_get_stats", "qeb_nonlocal_only"):
+                 "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
+                 "qeb_set_grid_dist"):
         getattr(L, name).restype = I
     _LIB = L
     return L
@@ -79,6 +86,21 @@ def divide_all(m: int, nproc: int, me: int):
     if L.qeb_divide_all(m, nproc, me, ctypes.byref(s), ctypes.byref(e)):
         raise QebError("divide_all: bad arguments")
     return s.value, e.value
+
+
+def allgather_columns(hpsi, m: int, group=None):
+    """The band-group all-gather of PW/src/h_psi.f90:58-63 for hosts that keep hpsi in torch tensors: every rank
+    of `group` owns the divide_all column block of hpsi (shape (m, lda[, 2])) and receives the others'. Works on
+    any torch.distributed backend (NCCL on GPUs, gloo on CPU)."""
+    import torch.distributed as dist
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    for r in range(world):
+        s, e = divide_all(m, world, r)
+        if e > s:
+            src = dist.get_global_rank(group, r) if group is not None else r
+            dist.broadcast(hpsi[s:e], src=src, group=group)
+    return hpsi
 
 
 def _ptr(a):
@@ -150,6 +172,34 @@ class HPsi:
         self.nr = (nr1, nr2, nr3)
         self._ck(self._L.qeb_set_grid(self._h, nr1, nr2, nr3, nr1x or nr1, nr2x or nr2, nr3x or nr3, nl.size, _ptr(nl),
                                       _ptr(nlm), int(gamma_only)), "qeb_set_grid")
+
+    def set_grid_dist(self, nr1, nr2, nr3, nproc, mype, nr3p, nsw, iss, ismap, nl, nlm=None, gamma_only=False):
+        """Per-rank descriptor of a slab-distributed dffts (fft_types.f90:35-185): see qeb_set_grid_dist."""
+        nr3p, nsw, iss, ismap, nl, nlm = map(_i32, (nr3p, nsw, iss, ismap, nl, nlm))
+        self.gamma_only = bool(gamma_only)
+        self.nr = (nr1, nr2, nr3)
+        self._ck(self._L.qeb_set_grid_dist(self._h, nr1, nr2, nr3, nproc, mype, _ptr(nr3p), _ptr(nsw), _ptr(iss),
+                                           _ptr(ismap), ismap.size, nl.size, _ptr(nl), _ptr(nlm), int(gamma_only)),
+                 "qeb_set_grid_dist")
+
+    def nccl_init(self, role=COMM_RG, group=None):
+        """Creates the library's own NCCL communicator for `role` over a torch.distributed group: rank 0 makes the
+        unique id, torch.distributed broadcasts it (the Fortran host would MPI_Bcast it), every rank joins."""
+        import torch
+        import torch.distributed as dist
+
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        buf = (ctypes.c_char * 128)()
+        if rank == 0 and self._L.qeb_nccl_unique_id(buf):
+            raise QebError("qeb_nccl_unique_id failed (libnccl not found? set QEB_NCCL_LIB)")
+        t = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+        on_gpu = dist.get_backend(group) == "nccl"
+        if on_gpu:
+            t = t.cuda()
+        src = dist.get_global_rank(group, 0) if group is not None else 0
+        dist.broadcast(t, src=src, group=group)
+        raw = bytes(t.cpu().numpy().tobytes())
+        self._ck(self._L.qeb_nccl_init(self._h, role, ctypes.c_char_p(raw), world, rank), "qeb_nccl_init")
 
     def set_kpoint(self, npw, npwx, igk, g2kin, vkb=None, nkb=0, gstart=1):
         igk = _i32(igk)

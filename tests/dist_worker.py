@@ -1,0 +1,87 @@
+"""Worker for the multi-GPU parity tests: one process per GPU (launched by torch.distributed.run), every rank
+holds its own rows of psi/vkb and its own z planes of V(r), runs the R&G-distributed h_psi through the C ABI and
+compares its rows with the serial CPU oracle. Also checks the band-group path (h_psi_bgrp + NCCL all-gather).
+Prints 'DIST_OK' from rank 0 when every rank agrees. usage: dist_worker.py CONFIG M"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import qe_b200  # noqa: E402
+from oracle import descriptor as D  # noqa: E402
+from oracle import dist as X  # noqa: E402
+from oracle import hpsi_ref as R  # noqa: E402
+
+TOL = 1e-11
+
+
+def setup_rank(h, d, dd, me, inp, pad):
+    rk = dd.ranks[me]
+    h.set_grid_dist(d.nr1, d.nr2, d.nr3, dd.nproc, me, dd.nr3p, dd.nsw, dd.iss, dd.ismap, rk.nl,
+                    rk.nlm if d.gamma_only else None, d.gamma_only)
+    n = inp["n"]
+    vkb_l = X.split_rows(dd, inp["vkb"][:, :n], pad=pad)[me]
+    lda = rk.npw + pad
+    h.set_kpoint(rk.npw, lda, None if d.gamma_only else rk.igk, rk.g2kin, vkb_l, vkb_l.shape[0], rk.gstart)
+    h.set_vloc(np.ascontiguousarray(X.v_slabs(dd, inp["vrs"])[me]).reshape(-1))
+    h.set_nonlocal(inp["nh_at"], inp["ofsbeta"], inp["deeq"])
+    return lda
+
+
+def main():
+    name, m = sys.argv[1], int(sys.argv[2])
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    d = D.config_descriptor(name)
+    nh = [8, 8, 8]
+    inp = R.synthetic_inputs(d, m, nh, seed=21, poison=False)
+    n = inp["n"]
+    ref, becp_ref = R.h_psi(d, inp["lda"], n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    ok = True
+    # ---- R&G distribution over all ranks ----
+    dd = X.distribute(d, world)
+    rk = dd.ranks[rank]
+    h = qe_b200.HPsi(device=local)
+    h.nccl_init(qe_b200.COMM_RG)
+    for batch in (0, 2):
+        if batch:
+            h.set_batch(batch)
+        lda = setup_rank(h, d, dd, rank, inp, pad=3)
+        psi_l = X.split_rows(dd, inp["psi"][:, :n], pad=3, fill=np.nan)[rank]
+        out = np.full((m, lda), np.nan + 1j * np.nan)
+        h.h_psi(lda, rk.npw, m, psi_l, out)
+        e1 = np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max() / np.abs(ref).max()
+        e2 = np.abs(h.get_becp(m) - becp_ref).max() / np.abs(becp_ref).max()
+        ok = ok and e1 < TOL and e2 < TOL and np.all(out[:, rk.npw:] == 0)
+        print(f"rank {rank} R&G batch={batch}: hpsi err {e1:.2e} becp err {e2:.2e}", flush=True)
+    h.close()
+    # ---- band groups: replicated data, column blocks, NCCL all-gather inside the library ----
+    hb = qe_b200.HPsi(device=local)
+    hb.nccl_init(qe_b200.COMM_BGRP)
+    hb.setup_from(d, inp)
+    psi_t = torch.from_numpy(np.nan_to_num(inp["psi"])).cuda()
+    out_t = torch.zeros_like(psi_t)
+    hb.h_psi_bgrp(inp["lda"], n, m, psi_t, out_t, world, rank)
+    torch.cuda.synchronize()
+    e3 = np.abs(out_t.cpu().numpy()[:, :n] - ref[:, :n]).max() / np.abs(ref).max()
+    ok = ok and e3 < TOL
+    print(f"rank {rank} band groups: hpsi err {e3:.2e}", flush=True)
+    hb.close()
+    t = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0 and int(t.item()) == 1:
+        print("DIST_OK", flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if int(t.item()) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -117,6 +117,7 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
     }
     t.vp = vp.data();
     t.g1_box = (size_t)H.nst * nr3;
+    t.g1_zs = (size_t)H.nst;
     t.g2_box = (size_t)H.nxw * t.npos;
     std::vector<cplx> g1(t.g1_box * batch), g2(t.g2_box * batch);
     t.g1 = g1.data(); t.g2 = g2.data();
