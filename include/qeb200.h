@@ -163,6 +163,43 @@ int qeb_set_grid_dist(qeb_ctx* ctx, int nr1, int nr2, int nr3, int nproc, int my
                       const int* iss, const int* ismap, int nismap, int ngm, const int* nl, const int* nlm,
                       int gamma_only);
 
+/* ---- host-side descriptor builder (no GPU needed) ------------------------ */
+/* For hosts that do not run the reference's own setup (benchmark, Python mirror, tests): the data of
+ * fft_type_init + ggen + fft_set_nl + gk_sort + g2_kin for one k-point, and the slab distribution of the grid.
+ *   grid dims     FFTXlib/src/fft_types.f90:1086-1197, fft_support.f90:61-165 (good_fft_order: factors 2,3,5)
+ *   G-vectors     Modules/recvec_subs.f90:111-258 (|G|^2 order with eps8 ties, Gamma half space, gstart)
+ *   nl / nlm      FFTXlib/src/fft_ggen.f90:28-108      igk / g2kin  PW/src/gk_sort.f90:9-98, g2_kin.f90:37-43
+ *   distribution  FFTXlib/src/stick_base.f90:214-601 + fft_types.f90:491-943 (slab; pencil is not built)
+ * at_cols: 3x3 row-major whose COLUMNS are a_1..a_3 in units of alat; xk in 2pi/alat (NULL = Gamma point);
+ * ecutrho <= 0 means 4*ecutwfc. Cutoffs in Ry, alat in bohr. */
+typedef struct qeb_desc qeb_desc;
+int qeb_good_fft_order(int nr);
+int qeb_desc_create(qeb_desc** d, const double* at_cols, double alat, double ecutwfc, double ecutrho,
+                    const double* xk, int gamma_only);
+int qeb_desc_destroy(qeb_desc* d);
+const char* qeb_desc_error(const qeb_desc* d);
+int qeb_desc_dims(const qeb_desc* d, int* nr1, int* nr2, int* nr3, int* ngm, int* npw, int* nst, int* gstart);
+/* slab distribution over nproc ranks; afterwards the per-rank arrays are available */
+int qeb_desc_distribute(qeb_desc* d, int nproc);
+int qeb_desc_rank_dims(const qeb_desc* d, int rank, int* ngm, int* npw, int* gstart, int* nismap);
+/* copies an array into `out` (caller-sized). rank < 0: the serial / global arrays; rank >= 0: that rank's. */
+#define QEB_DESC_NL 0      /* int[ngm]    1-based: serial x-fastest box index; rank: stick-major */
+#define QEB_DESC_NLM 1     /* int[ngm]    Gamma only */
+#define QEB_DESC_IGK 2     /* int[npw]    1-based into the (rank's) G list */
+#define QEB_DESC_G2KIN 3   /* double[npw] |k+G|^2 tpiba2 (Ry) */
+#define QEB_DESC_MILL 4    /* int[3*ngm]  Miller indices (global only) */
+#define QEB_DESC_GG 5      /* double[ngm] |G|^2 (global only) */
+#define QEB_DESC_ISIND 6   /* int[nr1*nr2] wave-stick mask of the serial descriptor */
+#define QEB_DESC_IPLW 7    /* int[nr1]    active x planes */
+#define QEB_DESC_NR3P 8    /* int[nproc] */
+#define QEB_DESC_NSW 9     /* int[nproc] */
+#define QEB_DESC_NSP 10    /* int[nproc] */
+#define QEB_DESC_ISS 11    /* int[nproc] */
+#define QEB_DESC_ISMAP 12  /* int[nismap] */
+#define QEB_DESC_IG_L2G 13 /* int[ngm_rank] 0-based index of the rank's G-vectors in the global list */
+#define QEB_DESC_PW_L2G 14 /* int[npw_rank] 0-based row of the serial psi holding the rank's plane waves */
+int qeb_desc_get(const qeb_desc* d, int what, int rank, void* out);
+
 /* ---- introspection for benchmarks / tests ------------------------------ */
 /* algorithmic HBM bytes per band of the V_loc path:
  * 16*(4*nst*nr3 + 4*nxw*nr2*nr3)[/2 Gamma] + 60*npw, and the table sizes */

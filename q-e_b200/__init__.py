@@ -8,3 +8,4 @@ context without a CUDA device raises.
 """
 from .hpsi import (COMM_BGRP, COMM_RG, HPsi, QebError, allgather_columns, divide_all, lib_path,  # noqa: F401
                    load_library)
+from . import descriptor  # noqa: F401,E402

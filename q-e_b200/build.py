@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libqeb200.so")
 BUILD = os.path.join(HERE, "build")
-SOURCES = ["context.cu", "vloc.cu", "gemm.cu", "fullfft.cu", "distfft.cu", "nccl_glue.cu"] + [
+SOURCES = ["context.cu", "vloc.cu", "gemm.cu", "fullfft.cu", "distfft.cu", "nccl_glue.cu", "descriptor.cu"] + [
     f"vloc_fast_{n}.cu" for n in (15, 25, 27, 64, 125, 135, 144, 200)]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
