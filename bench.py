@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="ausurf112")
     ap.add_argument("--bands", type=int, default=0, help="override m (default nbnd of the workload)")
-    ap.add_argument("--mode", default="pools", choices=["pools", "bgrp"])
+    ap.add_argument("--mode", default="pools", choices=["pools", "bgrp", "rg"])
     ap.add_argument("--cpu-sample-bands", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -102,16 +102,15 @@ class ClockSampler:
 # workload
 # ---------------------------------------------------------------------------
 def workload(name: str, seed: int = 0):
-    """descriptor + sizes from the restated grid rules (host setup, not timed)."""
-    from oracle import descriptor as D
+    """descriptor + sizes from the library's own descriptor builder (qeb_desc_*, host setup, not timed)."""
+    import qe_b200
 
-    c = dict(D.CONFIGS[name])
+    c = dict(qe_b200.descriptor.WORKLOADS[name])
     xk = np.array(c["xk"], dtype=float)
     if not c["gamma"] and seed:
         xk = xk + 0.01 * seed  # a different k-point per pool
-    d = D.build_descriptor(c["at"], c["alat"], c["ecutwfc"], xk=xk, gamma_only=c["gamma"], ecutrho=c["ecutrho"])
-    nh = c.get("nh_list") or [c["nh"]] * c["nat"]
-    return d, c, np.asarray(nh, dtype=np.int32)
+    d = qe_b200.descriptor.Descriptor(c["at"], c["alat"], c["ecutwfc"], c["ecutrho"], xk, c["gamma"])
+    return d, c, np.asarray(c["nh"], dtype=np.int32)
 
 
 def peaks():
@@ -211,25 +210,35 @@ def run_ours(args):
     dev = torch.device("cuda", local)
 
     pools = args.mode == "pools"
+    rg = args.mode == "rg"
     d, c, nh = workload(args.workload, seed=rank if pools else 0)
-    n = d.npw
-    lda = n
     m_total = args.bands or c["nbnd"]
     nkb = int(nh.sum())
-    if pools:
+    if rg:
+        # R&G: sticks / planes / plane waves of ONE k-point distributed over the ranks
+        d.distribute(world)
+        rk = d.ranks[rank]
+        n = rk.npw
+    else:
+        n = d.npw
+    lda = n
+    if pools or rg:
         m0, m1 = 0, m_total
     else:
         m0, m1 = qe_b200.divide_all(m_total, world, rank)
     m_loc = m1 - m0
 
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
-    psi = torch.randn((m_total, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(2 * n)
+    psi = torch.randn((m_total, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(2 * d.npw)
+    if d.gamma_only:
+        psi[:, 0, 1] = 0.0
     hpsi = torch.zeros_like(psi)
-    vkb = torch.randn((nkb, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(n)
+    vkb = torch.randn((nkb, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(d.npw)
+    if d.gamma_only:
+        vkb[:, 0, 1] = 0.0
     rng = np.random.default_rng(2234 + rank)
-    vrs = rng.uniform(-1.0, 0.0, d.nnr)
     nhm = int(nh.max())
-    deeq = rng.uniform(-1, 1, (len(nh), nhm, nhm))
+    deeq = np.random.default_rng(4234).uniform(-1, 1, (len(nh), nhm, nhm))
     deeq = 0.5 * (deeq + deeq.transpose(0, 2, 1))
     ofs = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
 
@@ -239,15 +248,23 @@ def run_ours(args):
     stream = tstream.cuda_stream
     assert stream != 0
     h = qe_b200.HPsi(device=local, stream=stream, batch=args.batch or None)
-    h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
-    h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
-    h.set_vloc(vrs)
+    if rg:
+        h.set_grid_dist(d.nr1, d.nr2, d.nr3, world, rank, d.nr3p, d.nsw, d.iss, d.ismap, rk.nl,
+                        rk.nlm if d.gamma_only else None, d.gamma_only)
+        if world > 1:
+            h.nccl_init(qe_b200.COMM_RG)
+        h.set_kpoint(n, lda, None if d.gamma_only else rk.igk, rk.g2kin, vkb, nkb, rk.gstart)
+        h.set_vloc(rng.uniform(-1.0, 0.0, d.nr1 * d.nr2 * int(d.nr3p[rank])))
+    else:
+        h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
+        h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
+        h.set_vloc(rng.uniform(-1.0, 0.0, d.nnr))
     h.set_nonlocal(nh, ofs, deeq)
     h.set_async(True)
     st = h.stats()
 
     def step():
-        if pools or world == 1:
+        if pools or rg or world == 1:
             h.h_psi(lda, n, m_total, psi, hpsi)
         else:
             h.h_psi_bgrp(lda, n, m_total, psi, hpsi, world, rank)
@@ -297,7 +314,7 @@ def run_ours(args):
         torch.cuda.synchronize()
         return a.elapsed_time(b) / reps
 
-    mm = m_total if pools else m_loc
+    mm = m_total if (pools or rg) else m_loc
     ms_vloc = time_section(lambda: (h.vloc_psi_gamma if d.gamma_only else h.vloc_psi_k)(lda, n, mm, psi, None, hpsi))
     ms_nl = time_section(lambda: h.nonlocal_only(lda, n, mm, psi, hpsi)) if nkb else 0.0
     peak, peak_src = peaks()
@@ -350,7 +367,7 @@ def run_ours(args):
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-        e2e = {"value": (mm * world if (pools or world == 1) else m_total) / dt, "unit": "band-applications/s",
+        e2e = {"value": (mm * world if pools else m_total) / dt, "unit": "band-applications/s",
                "h2d_bytes_per_step": int(mm * lda * 16), "d2h_bytes_per_step": int(mm * lda * 16),
                "ms_per_step": dt * 1e3}
         h.set_async(True)
@@ -361,7 +378,7 @@ def run_ours(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak" if pools else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "grid": [d.nr1, d.nr2, d.nr3], "npw": n, "bands_per_step": m_total,
-                       "nkb": nkb, "gamma_only": bool(d.gamma_only), "parallelism": ("k-pools" if pools else "band-groups") + f" x{world}",
+                       "nkb": nkb, "gamma_only": bool(d.gamma_only), "parallelism": {"pools": "k-pools", "bgrp": "band-groups", "rg": "R&G slab FFT"}[args.mode] + f" x{world}",
                        "vloc_batch_boxes": st["batch"], "l2": "inputs larger than L2 (psi+hpsi+vkb = %.1f GB)" % ((2 * m_total * lda * 16 + nkb * lda * 16) / 1e9)},
             "roofline": roofline,
             "roofline_vloc": roofline_vloc,

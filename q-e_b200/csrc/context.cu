@@ -892,7 +892,10 @@ int qeb_h_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
     if (m == 0) return 0;
     const size_t bytes = (size_t)lda * m * 16;
     const bool out_dev = is_device_ptr(hpsi);
-    if (!out_dev && !is_device_ptr(psi) && m >= c->pipeline_min_cols && (bytes >= ((size_t)8 << 20) || c->pipeline_chunk > 0))
+    // (distributed grids: the choice must not depend on the rank's own row count - every rank has to issue the same
+    // sequence of collectives)
+    if (!out_dev && !is_device_ptr(psi) && m >= c->pipeline_min_cols &&
+        (bytes >= ((size_t)8 << 20) || c->pipeline_chunk > 0 || c->dist))
         return h_psi_host_pipeline(c, lda, n, m, psi, hpsi);
     const void* psi_d;
     if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
@@ -1156,11 +1159,13 @@ int qeb_get_stats(qeb_ctx* c, double* vloc_bytes_per_band, double* gemm_flops_pe
     if (!c || !c->have_k) return 1;
     const HostVlocTables& H = c->H;
     double fftb = 16.0 * (4.0 * H.nst * H.nr3 + 4.0 * (double)H.nxw * H.nr2 * H.nr3);
+    if (c->dist)  // this rank's share: own sticks over all z, all active x planes over own z
+        fftb = 16.0 * (4.0 * H.nst * H.nr3 + 4.0 * (double)c->Hp.nxw * c->Hp.nr2 * c->Hp.nr3);
     if (c->gamma) fftb *= 0.5;
     if (vloc_bytes_per_band) *vloc_bytes_per_band = fftb + 60.0 * c->npw;
     if (gemm_flops_per_band) *gemm_flops_per_band = (c->gamma ? 8.0 : 16.0) * (double)c->nkb * c->npw;
     if (nst) *nst = H.nst;
-    if (nxw) *nxw = H.nxw;
+    if (nxw) *nxw = c->dist ? c->Hp.nxw : H.nxw;
     if (nboxes) *nboxes = c->batch;
     return 0;
 }
