@@ -189,7 +189,7 @@ def run_reference(args):
         "e2e": {"value": val, "unit": "band-applications/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -396,13 +396,28 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": m_s / dt, "unit": "band-applications/s", "cores": cores, "kind": kind,
                                     "sample": f"{m_s} bands of the same h_psi (V_loc: reference C FFT engine, OpenMP "
                                               f"over bands; projectors: OpenBLAS zgemm), {dt:.1f} s"}
-        print(json.dumps(line))
+        emit(line)
     h.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """the ONE JSON line, on the process's real stdout"""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
+    global _REAL_STDOUT
+    # libraries (NCCL prints its version banner on stdout) must not pollute the one-line contract: everything
+    # written to fd 1 while the benchmark runs goes to stderr, the JSON line goes to the saved stdout
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args = parse()
     if args.impl == "reference":
         run_reference(args)

@@ -513,10 +513,11 @@ static int size_workspaces(qeb_ctx* c)
     t.g2_box = (size_t)H.nxw * t.npos;
     int nb = c->batch_user;
     if (nb <= 0) {
-        // keep the G2 planes of the batches in flight L2-resident
-        const size_t target = ((size_t)56 << 20) / c->vloc_nstreams;
+        // enough boxes per launch to fill the SMs (measured on B200, tools/vloc_sweep.py: throughput saturates from
+        // ~8 boxes of a large grid; keeping the planes L2-resident matters less than filling the machine)
+        const size_t target = (size_t)192 << 20;
         nb = (int)(target / (t.g2_box * 16 + 1));
-        if (nb < 1) nb = 1;
+        if (nb < 8) nb = 8;
         if (nb > 64) nb = 64;
     }
     c->batch = nb;
@@ -541,16 +542,19 @@ static int size_workspaces_dist(qeb_ctx* c)
     tp.g2_box = (size_t)tp.nxw * tp.npos;
     int nb = c->batch_user;
     if (nb <= 0) {
-        const size_t target = (size_t)48 << 20;
+        // enough boxes per launch to fill the SMs (measured: throughput saturates from ~8 boxes of a large grid,
+        // L2 residency of the planes matters less), bounded by workspace memory
+        const size_t target = (size_t)192 << 20;
         nb = (int)(target / (tp.g2_box * 16 + 1));
-        if (nb < 1) nb = 1;
+        if (nb < 8) nb = 8;
         if (nb > 64) nb = 64;
     }
     c->batch = nb;
-    QEB_CUDA(c, c->sbuf_d.ensure(std::max<size_t>(16, nst_me * c->nr3 * 16 * nb)));
-    QEB_CUDA(c, c->rbuf_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb)));
-    QEB_CUDA(c, c->g1_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb)));
-    QEB_CUDA(c, c->g2_d.ensure(std::max<size_t>(16, tp.g2_box * 16 * nb)));
+    const size_t ns = (size_t)c->vloc_nstreams;
+    QEB_CUDA(c, c->sbuf_d.ensure(std::max<size_t>(16, nst_me * c->nr3 * 16 * nb * ns)));
+    QEB_CUDA(c, c->rbuf_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb * ns)));
+    QEB_CUDA(c, c->g1_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb * ns)));
+    QEB_CUDA(c, c->g2_d.ensure(std::max<size_t>(16, tp.g2_box * 16 * nb * ns)));
     tz.g1 = (cplx*)c->sbuf_d.p;
     tz.g2 = nullptr;
     tz.g1_box = nst_me;  // [z][box][stick]: see VlocTables::g1_zs
@@ -685,22 +689,44 @@ static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hp
         // cft_1z | fft_scatter | cft_2xy * V * cft_2xy | fft_scatter | cft_1z  (fft_parallel_2d.f90:36-204)
         const DistHost& D = c->DH;
         if (D.nproc > 1 && !c->nccl_rg) QEB_FAIL(c, 53, "V_loc: no NCCL communicator for the R&G group (qeb_nccl_init)");
-        cplx* S = (cplx*)c->sbuf_d.p;
-        cplx* R = (cplx*)c->rbuf_d.p;
-        for (int b0 = 0; b0 < nboxes; b0 += c->batch) {
+        // batches alternate between the V_loc streams (own S/R/G1/G2 slices): the exchange of one batch overlaps
+        // the FFT passes of the other. Every rank issues the collectives in the same order.
+        const int nbatches_d = (nboxes + c->batch - 1) / c->batch;
+        const int nsd = std::min(c->vloc_nstreams, nbatches_d);
+        if (nsd > 1) {
+            QEB_CUDA(c, cudaEventRecord(c->vev[0], c->stream));
+            for (int s = 1; s < nsd; ++s) QEB_CUDA(c, cudaStreamWaitEvent(c->vstream[s], c->vev[0], 0));
+        }
+        const size_t s_slice = (size_t)D.nsw[D.me] * c->nr3 * c->batch;
+        const size_t r_slice = c->Tp.g1_box * c->batch;
+        const size_t g2_slice = c->Tp.g2_box * c->batch;
+        int ib = 0;
+        for (int b0 = 0; b0 < nboxes; b0 += c->batch, ++ib) {
             const int nb = std::min(c->batch, nboxes - b0);
+            const int si = ib % nsd;
+            cudaStream_t st = si == 0 ? c->stream : c->vstream[si];
+            cplx* S = (cplx*)c->sbuf_d.p + si * s_slice;
+            cplx* R = (cplx*)c->rbuf_d.p + si * r_slice;
             io.band0 = c->gamma ? 2 * b0 : b0;
             VlocTables tz = c->T;
+            tz.g1 = S;
             tz.g1_zs = (size_t)nb * tz.g1_box;
+            VlocTables tp = c->Tp;
+            tp.g1 += si * r_slice;
+            tp.g2 += si * g2_slice;
             const char* msg = "";
             int rc;
-            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, c->stream));
-            if ((rc = dist_exchange(D, c->nccl_rg, true, S, R, nb, c->stream, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-            QEB_CUDA(c, dist_unpack(c->DD, R, c->Tp.g1, nb, c->stream));
-            QEB_CUDA(c, vloc_launch_planes(c->Tp, c->cfgp, nb, c->stream));
-            QEB_CUDA(c, dist_pack(c->DD, c->Tp.g1, R, nb, c->stream));
-            if ((rc = dist_exchange(D, c->nccl_rg, false, S, R, nb, c->stream, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-            QEB_CUDA(c, vloc_launch_zpass(false, tz, io, c->cfg, nb, c->stream));
+            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
+            if ((rc = dist_exchange(D, c->nccl_rg, true, S, R, nb, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            QEB_CUDA(c, dist_unpack(c->DD, R, tp.g1, nb, st));
+            QEB_CUDA(c, vloc_launch_planes(tp, c->cfgp, nb, st));
+            QEB_CUDA(c, dist_pack(c->DD, tp.g1, R, nb, st));
+            if ((rc = dist_exchange(D, c->nccl_rg, false, S, R, nb, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            QEB_CUDA(c, vloc_launch_zpass(false, tz, io, c->cfg, nb, st));
+        }
+        for (int s = 1; s < nsd; ++s) {
+            QEB_CUDA(c, cudaEventRecord(c->vev[s], c->vstream[s]));
+            QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->vev[s], 0));
         }
         return 0;
     }

@@ -1,7 +1,7 @@
 #!/bin/bash
 # per-kernel average durations (ncu, serialised): usage tools/klist.sh TAG [env...]
 T=$1; shift
-env "$@" ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_kl.csv python tools/prof_run.py --bands 32 --calls 2 > /dev/null 2>&1
+env "$@" ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_kl.csv python tools/prof_run.py --bands ${KL_BANDS:-32} --calls 2 $KL_ARGS > /dev/null 2>&1
 python - <<PY
 import csv,collections
 rows=[r for r in csv.reader(open('gpurun_out/${T}_kl.csv')) if len(r)>10 and r[0].isdigit()]

@@ -17,6 +17,7 @@ ap.add_argument("--workload", default="ausurf112")
 ap.add_argument("--bands", type=int, default=64)
 ap.add_argument("--calls", type=int, default=2)
 ap.add_argument("--batch", type=int, default=0)
+ap.add_argument("--mode", default="serial", choices=["serial", "rg"])
 a = ap.parse_args()
 d, c, nh = workload(a.workload)
 n = lda = d.npw
@@ -31,8 +32,15 @@ nhm = int(nh.max())
 deeq = rng.uniform(-1, 1, (len(nh), nhm, nhm))
 ofs = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
 h = qe_b200.HPsi(batch=a.batch or None)
-h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
-h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
+if a.mode == "rg":  # the slab-distributed code path on one rank (exchange = device copy)
+    d.distribute(1)
+    rk = d.ranks[0]
+    h.set_grid_dist(d.nr1, d.nr2, d.nr3, 1, 0, d.nr3p, d.nsw, d.iss, d.ismap, rk.nl, rk.nlm if d.gamma_only else None,
+                    d.gamma_only)
+    h.set_kpoint(n, lda, None if d.gamma_only else rk.igk, rk.g2kin, vkb, nkb, rk.gstart)
+else:
+    h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
+    h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
 h.set_vloc(rng.uniform(-1, 0, d.nnr))
 h.set_nonlocal(nh, ofs, deeq)
 for _ in range(a.calls):
