@@ -13,6 +13,7 @@
 // multi-stage pipeline, split-K with a fixed-order reduction (deterministic).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "gemm.h"
 
@@ -173,6 +174,123 @@ k_calbec(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi, i
                     if (j < m) P[(sbase + j) * nkb + i] = acc[mi][nj][e];
                 }
         }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// calbec, complex case, 3-multiplication form. With a = vkb(g,i), b = psi(g,j):
+//   P1 = sum ar*br, P2 = sum ai*bi, P3 = sum (ar+ai)*(bi-br)
+//   Re <a|b> = P1 + P2,   Im <a|b> = P3 + P1 - P2
+// i.e. three real MMAs per complex multiply-add instead of four (25 % fewer DMMA). The MMA K index is the complex
+// G-vector; each thread reads its fragment elements as one 16-byte complex and forms the sums in registers. The
+// result differs from the 4-multiplication form only by rounding (normwise error ~ eps*sqrt(K)*|a||b|, far below
+// the 1e-11 parity bound). CTA tile 128 projectors x 48 bands, warp tile 32 x 24, 8 warps (4 x 2).
+// ---------------------------------------------------------------------------
+constexpr int C3_MT = 128;
+constexpr int C3_NT = 48;
+constexpr int C3_KG = 16;        // complex G-vectors per stage
+constexpr int C3_LD = 20;        // complex per smem row: 16 + 4 pad (row stride = 4 mod 8 sixteen-byte banks)
+constexpr int C3_STAGES = 3;
+constexpr size_t C3_STAGE_CPLX = (size_t)(C3_MT + C3_NT) * C3_LD;
+constexpr size_t C3_SMEM = C3_STAGE_CPLX * 16 * C3_STAGES;
+
+__global__ void __launch_bounds__(256, 1)
+k_calbec3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi, int lda, int n, int nkb, int m,
+           int gchunk, cplx* __restrict__ part)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 3, wn = warp >> 2;
+    const int r = lane >> 2, k = lane & 3;
+    const int i0 = blockIdx.x * C3_MT, j0 = blockIdx.y * C3_NT;
+    const int g_beg = blockIdx.z * gchunk;
+    const int g_end = min(n, g_beg + gchunk);
+    const int nkt = (g_end - g_beg + C3_KG - 1) / C3_KG;
+
+    double p1[4][3][2], p2[4][3][2], p3[4][3][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) p1[a][b][e] = p2[a][b][e] = p3[a][b][e] = 0.0;
+
+    auto load_stage = [&](int st, int kt) {
+        cplx* As = sm + (size_t)st * C3_STAGE_CPLX;
+        cplx* Bs = As + (size_t)C3_MT * C3_LD;
+        const int g0 = g_beg + kt * C3_KG;
+#pragma unroll
+        for (int it = 0; it < C3_MT * C3_KG / 256; ++it) {
+            const int c = tid + it * 256;
+            const int row = c >> 4, cc = c & 15;
+            const bool ok = (i0 + row < nkb) && (g0 + cc < g_end) && kt < nkt;
+            const cplx* src = ok ? vkb + (size_t)(i0 + row) * npwx + g0 + cc : vkb;
+            cp_async16(As + row * C3_LD + cc, src, ok);
+        }
+#pragma unroll
+        for (int it = 0; it < C3_NT * C3_KG / 256; ++it) {
+            const int c = tid + it * 256;
+            const int row = c >> 4, cc = c & 15;
+            const bool ok = (j0 + row < m) && (g0 + cc < g_end) && kt < nkt;
+            const cplx* src = ok ? psi + (size_t)(j0 + row) * lda + g0 + cc : psi;
+            cp_async16(Bs + row * C3_LD + cc, src, ok);
+        }
+    };
+
+#pragma unroll
+    for (int s = 0; s < C3_STAGES - 1; ++s) {
+        load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nkt; ++kt) {
+        cp_async_wait<C3_STAGES - 2>();
+        __syncthreads();
+        load_stage((kt + C3_STAGES - 1) % C3_STAGES, kt + C3_STAGES - 1);
+        cp_async_commit();
+        const cplx* As = sm + (size_t)(kt % C3_STAGES) * C3_STAGE_CPLX;
+        const cplx* Bs = As + (size_t)C3_MT * C3_LD;
+        const cplx* Aw = As + (size_t)(wm * 32 + r) * C3_LD + k;
+        const cplx* Bw = Bs + (size_t)(wn * 24 + r) * C3_LD + k;
+#pragma unroll
+        for (int kk = 0; kk < C3_KG; kk += 4) {
+            double ar[4], ai[4], as[4];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi) {
+                const cplx a = Aw[(size_t)mi * 8 * C3_LD + kk];
+                ar[mi] = a.x;
+                ai[mi] = a.y;
+                as[mi] = a.x + a.y;
+            }
+#pragma unroll
+            for (int nj = 0; nj < 3; ++nj) {
+                const cplx b = Bw[(size_t)nj * 8 * C3_LD + kk];
+                const double bd = b.y - b.x;
+#pragma unroll
+                for (int mi = 0; mi < 4; ++mi) {
+                    dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], b.x);
+                    dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], b.y);
+                    dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bd);
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+    // partials: part[s][j][i]
+    const size_t sbase = (size_t)blockIdx.z * m;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi) {
+        const int i = i0 + wm * 32 + mi * 8 + r;
+        if (i >= nkb) continue;
+#pragma unroll
+        for (int nj = 0; nj < 3; ++nj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int j = j0 + wn * 24 + nj * 8 + 2 * k + e;
+                if (j < m)
+                    part[(sbase + j) * nkb + i] =
+                        mk(p1[mi][nj][e] + p2[mi][nj][e], p3[mi][nj][e] + (p1[mi][nj][e] - p2[mi][nj][e]));
+            }
     }
 }
 
@@ -369,6 +487,124 @@ k_addvus(const cplx* __restrict__ vkb, int npwx, const void* __restrict__ ps_, i
     }
 }
 
+// ---------------------------------------------------------------------------
+// add_vuspsi, complex case, 3-multiplication form. With p = ps(i,j), v = vkb(g,i):
+//   P1 = sum pr*vr, P2 = sum pi*vi, P3 = sum (pr+pi)*(vr+vi)
+//   Re (v p) = P1 - P2,   Im (v p) = P3 - P1 - P2
+// MMA-M = bands, MMA-N = G-vectors, MMA-K = projectors (all complex indices; fragments are 16-byte complex loads).
+// CTA tile 64 bands x 96 G-vectors, warp tile 32 x 24, 8 warps (2 x 4).
+// ---------------------------------------------------------------------------
+constexpr int A3_BT = 64;
+constexpr int A3_GT = 96;
+constexpr int A3_KI = 16;        // projectors per stage
+constexpr int A3_LDP = 20;       // complex per ps row (16 + 4 pad)
+constexpr int A3_LDV = 98;       // complex per vkb row (96 + 2 pad: row stride = 2 mod 8 sixteen-byte banks)
+constexpr int A3_STAGES = 4;
+constexpr size_t A3_STAGE_CPLX = (size_t)A3_BT * A3_LDP + (size_t)A3_KI * A3_LDV;
+constexpr size_t A3_SMEM = A3_STAGE_CPLX * 16 * A3_STAGES;
+
+__global__ void __launch_bounds__(256, 1)
+k_addvus3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ ps, int ldps, int n, int nkb, int m,
+           cplx* __restrict__ hpsi, int lda)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 1, wn = warp >> 1;
+    const int r = lane >> 2, k = lane & 3;
+    const int j0 = blockIdx.x * A3_BT, g0 = blockIdx.y * A3_GT;
+    const int nkt = (nkb + A3_KI - 1) / A3_KI;
+
+    double p1[4][3][2], p2[4][3][2], p3[4][3][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) p1[a][b][e] = p2[a][b][e] = p3[a][b][e] = 0.0;
+
+    auto load_stage = [&](int st, int kt) {
+        cplx* Ps = sm + (size_t)st * A3_STAGE_CPLX;
+        cplx* Vs = Ps + (size_t)A3_BT * A3_LDP;
+        const int ib = kt * A3_KI;
+        // ps tile: 64 bands x 16 projectors
+#pragma unroll
+        for (int it = 0; it < A3_BT * A3_KI / 256; ++it) {
+            const int c = tid + it * 256;
+            const int row = c >> 4, cc = c & 15;
+            const bool ok = (j0 + row < m) && (ib + cc < nkb) && kt < nkt;
+            const cplx* src = ok ? ps + (size_t)(j0 + row) * ldps + ib + cc : ps;
+            cp_async16(Ps + row * A3_LDP + cc, src, ok);
+        }
+        // vkb tile: 16 projectors x 96 G-vectors
+#pragma unroll
+        for (int it = 0; it < A3_KI * A3_GT / 256; ++it) {
+            const int c = tid + it * 256;
+            const int row = c / A3_GT, cc = c - row * A3_GT;
+            const bool ok = (ib + row < nkb) && (g0 + cc < n) && kt < nkt;
+            const cplx* src = ok ? vkb + (size_t)(ib + row) * npwx + g0 + cc : vkb;
+            cp_async16(Vs + row * A3_LDV + cc, src, ok);
+        }
+    };
+
+#pragma unroll
+    for (int s = 0; s < A3_STAGES - 1; ++s) {
+        load_stage(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nkt; ++kt) {
+        cp_async_wait<A3_STAGES - 2>();
+        __syncthreads();
+        load_stage((kt + A3_STAGES - 1) % A3_STAGES, kt + A3_STAGES - 1);
+        cp_async_commit();
+        const cplx* Ps = sm + (size_t)(kt % A3_STAGES) * A3_STAGE_CPLX;
+        const cplx* Vs = Ps + (size_t)A3_BT * A3_LDP;
+        const cplx* Aw = Ps + (size_t)(wm * 32 + r) * A3_LDP + k;   // A[band][i]
+        const cplx* Bw = Vs + (size_t)k * A3_LDV + wn * 24 + r;     // B[i][g]
+#pragma unroll
+        for (int kk = 0; kk < A3_KI; kk += 4) {
+            double ar[4], ai[4], as[4];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi) {
+                const cplx a = Aw[(size_t)mi * 8 * A3_LDP + kk];
+                ar[mi] = a.x;
+                ai[mi] = a.y;
+                as[mi] = a.x + a.y;
+            }
+#pragma unroll
+            for (int nj = 0; nj < 3; ++nj) {
+                const cplx b = Bw[(size_t)kk * A3_LDV + nj * 8];
+                const double bs = b.x + b.y;
+#pragma unroll
+                for (int mi = 0; mi < 4; ++mi) {
+                    dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], b.x);
+                    dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], b.y);
+                    dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bs);
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi) {
+        const int j = j0 + wm * 32 + mi * 8 + r;
+        if (j >= m) continue;
+#pragma unroll
+        for (int nj = 0; nj < 3; ++nj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int g = g0 + wn * 24 + nj * 8 + 2 * k + e;
+                if (g < n) {
+                    cplx* h = hpsi + (size_t)j * lda + g;
+                    const cplx o = *h;
+                    const double re = p1[mi][nj][e] - p2[mi][nj][e];
+                    const double im = p3[mi][nj][e] - (p1[mi][nj][e] + p2[mi][nj][e]);
+                    *h = mk(o.x + re, o.y + im);
+                }
+            }
+    }
+}
+
 // Gamma: Im hpsi(G=0) = 0 (h_psi.f90:294-295)
 __global__ void k_zero_im_g0(cplx* hpsi, int lda, int m)
 {
@@ -380,6 +616,7 @@ __global__ void k_zero_im_g0(cplx* hpsi, int lda, int m)
 // host launchers
 // ---------------------------------------------------------------------------
 static int g_smem_set = 0;
+static bool g_use_3m = true;  // complex projector GEMMs in the 3-multiplication form (QEB_GEMM_4M=1: the 4-mult kernels)
 static cudaError_t set_smem_attrs()
 {
     if (g_smem_set) return cudaSuccess;
@@ -388,13 +625,16 @@ static cudaError_t set_smem_attrs()
     if ((e = cudaFuncSetAttribute(k_calbec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CbCfg<false>::smem))) return e;
     if ((e = cudaFuncSetAttribute(k_addvus<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AvCfg<true>::smem))) return e;
     if ((e = cudaFuncSetAttribute(k_addvus<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AvCfg<false>::smem))) return e;
+    if ((e = cudaFuncSetAttribute(k_calbec3m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM))) return e;
+    if ((e = cudaFuncSetAttribute(k_addvus3m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A3_SMEM))) return e;
+    if (const char* v = getenv("QEB_GEMM_4M")) g_use_3m = atoi(v) == 0;
     g_smem_set = 1;
     return cudaSuccess;
 }
 
 void calbec_plan(int n, int nkb, int m, bool cplx_mode, int num_sms, int* nsplit, int* gchunk)
 {
-    const int NT = cplx_mode ? 64 : 128;
+    const int NT = cplx_mode ? (g_use_3m ? C3_NT : 64) : 128;
     const long tiles = (long)((nkb + CB_MT - 1) / CB_MT) * ((m + NT - 1) / NT);
     const int max_split = 64;
     // each split handles >= 256 G-vectors (16 k-tiles); pick the split count
@@ -435,9 +675,11 @@ cudaError_t launch_calbec(const cplx* vkb, int npwx, const cplx* psi, int lda, i
     cudaError_t e = set_smem_attrs();
     if (e) return e;
     if (nkb <= 0 || m <= 0) return cudaSuccess;
-    const int NT = cplx_mode ? 64 : 128;
+    const int NT = cplx_mode ? (g_use_3m ? C3_NT : 64) : 128;
     dim3 grid((nkb + CB_MT - 1) / CB_MT, (m + NT - 1) / NT, nsplit);
-    if (cplx_mode)
+    if (cplx_mode && g_use_3m)
+        k_calbec3m<<<grid, 256, C3_SMEM, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, (cplx*)part);
+    else if (cplx_mode)
         k_calbec<true><<<grid, 256, CbCfg<true>::smem, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, part);
     else
         k_calbec<false><<<grid, 256, CbCfg<false>::smem, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, part);
@@ -472,7 +714,10 @@ cudaError_t launch_addvus(const cplx* vkb, int npwx, const void* ps, int ldps, i
     if (e) return e;
     if (nkb <= 0 || m <= 0 || n <= 0) return cudaSuccess;
     dim3 grid((m + AV_BT - 1) / AV_BT, (n + AV_GT - 1) / AV_GT);
-    if (cplx_mode)
+    if (cplx_mode && g_use_3m) {
+        dim3 grid3((m + A3_BT - 1) / A3_BT, (n + A3_GT - 1) / A3_GT);
+        k_addvus3m<<<grid3, 256, A3_SMEM, st>>>(vkb, npwx, (const cplx*)ps, ldps, n, nkb, m, hpsi, lda);
+    } else if (cplx_mode)
         k_addvus<true><<<grid, 256, AvCfg<true>::smem, st>>>(vkb, npwx, ps, ldps, n, nkb, m, hpsi, lda);
     else
         k_addvus<false><<<grid, 256, AvCfg<false>::smem, st>>>(vkb, npwx, ps, ldps, n, nkb, m, hpsi, lda);
