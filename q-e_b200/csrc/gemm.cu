@@ -194,23 +194,25 @@ constexpr int C3_STAGES = 3;
 constexpr size_t C3_STAGE_CPLX = (size_t)(C3_MT + C3_NT) * C3_LD;
 constexpr size_t C3_SMEM = C3_STAGE_CPLX * 16 * C3_STAGES;
 
-__global__ void __launch_bounds__(256, 1)
+template <int MI>  // 8-row MMA blocks per warp: 4 -> 8 warps (4 x 2), 2 -> 16 warps (8 x 2)
+__global__ void __launch_bounds__(1024 / MI, 1)
 k_calbec3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi, int lda, int n, int nkb, int m,
            int gchunk, cplx* __restrict__ part)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cplx* sm = reinterpret_cast<cplx*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp & 3, wn = warp >> 2;
+    constexpr int NTHR = 1024 / MI, WM = 16 / MI;  // warps along the projector dimension
+    const int wm = warp % WM, wn = warp / WM;
     const int r = lane >> 2, k = lane & 3;
     const int i0 = blockIdx.x * C3_MT, j0 = blockIdx.y * C3_NT;
     const int g_beg = blockIdx.z * gchunk;
     const int g_end = min(n, g_beg + gchunk);
     const int nkt = (g_end - g_beg + C3_KG - 1) / C3_KG;
 
-    double p1[4][3][2], p2[4][3][2], p3[4][3][2];
+    double p1[MI][3][2], p2[MI][3][2], p3[MI][3][2];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < MI; ++a)
 #pragma unroll
         for (int b = 0; b < 3; ++b)
 #pragma unroll
@@ -221,16 +223,17 @@ k_calbec3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi,
         cplx* Bs = As + (size_t)C3_MT * C3_LD;
         const int g0 = g_beg + kt * C3_KG;
 #pragma unroll
-        for (int it = 0; it < C3_MT * C3_KG / 256; ++it) {
-            const int c = tid + it * 256;
+        for (int it = 0; it < C3_MT * C3_KG / NTHR; ++it) {
+            const int c = tid + it * NTHR;
             const int row = c >> 4, cc = c & 15;
             const bool ok = (i0 + row < nkb) && (g0 + cc < g_end) && kt < nkt;
             const cplx* src = ok ? vkb + (size_t)(i0 + row) * npwx + g0 + cc : vkb;
             cp_async16(As + row * C3_LD + cc, src, ok);
         }
 #pragma unroll
-        for (int it = 0; it < C3_NT * C3_KG / 256; ++it) {
-            const int c = tid + it * 256;
+        for (int it = 0; it < (C3_NT * C3_KG + NTHR - 1) / NTHR; ++it) {
+            const int c = tid + it * NTHR;
+            if (c >= C3_NT * C3_KG) break;
             const int row = c >> 4, cc = c & 15;
             const bool ok = (j0 + row < m) && (g0 + cc < g_end) && kt < nkt;
             const cplx* src = ok ? psi + (size_t)(j0 + row) * lda + g0 + cc : psi;
@@ -250,37 +253,46 @@ k_calbec3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi,
         cp_async_commit();
         const cplx* As = sm + (size_t)(kt % C3_STAGES) * C3_STAGE_CPLX;
         const cplx* Bs = As + (size_t)C3_MT * C3_LD;
-        const cplx* Aw = As + (size_t)(wm * 32 + r) * C3_LD + k;
+        const cplx* Aw = As + (size_t)(wm * 8 * MI + r) * C3_LD + k;
         const cplx* Bw = Bs + (size_t)(wn * 24 + r) * C3_LD + k;
 #pragma unroll
         for (int kk = 0; kk < C3_KG; kk += 4) {
-            double ar[4], ai[4], as[4];
+            double ar[MI], ai[MI], as[MI];
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi) {
+            for (int mi = 0; mi < MI; ++mi) {
                 const cplx a = Aw[(size_t)mi * 8 * C3_LD + kk];
                 ar[mi] = a.x;
                 ai[mi] = a.y;
                 as[mi] = a.x + a.y;
             }
+            // the sums are issued first and consumed last (P3), so the DMMAs of P1/P2 cover their latency
+            double br[3], bi[3], bd[3];
 #pragma unroll
             for (int nj = 0; nj < 3; ++nj) {
                 const cplx b = Bw[(size_t)nj * 8 * C3_LD + kk];
-                const double bd = b.y - b.x;
-#pragma unroll
-                for (int mi = 0; mi < 4; ++mi) {
-                    dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], b.x);
-                    dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], b.y);
-                    dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bd);
-                }
+                br[nj] = b.x;
+                bi[nj] = b.y;
+                bd[nj] = b.y - b.x;
             }
+#pragma unroll
+            for (int nj = 0; nj < 3; ++nj)
+#pragma unroll
+                for (int mi = 0; mi < MI; ++mi) {
+                    dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], br[nj]);
+                    dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], bi[nj]);
+                }
+#pragma unroll
+            for (int nj = 0; nj < 3; ++nj)
+#pragma unroll
+                for (int mi = 0; mi < MI; ++mi) dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bd[nj]);
         }
     }
     cp_async_wait<0>();
     // partials: part[s][j][i]
     const size_t sbase = (size_t)blockIdx.z * m;
 #pragma unroll
-    for (int mi = 0; mi < 4; ++mi) {
-        const int i = i0 + wm * 32 + mi * 8 + r;
+    for (int mi = 0; mi < MI; ++mi) {
+        const int i = i0 + wm * 8 * MI + mi * 8 + r;
         if (i >= nkb) continue;
 #pragma unroll
         for (int nj = 0; nj < 3; ++nj)
@@ -503,21 +515,23 @@ constexpr int A3_STAGES = 4;
 constexpr size_t A3_STAGE_CPLX = (size_t)A3_BT * A3_LDP + (size_t)A3_KI * A3_LDV;
 constexpr size_t A3_SMEM = A3_STAGE_CPLX * 16 * A3_STAGES;
 
-__global__ void __launch_bounds__(256, 1)
+template <int MI>  // 4 -> 8 warps (2 x 4), 2 -> 16 warps (4 x 4)
+__global__ void __launch_bounds__(1024 / MI, 1)
 k_addvus3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ ps, int ldps, int n, int nkb, int m,
            cplx* __restrict__ hpsi, int lda)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cplx* sm = reinterpret_cast<cplx*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp & 1, wn = warp >> 1;
+    constexpr int NTHR = 1024 / MI, WM = 8 / MI;  // warps along the band dimension
+    const int wm = warp % WM, wn = warp / WM;
     const int r = lane >> 2, k = lane & 3;
     const int j0 = blockIdx.x * A3_BT, g0 = blockIdx.y * A3_GT;
     const int nkt = (nkb + A3_KI - 1) / A3_KI;
 
-    double p1[4][3][2], p2[4][3][2], p3[4][3][2];
+    double p1[MI][3][2], p2[MI][3][2], p3[MI][3][2];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < MI; ++a)
 #pragma unroll
         for (int b = 0; b < 3; ++b)
 #pragma unroll
@@ -529,8 +543,8 @@ k_addvus3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ ps, 
         const int ib = kt * A3_KI;
         // ps tile: 64 bands x 16 projectors
 #pragma unroll
-        for (int it = 0; it < A3_BT * A3_KI / 256; ++it) {
-            const int c = tid + it * 256;
+        for (int it = 0; it < A3_BT * A3_KI / NTHR; ++it) {
+            const int c = tid + it * NTHR;
             const int row = c >> 4, cc = c & 15;
             const bool ok = (j0 + row < m) && (ib + cc < nkb) && kt < nkt;
             const cplx* src = ok ? ps + (size_t)(j0 + row) * ldps + ib + cc : ps;
@@ -538,8 +552,8 @@ k_addvus3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ ps, 
         }
         // vkb tile: 16 projectors x 96 G-vectors
 #pragma unroll
-        for (int it = 0; it < A3_KI * A3_GT / 256; ++it) {
-            const int c = tid + it * 256;
+        for (int it = 0; it < A3_KI * A3_GT / NTHR; ++it) {
+            const int c = tid + it * NTHR;
             const int row = c / A3_GT, cc = c - row * A3_GT;
             const bool ok = (ib + row < nkb) && (g0 + cc < n) && kt < nkt;
             const cplx* src = ok ? vkb + (size_t)(ib + row) * npwx + g0 + cc : vkb;
@@ -559,35 +573,43 @@ k_addvus3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ ps, 
         cp_async_commit();
         const cplx* Ps = sm + (size_t)(kt % A3_STAGES) * A3_STAGE_CPLX;
         const cplx* Vs = Ps + (size_t)A3_BT * A3_LDP;
-        const cplx* Aw = Ps + (size_t)(wm * 32 + r) * A3_LDP + k;   // A[band][i]
+        const cplx* Aw = Ps + (size_t)(wm * 8 * MI + r) * A3_LDP + k;   // A[band][i]
         const cplx* Bw = Vs + (size_t)k * A3_LDV + wn * 24 + r;     // B[i][g]
 #pragma unroll
         for (int kk = 0; kk < A3_KI; kk += 4) {
-            double ar[4], ai[4], as[4];
+            double ar[MI], ai[MI], as[MI];
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi) {
+            for (int mi = 0; mi < MI; ++mi) {
                 const cplx a = Aw[(size_t)mi * 8 * A3_LDP + kk];
                 ar[mi] = a.x;
                 ai[mi] = a.y;
                 as[mi] = a.x + a.y;
             }
+            double br[3], bi[3], bs[3];
 #pragma unroll
             for (int nj = 0; nj < 3; ++nj) {
                 const cplx b = Bw[(size_t)kk * A3_LDV + nj * 8];
-                const double bs = b.x + b.y;
-#pragma unroll
-                for (int mi = 0; mi < 4; ++mi) {
-                    dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], b.x);
-                    dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], b.y);
-                    dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bs);
-                }
+                br[nj] = b.x;
+                bi[nj] = b.y;
+                bs[nj] = b.x + b.y;
             }
+#pragma unroll
+            for (int nj = 0; nj < 3; ++nj)
+#pragma unroll
+                for (int mi = 0; mi < MI; ++mi) {
+                    dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], br[nj]);
+                    dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], bi[nj]);
+                }
+#pragma unroll
+            for (int nj = 0; nj < 3; ++nj)
+#pragma unroll
+                for (int mi = 0; mi < MI; ++mi) dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bs[nj]);
         }
     }
     cp_async_wait<0>();
 #pragma unroll
-    for (int mi = 0; mi < 4; ++mi) {
-        const int j = j0 + wm * 32 + mi * 8 + r;
+    for (int mi = 0; mi < MI; ++mi) {
+        const int j = j0 + wm * 8 * MI + mi * 8 + r;
         if (j >= m) continue;
 #pragma unroll
         for (int nj = 0; nj < 3; ++nj)
@@ -616,6 +638,7 @@ __global__ void k_zero_im_g0(cplx* hpsi, int lda, int m)
 // host launchers
 // ---------------------------------------------------------------------------
 static int g_smem_set = 0;
+static int g_3m_warps = 8;  // measured on B200: 8 warps (warp tile 32x24) 63.3 ms, 16 warps (16x24) 65.2 ms per AUSURF112 call
 static bool g_use_3m = true;  // complex projector GEMMs in the 3-multiplication form (QEB_GEMM_4M=1: the 4-mult kernels)
 static cudaError_t set_smem_attrs()
 {
@@ -625,8 +648,11 @@ static cudaError_t set_smem_attrs()
     if ((e = cudaFuncSetAttribute(k_calbec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CbCfg<false>::smem))) return e;
     if ((e = cudaFuncSetAttribute(k_addvus<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AvCfg<true>::smem))) return e;
     if ((e = cudaFuncSetAttribute(k_addvus<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AvCfg<false>::smem))) return e;
-    if ((e = cudaFuncSetAttribute(k_calbec3m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM))) return e;
-    if ((e = cudaFuncSetAttribute(k_addvus3m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A3_SMEM))) return e;
+    if ((e = cudaFuncSetAttribute(k_calbec3m<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM))) return e;
+    if ((e = cudaFuncSetAttribute(k_addvus3m<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A3_SMEM))) return e;
+    if ((e = cudaFuncSetAttribute(k_calbec3m<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM))) return e;
+    if ((e = cudaFuncSetAttribute(k_addvus3m<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A3_SMEM))) return e;
+    if (const char* v = getenv("QEB_GEMM_WARPS")) g_3m_warps = atoi(v) == 16 ? 16 : 8;
     if (const char* v = getenv("QEB_GEMM_4M")) g_use_3m = atoi(v) == 0;
     g_smem_set = 1;
     return cudaSuccess;
@@ -677,9 +703,12 @@ cudaError_t launch_calbec(const cplx* vkb, int npwx, const cplx* psi, int lda, i
     if (nkb <= 0 || m <= 0) return cudaSuccess;
     const int NT = cplx_mode ? (g_use_3m ? C3_NT : 64) : 128;
     dim3 grid((nkb + CB_MT - 1) / CB_MT, (m + NT - 1) / NT, nsplit);
-    if (cplx_mode && g_use_3m)
-        k_calbec3m<<<grid, 256, C3_SMEM, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, (cplx*)part);
-    else if (cplx_mode)
+    if (cplx_mode && g_use_3m) {
+        if (g_3m_warps == 16)
+            k_calbec3m<2><<<grid, 512, C3_SMEM, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, (cplx*)part);
+        else
+            k_calbec3m<4><<<grid, 256, C3_SMEM, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, (cplx*)part);
+    } else if (cplx_mode)
         k_calbec<true><<<grid, 256, CbCfg<true>::smem, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, part);
     else
         k_calbec<false><<<grid, 256, CbCfg<false>::smem, st>>>(vkb, npwx, psi, lda, n, nkb, m, gchunk, part);
@@ -716,7 +745,10 @@ cudaError_t launch_addvus(const cplx* vkb, int npwx, const void* ps, int ldps, i
     dim3 grid((m + AV_BT - 1) / AV_BT, (n + AV_GT - 1) / AV_GT);
     if (cplx_mode && g_use_3m) {
         dim3 grid3((m + A3_BT - 1) / A3_BT, (n + A3_GT - 1) / A3_GT);
-        k_addvus3m<<<grid3, 256, A3_SMEM, st>>>(vkb, npwx, (const cplx*)ps, ldps, n, nkb, m, hpsi, lda);
+        if (g_3m_warps == 16)
+            k_addvus3m<2><<<grid3, 512, A3_SMEM, st>>>(vkb, npwx, (const cplx*)ps, ldps, n, nkb, m, hpsi, lda);
+        else
+            k_addvus3m<4><<<grid3, 256, A3_SMEM, st>>>(vkb, npwx, (const cplx*)ps, ldps, n, nkb, m, hpsi, lda);
     } else if (cplx_mode)
         k_addvus<true><<<grid, 256, AvCfg<true>::smem, st>>>(vkb, npwx, ps, ldps, n, nkb, m, hpsi, lda);
     else
