@@ -66,6 +66,12 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_get_becp(ctx, becp, m) BIND(C, name='qeb_get_becp')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, becp; INTEGER(C_INT), VALUE :: m
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_qq(ctx, nat, nhm, qq_at) BIND(C, name='qeb_set_qq')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, qq_at; INTEGER(C_INT), VALUE :: nat, nhm
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_s_psi(ctx, lda, n, m, psi, spsi) BIND(C, name='qeb_s_psi')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, spsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
   END INTERFACE
 END MODULE qeb200_c
 
@@ -85,6 +91,7 @@ MODULE qeb200_state
   INTEGER :: deeq_version = -1   ! bumped by qeb200_touch_deeq (call it after newd, electrons.f90:1045)
   INTEGER :: deeq_loaded = -2
   INTEGER :: spin_loaded = -1
+  LOGICAL :: qq_loaded = .FALSE.   ! qq_at is filled once per run (upflib/init_us_1.f90)
 CONTAINS
   SUBROUTINE qeb200_check(rc, routine)
     INTEGER(C_INT), INTENT(IN) :: rc
@@ -114,7 +121,7 @@ CONTAINS
     USE wvfct,         ONLY: npwx, g2kin, current_k
     USE scf,           ONLY: vrs
     USE lsda_mod,      ONLY: current_spin
-    USE uspp,          ONLY: vkb, nkb, deeq, ofsbeta
+    USE uspp,          ONLY: vkb, nkb, deeq, ofsbeta, qq_at, okvan
     USE uspp_param,    ONLY: nh, nhm
     USE ions_base,     ONLY: nat, ityp
     USE control_flags, ONLY: gamma_only
@@ -151,6 +158,10 @@ CONTAINS
                         'qeb_set_nonlocal')
       deeq_loaded = deeq_version
       DEALLOCATE(nh_at, ofs0)
+      IF (okvan .AND. .NOT. qq_loaded) THEN   ! S = 1 + sum |beta> qq <beta| (PW/src/s_psi.f90:10)
+        CALL qeb200_check(qeb_set_qq(ctx, nat, nhm, C_LOC(qq_at)), 'qeb_set_qq')
+        qq_loaded = .TRUE.
+      END IF
     END IF
     spin_loaded = current_spin
   END SUBROUTINE
@@ -289,6 +300,30 @@ CONTAINS
     END IF
   END SUBROUTINE
 END MODULE qeb200_becmod
+
+!----------------------------------------------------------------------------
+SUBROUTINE s_psi_qeb(lda, n, m, psi, spsi)
+  !! s_psi(lda,n,m,psi,spsi) (PW/src/s_psi.f90:10-76): same EXTERNAL signature cegterg/regterg receive as
+  !! s_psi_ptr (KS_Solvers/Davidson/cegterg.f90:110-118,196,467). Uses the projections of these m bands that the
+  !! h_psi_qeb call just before left in the context (s_psi.f90:15), so becmod::becp is not re-uploaded.
+  !! Branches outside the library (real_space, noncolin) go to the reference routine.
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds,            ONLY: DP
+  USE noncollin_module, ONLY: noncolin
+  USE realus,           ONLY: real_space
+  USE qeb200_c
+  USE qeb200_state
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n, m
+  COMPLEX(DP), INTENT(IN),  TARGET :: psi(lda, m)
+  COMPLEX(DP), INTENT(OUT), TARGET :: spsi(lda, m)
+  IF (noncolin .OR. real_space) THEN
+    CALL s_psi(lda, n, m, psi, spsi)
+    RETURN
+  END IF
+  CALL qeb200_sync_state()
+  CALL qeb200_check(qeb_s_psi(ctx, lda, n, m, C_LOC(psi), C_LOC(spsi)), 's_psi')
+END SUBROUTINE s_psi_qeb
 
 !----------------------------------------------------------------------------
 SUBROUTINE invfft_qeb(fft_kind, f, howmany)

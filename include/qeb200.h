@@ -119,6 +119,19 @@ int qeb_add_vuspsi(qeb_ctx* ctx, int lda, int n, int m, void* hpsi, const void* 
 /* becp of the last qeb_h_psi / qeb_calbec: (nkb,m) complex (k) or real (Gamma) */
 int qeb_get_becp(qeb_ctx* ctx, void* becp, int m);
 
+/* Augmentation charges of the S matrix: qq_at(nhm,nhm,nat) real (upflib/uspp.f90:56-89; zero for atoms whose
+ * type is not ultrasoft/PAW), same nat/nhm/ofsbeta as the last qeb_set_nonlocal. Call after qeb_set_nonlocal
+ * (the reference fills it once per run, upflib/init_us_1.f90). */
+int qeb_set_qq(qeb_ctx* ctx, int nat, int nhm, const double* qq_at);
+
+/* s_psi(lda,n,m,psi,spsi)  PW/src/s_psi.f90:10-262 (s_psi_gamma :183-238, s_psi_k :242-306):
+ * spsi = psi (all lda rows), and with an ultrasoft S (qeb_set_qq called, nkb > 0)
+ * spsi(1:n,1:m) += vkb * (blockdiag(qq_at) * becp), where becp are the projections of THESE m bands left in the
+ * context by the qeb_h_psi / qeb_calbec that preceded (s_psi.f90:15: "Requires the products of psi with all
+ * beta functions in array becp(nkb,m) (calculated in h_psi or by calbec)"). Without qeb_set_qq it is the copy
+ * the reference does for norm-conserving runs (:120 "IF (nkb == 0 .OR. .NOT. okvan) RETURN"). */
+int qeb_s_psi(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* spsi);
+
 /* ---- multi-GPU (one process per GPU) ----------------------------------- */
 /* divide_all(comm, m, m_start, m_end, recv_counts, displs)  UtilXlib/divide.f90:55-106.
  * 0-based start/end(exclusive) of group `me` of `nproc`. */

@@ -180,6 +180,33 @@ def h_psi(d: Descriptor, lda, n, m, psi, vrs, vkb=None, deeq=None, nh_at=None, o
     return hpsi, becp
 
 
+def s_psi(d: Descriptor, lda, n, m, psi, becp, vkb=None, qq_at=None, nh_at=None, ofsbeta=None):
+    """s_psi_ (PW/src/s_psi.f90:79-262): spsi = psi on ALL lda rows (threaded_memcpy, :118); with an ultrasoft S,
+    ps = blockdiag(qq_at) becp per atom (s_psi_gamma :205-219 DGEMM, s_psi_k :262-276 ZGEMM with qq copied to
+    complex) and spsi(1:n) += vkb ps (:222-228, :293-302). becp (m,nkb) is the one h_psi/calbec left (:15)."""
+    spsi = np.array(psi[:m], dtype=np.complex128, copy=True)
+    if vkb is None or vkb.shape[0] == 0 or qq_at is None:
+        return spsi
+    ps = apply_deeq(becp, qq_at, nh_at, ofsbeta)
+    if d.gamma_only:
+        spsi[:m, :n] += ps[:m] @ vkb[:, :n]
+    else:
+        spsi[:m, :n] += ps[:m] @ vkb[:, :n]
+    return spsi
+
+
+def synthetic_qq(nh_at, seed: int = 0):
+    """qq_at(nhm,nhm,nat) as numpy (nat,nhm,nhm): symmetric, like the integrals of Q_ij (upflib/init_us_1.f90)."""
+    nh_at = np.asarray(nh_at, dtype=np.int32)
+    nhm = int(nh_at.max()) if len(nh_at) else 0
+    rng = np.random.default_rng(5234 + seed)
+    qq = np.zeros((len(nh_at), nhm, nhm))
+    for a, nh in enumerate(nh_at):
+        Q = rng.uniform(-0.5, 0.5, (nh, nh))
+        qq[a, :nh, :nh] = 0.5 * (Q + Q.T)
+    return qq
+
+
 def divide_all(m: int, nproc: int):
     """UtilXlib/divide.f90:55-106 -> (recv_counts, displs) 0-based displs."""
     base, rest = divmod(m, nproc)

@@ -98,7 +98,8 @@ struct qeb_ctx {
     // nonlocal
     bool have_nl = false;
     int nat = 0, nhm = 0, nl_rows = 0;
-    DevBuf nlint_d, deeq_d;
+    DevBuf nlint_d, deeq_d, qq_d;
+    bool have_qq = false;
     const int *row_atom_d = nullptr, *ofs_d = nullptr, *nh_d = nullptr;
     DevBuf becp_d, ps_d, part_d;
     int becp_m = 0;
@@ -784,9 +785,10 @@ static int run_calbec(qeb_ctx* c, const cplx* beta, int npwx, int nkb, const cpl
     return 0;
 }
 
-static int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi, int col0 = 0)
+static int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi, int col0 = 0, const double* dmat = nullptr)
 {
     if (!c->have_nl) QEB_FAIL(c, 51, "add_vuspsi: qeb_set_nonlocal has not been called");
+    if (!dmat) dmat = (const double*)c->deeq_d.p;
     const int nkb = c->nkb;
     if (nkb > c->nl_rows) QEB_FAIL(c, 52, "add_vuspsi: vkb has projectors not covered by ofsbeta/nh of qeb_set_nonlocal");
     const int ldps = (nkb + 1) & ~1;
@@ -794,7 +796,7 @@ static int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi, int col0 = 
     const char* becp = (const char*)c->becp_d.p + (size_t)col0 * nkb * el;
     char* ps = (char*)c->ps_d.p + (size_t)col0 * ldps * el;
     QEB_CUDA(c, launch_apply_deeq(becp, nkb, m, !c->gamma, c->row_atom_d, c->ofs_d, c->nh_d,
-                                  (const double*)c->deeq_d.p, c->nhm, ps, ldps, c->stream));
+                                  dmat, c->nhm, ps, ldps, c->stream));
     QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, ps, ldps, n, nkb, m, !c->gamma, hpsi, lda, c->stream));
     return 0;
 }
@@ -1033,6 +1035,58 @@ int qeb_add_vuspsi(qeb_ctx* c, int lda, int n, int m, void* hpsi, const void* be
     if ((rc = run_addvus(c, lda, n, m, (cplx*)hin))) return rc;
     if (!out_dev) {
         QEB_CUDA(c, cudaMemcpyAsync(hpsi, hin, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+int qeb_set_qq(qeb_ctx* c, int nat, int nhm, const double* qq_at)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_nl) QEB_FAIL(c, 42, "qeb_set_qq: qeb_set_nonlocal has not been called");
+    if (nat != c->nat || nhm != c->nhm) QEB_FAIL(c, 43, "qeb_set_qq: nat/nhm differ from qeb_set_nonlocal");
+    const size_t nd = (size_t)nhm * nhm * nat;
+    if (nd && !qq_at) QEB_FAIL(c, 43, "qeb_set_qq: null qq_at");
+    QEB_CUDA(c, c->qq_d.ensure(nd * 8 + 8));
+    if (nd)
+        QEB_CUDA(c, cudaMemcpyAsync(c->qq_d.p, qq_at, nd * 8,
+                                    is_device_ptr(qq_at) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_qq = true;
+    return 0;
+}
+
+// s_psi_ (PW/src/s_psi.f90:79-262): spsi = psi (all lda rows, threaded_memcpy :118), then, when there are
+// projectors with an augmentation part, spsi(1:n,:) += vkb * (blockdiag(qq_at) * becp) with the becp that h_psi or
+// calbec left behind (:15, :132 "the becp are already computed"). Atoms of a non-ultrasoft type contribute
+// ps = 0 (:232-240): the caller passes qq_at = 0 for them, which is what uspp holds for such types.
+int qeb_s_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* spsi)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, psi, spsi, "qeb_s_psi");
+    if (rc) return rc;
+    if (m == 0) return 0;
+    const size_t bytes = (size_t)lda * m * 16;
+    const bool okvan = c->nkb > 0 && c->have_qq;
+    if (okvan && c->becp_m < m) QEB_FAIL(c, 76, "qeb_s_psi: no projections in the context for these bands (h_psi/calbec first)");
+    const bool out_dev = is_device_ptr(spsi);
+    cplx* sd = (cplx*)spsi;
+    if (!out_dev) {
+        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
+        sd = (cplx*)c->hpsi_stage.p;
+    }
+    QEB_CUDA(c, cudaMemcpyAsync(sd, psi, bytes, is_device_ptr(psi) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                                c->stream));
+    if (okvan) {
+        const int ldps = (c->nkb + 1) & ~1;
+        QEB_CUDA(c, cudaMemsetAsync(c->ps_d.p, 0, (size_t)ldps * m * (c->gamma ? 8 : 16), c->stream));
+        if ((rc = run_addvus(c, lda, n, m, sd, 0, (const double*)c->qq_d.p))) return rc;
+    }
+    if (!out_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(spsi, sd, bytes, cudaMemcpyDeviceToHost, c->stream));
         QEB_CUDA(c, cudaStreamSynchronize(c->stream));
         return 0;
     }

@@ -59,6 +59,8 @@ def load_library():
     L.qeb_calbec.argtypes = [P, I, P, I, P, I, I, P]
     L.qeb_add_vuspsi.argtypes = [P, I, I, I, P, P]
     L.qeb_get_becp.argtypes = [P, P, I]
+    L.qeb_set_qq.argtypes = [P, I, I, P]
+    L.qeb_s_psi.argtypes = [P, I, I, I, P, P]
     L.qeb_divide_all.argtypes = [I, I, I, ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_h_psi_bgrp.argtypes = [P, I, I, I, P, P, I, I]
     L.qeb_set_nccl.argtypes = [P, P, I, I]
@@ -73,7 +75,7 @@ def load_library():
                  "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
-                 "qeb_set_grid_dist"):
+                 "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi"):
         getattr(L, name).restype = I
     _LIB = L
     return L
@@ -222,7 +224,17 @@ class HPsi:
         nhm = deeq.shape[-1] if deeq.size else 0
         self._ck(self._L.qeb_set_nonlocal(self._h, nat, nhm, _ptr(nh), _ptr(ofs), _ptr(deeq)), "qeb_set_nonlocal")
 
+    def set_qq(self, qq_at):
+        """qq_at: Fortran qq_at(nhm,nhm,nat), i.e. numpy shape (nat,nhm,nhm) (upflib/uspp.f90); after set_nonlocal."""
+        qq = np.ascontiguousarray(qq_at, dtype=np.float64)
+        self._ck(self._L.qeb_set_qq(self._h, qq.shape[0], qq.shape[-1] if qq.size else 0, _ptr(qq)), "qeb_set_qq")
+
     # -- reference entry points --------------------------------------------
+    def s_psi(self, lda, n, m, psi, spsi):
+        """s_psi(lda, n, m, psi, spsi) (PW/src/s_psi.f90:10): uses the becp the preceding h_psi/calbec left."""
+        self._ck(self._L.qeb_s_psi(self._h, lda, n, m, _ptr(psi), _ptr(spsi)), "qeb_s_psi")
+        return spsi
+
     def h_psi(self, lda, n, m, psi, hpsi):
         self._ck(self._L.qeb_h_psi(self._h, lda, n, m, _ptr(psi), _ptr(hpsi)), "qeb_h_psi")
         return hpsi

@@ -279,3 +279,56 @@ def test_h_psi_host_pipeline(mods, name, m, chunk):
         assert np.all(out[:, n:] == 0)
         assert relerr(h.get_becp(m), becp_ref) < TOL
     h.close()
+
+
+@pytest.mark.parametrize("name", SMALL + ["si2", "al4"])
+@pytest.mark.parametrize("m", [1, 4, 9])
+def test_s_psi_after_h_psi(mods, name, m):
+    """s_psi (PW/src/s_psi.f90:10-262) right after h_psi, as cegterg calls them (cegterg.f90:192-196): it re-uses
+    the becp that h_psi left behind; every lda row of psi is copied (threaded_memcpy, :118)."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    c = d.extra["config"]
+    nh = c.get("nh_list") or [c["nh"]] * c["nat"]
+    inp = R.synthetic_inputs(d, m, nh, seed=5, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    qq = R.synthetic_qq(nh, seed=5)
+    _, becp_ref = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    ref = R.s_psi(d, lda, n, m, inp["psi"], becp_ref, inp["vkb"], qq, inp["nh_at"], inp["ofsbeta"])
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    out = np.empty((m, lda), dtype=complex)
+    # norm-conserving run (no qq): plain copy
+    h.h_psi(lda, n, m, inp["psi"], out)
+    sp = np.full((m, lda), np.nan + 1j * np.nan)
+    h.s_psi(lda, n, m, inp["psi"], sp)
+    assert np.array_equal(sp, inp["psi"])
+    # ultrasoft S
+    h.set_qq(qq)
+    h.s_psi(lda, n, m, inp["psi"], sp)
+    assert relerr(sp, ref) < TOL
+    assert np.array_equal(sp[:, n:], inp["psi"][:, n:])
+    # device pointers
+    psi_t = torch.from_numpy(inp["psi"]).cuda()
+    sp_t = torch.empty_like(psi_t)
+    hp_t = torch.empty_like(psi_t)
+    h.h_psi(lda, n, m, psi_t, hp_t)
+    h.s_psi(lda, n, m, psi_t, sp_t)
+    torch.cuda.synchronize()
+    assert relerr(sp_t.cpu().numpy(), ref) < TOL
+    h.close()
+
+
+def test_s_psi_needs_becp(mods):
+    qe, D, R, torch = mods
+    d = D.config_descriptor("si2_small")
+    inp = R.synthetic_inputs(d, 3, [4, 4], poison=False)
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    h.set_qq(R.synthetic_qq([4, 4]))
+    with pytest.raises(qe.QebError):
+        h.s_psi(inp["lda"], inp["n"], 3, inp["psi"], inp["psi"].copy())  # no h_psi / calbec before
+    out = np.zeros((3, inp["nkb"]), dtype=complex)
+    h.calbec(inp["n"], None, inp["psi"], out, 3, lda=inp["lda"])
+    h.s_psi(inp["lda"], inp["n"], 3, inp["psi"], inp["psi"].copy())
+    h.close()

@@ -160,3 +160,26 @@ def test_hpsi_hermitian_and_gamma_real():
 def test_divide_all():
     c, dsp = R.divide_all(10, 4)
     assert list(c) == [3, 3, 2, 2] and list(dsp) == [0, 3, 6, 8]
+
+
+def test_s_psi_restatement_hermitian_and_copy():
+    """S = 1 + sum |beta_i> qq_ij <beta_j| (PW/src/s_psi.f90:10-262) is Hermitian for symmetric qq; without qq
+    (norm-conserving, :120) it is the copy of all lda rows."""
+    for name in ("ortho_small", "ortho_small_gamma"):
+        d = D.config_descriptor(name)
+        c = d.extra["config"]
+        nh = [c["nh"]] * c["nat"]
+        inp = R.synthetic_inputs(d, 2, nh, seed=4, poison=False)
+        lda, n = inp["lda"], inp["n"]
+        _, becp = R.h_psi(d, lda, n, 2, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+        assert np.array_equal(R.s_psi(d, lda, n, 2, inp["psi"], becp), inp["psi"])
+        qq = R.synthetic_qq(nh, seed=4)
+        s = R.s_psi(d, lda, n, 2, inp["psi"], becp, inp["vkb"], qq, inp["nh_at"], inp["ofsbeta"])
+        assert np.array_equal(s[:, n:], inp["psi"][:, n:])
+        a, b = inp["psi"][0, :n], inp["psi"][1, :n]
+        if d.gamma_only:
+            def dot(x, y):
+                return 2.0 * np.vdot(x, y).real - (x[0].conjugate() * y[0]).real
+            assert abs(dot(a, s[1, :n]) - dot(b, s[0, :n])) < 1e-12
+        else:
+            assert abs(np.vdot(a, s[1, :n]) - np.conj(np.vdot(b, s[0, :n]))) < 1e-12
