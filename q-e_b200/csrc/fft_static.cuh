@@ -39,6 +39,11 @@ struct SPlan {
 };
 
 constexpr int QEB_TL = 32;  // lines per tile = lanes
+#ifdef QEB_NO_VPREFETCH       // tuning aid (q-e_b200/build.py --variant): fetch the pointwise factor without pipelining
+constexpr bool QEB_VPF = false;
+#else
+constexpr bool QEB_VPF = true;
+#endif
 
 // twiddle from a table that the fast kernels stage in shared memory (plain load: LDS once inlined)
 QEB_HD cplx stw(const cplx* tw, int j, double sgn) { return mk(tw[j].x, sgn * tw[j].y); }
@@ -53,15 +58,30 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
     constexpr int NB = PL::N / L;
     constexpr int NJ = PL::N / R;
     if (lane >= nl) return;
+    double fnext[FUSE2 ? R : 1];
+    if (FUSE2 && QEB_VPF && warp < NJ) {  // pointwise factor of the first butterfly (software pipeline, see below)
+        const int blk = warp / A;
+        const int base = blk * L + (warp - blk * A);
+#pragma unroll
+        for (int d = 0; d < R; ++d) fnext[d] = mid.fetch(lane, base + d);
+    }
     for (int j = warp; j < NJ; j += nwarps) {
         const int blk = j / A;
         const int a = j - blk * A;
         const int base = blk * L + a;
         cplx v[R];
         double f[FUSE2 ? R : 1];
-        if (FUSE2) {  // issue the loads of the pointwise factor first: they overlap the tile loads and the butterfly
+        if (FUSE2) {  // the factor of this butterfly was fetched one iteration ago; fetch the next one now so that
+                      // its L2 latency hides behind this butterfly
 #pragma unroll
-            for (int d = 0; d < R; ++d) f[d] = mid.fetch(lane, base + d);
+            for (int d = 0; d < R; ++d) f[d] = QEB_VPF ? fnext[d] : mid.fetch(lane, base + d);
+            const int jn = j + nwarps;
+            if (QEB_VPF && jn < NJ) {
+                const int blkn = jn / A;
+                const int basen = blkn * L + (jn - blkn * A);
+#pragma unroll
+                for (int d = 0; d < R; ++d) fnext[d] = mid.fetch(lane, basen + d);
+            }
         }
 #pragma unroll
         for (int b = 0; b < R; ++b) v[b] = src.load(lane, base + A * b);

@@ -9,6 +9,7 @@
 // coefficient transform to zero (G->R) and are never gathered (R->G), so the
 // results are identical.
 #pragma once
+#include <cstdlib>
 #include <algorithm>
 #include <string>
 #include <vector>
@@ -115,6 +116,7 @@ inline std::string build_vloc_tables(int nr1, int nr2, int nr3, int npw, const i
         int cap = (int)(smem_cap / (16 * (size_t)nr3));
         int tz = std::min(32, std::max(1, cap));
         if (tz >= 8) tz &= ~7;
+        if (const char* e = getenv("QEB_TZ")) tz = std::max(1, std::min(32, atoi(e)));  // tuning aid (tools/vloc_sweep.py)
         if (T.gamma && tz < 2) tz = 2;
         T.TZ = std::max(1, std::min(tz, std::max(T.nst, T.gamma ? 2 : 1)));
         if (T.gamma && T.TZ < 2) T.TZ = 2;
@@ -125,7 +127,11 @@ inline std::string build_vloc_tables(int nr1, int nr2, int nr3, int npw, const i
         {
             const int nt = (nr3 + ty_hi - 1) / ty_hi;
             T.TY = (nr3 + nt - 1) / nt;
+            // full 32-line tiles keep every 512-byte G2 row segment sector-aligned; measured +2% on the V_loc section
+            // at nr3 = 200 (profiles/r1m_sweep.log) - taken when the short last tile wastes little
+            if (ty_hi == 32 && (nt * 32 - nr3) * 100 <= 12 * nt * 32) T.TY = 32;
         }
+        if (const char* e = getenv("QEB_TY")) T.TY = std::max(1, std::min(ty_hi, atoi(e)));  // tuning aid
         T.nty = (nr3 + T.TY - 1) / T.TY;
         T.smem_y = ((size_t)nr2 * T.TY + (size_t)T.nsmax * (T.TY + 1)) * 16;
         int tx_hi = 32;
