@@ -89,7 +89,7 @@ struct qeb_ctx {
     cudaEvent_t vev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // potential
     bool have_v = false;
-    DevBuf v_d, vp_d;
+    DevBuf v_d, vp_d, vpl_d;
     DevBuf revx_d;
     // full-box FFT plans
     DevBuf full_plan_d;
@@ -216,7 +216,7 @@ int qeb_destroy(qeb_ctx* c)
     if (!c) return 0;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf* bufs[] = {&c->g2kin_d, &c->vkb_own, &c->tab_d, &c->plan_d, &c->g1_d, &c->g2_d, &c->v_d, &c->vp_d,
+    DevBuf* bufs[] = {&c->g2kin_d, &c->vkb_own, &c->tab_d, &c->plan_d, &c->g1_d, &c->g2_d, &c->v_d, &c->vp_d, &c->vpl_d,
                       &c->revx_d, &c->full_plan_d, &c->nlint_d, &c->deeq_d, &c->becp_d, &c->ps_d, &c->part_d,
                       &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage, &c->tabp_d, &c->planp_d,
                       &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d};
@@ -433,7 +433,8 @@ static int upload_tables(qeb_ctx* c, HostVlocTables& H, DevBuf& tab_d, DevBuf& p
 {
     // integer tables in one allocation
     std::vector<const std::vector<int>*> vs = {&H.xmap, &H.plane_s0, &H.plane_ns, &H.ymap, &H.grp_stick, &H.grp_nl,
-                                               &H.grp_coef_off, &H.coef_ig, &H.coef_slot, &H.coef_slot2};
+                                               &H.grp_coef_off, &H.coef_ig, &H.coef_slot, &H.coef_slot2,
+                                               &H.pl_ymapT, &H.plane_x};
     size_t tot = 0;
     std::vector<size_t> offs;
     for (auto v : vs) {
@@ -467,6 +468,10 @@ static int upload_tables(qeb_ctx* c, HostVlocTables& H, DevBuf& tab_d, DevBuf& p
     t.coef_slot = base + offs[8];
     t.coef_slot2 = H.gamma ? base + offs[9] : nullptr;
     t.grp_div = (const FastDiv*)(base + div_off);
+    t.pl_ymapT = base + offs[10];
+    t.pl_xact = base + offs[11];
+    t.pl_ldp = H.pl_ldp;
+    t.pl_v = nullptr;  // set by prepare_v when the plane kernel is usable
     t.TZ = H.TZ;
     t.ngrp = H.ngrp;
     t.TY = H.TY;
@@ -499,6 +504,9 @@ static int upload_tables(qeb_ctx* c, HostVlocTables& H, DevBuf& tab_d, DevBuf& p
     cfg.smem_y = H.smem_y;
     cfg.smem_x = H.smem_x;
     cfg.threads_z = cfg.threads_y = cfg.threads_x = 256;
+    cfg.smem_plane = H.smem_plane;
+    cfg.max_smem = c->max_smem;
+    cfg.num_sms = c->num_sms;
     if (H.smem_z > c->max_smem || H.smem_y > c->max_smem || H.smem_x > c->max_smem)
         QEB_FAIL(c, 21, "FFT dimension too large for the shared-memory pencil kernels");
     return 0;
@@ -621,6 +629,14 @@ static int prepare_v(qeb_ctx* c, const double* v)
     QEB_CUDA(c, vloc_prepare_v((const double*)vd, (double*)c->vp_d.p, c->fpx.rev, c->nr1, c->nr2, nz, scale, c->stream));
     c->T.vp = (const double*)c->vp_d.p;
     c->Tp.vp = (const double*)c->vp_d.p;
+    // fused plane pass (serial descriptor): the potential again, permuted for the shared-memory plane
+    c->T.pl_v = nullptr;
+    if (!c->dist && c->cfg.smem_plane > 0 && c->cfg.smem_plane <= c->max_smem && vloc_plane_available(c->T)) {
+        QEB_CUDA(c, c->vpl_d.ensure(nnr * 8));
+        QEB_CUDA(c, vloc_prepare_v_plane((const double*)vd, (double*)c->vpl_d.p, c->T.px.rev, c->T.py.rev, c->nr1, c->nr2,
+                                         nz, scale, c->stream));
+        c->T.pl_v = (const double*)c->vpl_d.p;
+    }
     c->have_v = true;
     return 0;
 }

@@ -107,10 +107,37 @@ inline bool preferred_factors(int n, std::vector<int>& out)
     }
 }
 
-inline bool make_host_plan(int n, HostPlan& hp, int maxr = 10)
+// "8,5,5" -> {8,5,5} when the product is n and every radix has a butterfly; tuning aid for the QEB_[XYZ]PLAN
+// environment overrides (an alternative radix list only takes the fast kernels if fft_static.cuh instantiates it)
+inline bool parse_plan(const char* txt, int n, std::vector<int>& out)
+{
+    out.clear();
+    if (!txt) return false;
+    long prod = 1;
+    for (const char* c = txt; *c;) {
+        int r = 0;
+        while (*c >= '0' && *c <= '9') r = r * 10 + (*c++ - '0');
+        if (r < 2 || r > 27) return false;
+        out.push_back(r);
+        prod *= r;
+        if (*c == ',') ++c;
+        else if (*c) return false;
+    }
+    return prod == n && (int)out.size() <= QEB_MAXPASS;
+}
+
+inline bool make_host_plan(int n, HostPlan& hp, int maxr = 10, const char* override_txt = nullptr)
 {
     hp.n = n;
-    if (!(maxr >= 10 && preferred_factors(n, hp.r)) && !factorize(n, hp.r, maxr)) return false;
+    if (parse_plan(override_txt, n, hp.r)) {
+        static const int ok[] = {2, 3, 4, 5, 8, 9, 12, 15, 25, 27};
+        for (int r : hp.r) {
+            bool f = false;
+            for (int o : ok) f = f || (o == r);
+            if (!f) return false;
+        }
+    } else if (!(maxr >= 10 && preferred_factors(n, hp.r)) && !factorize(n, hp.r, maxr))
+        return false;
     if (hp.r.empty()) hp.r.push_back(1);  // n == 1: not used by the kernels
     hp.L.clear();
     int L = n;

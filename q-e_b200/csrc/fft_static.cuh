@@ -131,5 +131,10 @@ using SP125 = SPlan<125, 25, 5>;
 using SP135 = SPlan<135, 15, 9>;
 using SP144 = SPlan<144, 12, 12>;
 using SP200 = SPlan<200, 25, 8>;
+// low-register alternatives (radices <= 8: about half the registers per thread, twice the resident warps, one more
+// shared-memory exchange); selected with QEB_XPLAN / QEB_YPLAN / QEB_ZPLAN
+using SP200b = SPlan<200, 8, 5, 5>;
+using SP125b = SPlan<125, 5, 5, 5>;
+using SP64b = SPlan<64, 4, 4, 4>;
 
 }  // namespace qeb

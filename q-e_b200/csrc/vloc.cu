@@ -3,6 +3,7 @@
 // reference lines it replaces.
 #include "vloc.h"
 #include "vloc_fast_inst.cuh"
+#include "vloc_plane_inst.cuh"
 
 namespace qeb {
 
@@ -60,7 +61,7 @@ __global__ void __launch_bounds__(256) k_vloc_xfus(const __grid_constant__ VlocT
 
 
 // ---- fast variants (vloc_fast_inst.cuh, instantiated in vloc_fast_<N>.cu) ----
-#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200)
+#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200) X(SP200b)
 #define X(PL) extern template struct FastLaunch<PL>;
 QEB_FOR_PLANS(X)
 #undef X
@@ -102,6 +103,47 @@ static bool launch_x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, 
     return false;
 }
 
+// ---- fused plane pass (vloc_plane_inst.cuh, instantiated in vloc_plane_<n1>_<n2>.cu) ----
+#define QEB_FOR_PLANES(X) \
+    X(SP125, SP64, 512) X(SP25, SP25, 512) X(SP27, SP27, 512) X(SP15, SP15, 512) X(SP64, SP64, 512) \
+    X(SP125b, SP64, 1024) X(SP125b, SP64b, 1024)
+#define X(PX, PY, MT) extern template struct PlaneLaunch<PX, PY, MT>;
+QEB_FOR_PLANES(X)
+#undef X
+
+bool vloc_plane_available(const VlocTables& t)
+{
+#define X(PX, PY, MT) \
+    if (PX::matches(t.px) && PY::matches(t.py)) return true;
+    QEB_FOR_PLANES(X)
+#undef X
+    return false;
+}
+
+static bool launch_plane(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
+{
+    if (!t.pl_v || cfg.smem_plane == 0 || cfg.smem_plane > cfg.max_smem || env_int("QEB_GENERIC", 0) ||
+        !env_int("QEB_PLANE", 1))
+        return false;
+#define X(PX, PY, MT) \
+    if (PlaneLaunch<PX, PY, MT>::run(t, nboxes, cfg.num_sms, cfg.max_smem, st)) return true;
+    QEB_FOR_PLANES(X)
+#undef X
+    return false;
+}
+
+__global__ void k_prepare_v_plane(const double* __restrict__ v, double* __restrict__ vpl, const int* __restrict__ rev_x,
+                                  const int* __restrict__ rev_y, int nr1, int nr2, int nr3, double scale)
+{
+    // one block per (xpos chunk, z): reads are a gather inside one (x,y) plane (L1/L2 resident), writes coalesced
+    const int z = blockIdx.y;
+    const size_t plane = (size_t)nr1 * nr2;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < (int)plane; i += gridDim.x * blockDim.x) {
+        const int xp = i / nr2, yp = i - xp * nr2;
+        vpl[(size_t)z * plane + i] = v[rev_x[xp] + (size_t)nr1 * (rev_y[yp] + (size_t)nr2 * z)] * scale;
+    }
+}
+
 __global__ void k_prepare_v(const double* __restrict__ v, double* __restrict__ vp, const int* __restrict__ rev_x,
                             int nr1, int nr2, int nr3, double scale)
 {
@@ -134,6 +176,10 @@ cudaError_t vloc_init_attrs(size_t max_smem)
 #define X(PL) FastLaunch<PL>::attrs(s);
     QEB_FOR_PLANS(X)
 #undef X
+#define X(PX, PY, MT) \
+    if ((e = PlaneLaunch<PX, PY, MT>::attrs(s))) return e;
+    QEB_FOR_PLANES(X)
+#undef X
     return cudaGetLastError();
 }
 
@@ -153,6 +199,7 @@ cudaError_t vloc_launch_zpass(bool inv, const VlocTables& t, const VlocIO& io, c
 cudaError_t vloc_launch_planes(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
 {
     if (nboxes <= 0 || t.nxw <= 0 || t.npos <= 0) return cudaSuccess;
+    if (launch_plane(t, cfg, nboxes, st)) return cudaGetLastError();
     if (!launch_y(true, t, cfg, nboxes, st))
         k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
     if (!launch_x(t, cfg, nboxes, st))
@@ -177,6 +224,15 @@ cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr
 {
     dim3 grid((nr3 + 31) / 32, nr2);
     k_prepare_v<<<grid, 256, (size_t)32 * (nr1 + 1) * 8, st>>>(v, vp, rev_x, nr1, nr2, nr3, scale);
+    return cudaGetLastError();
+}
+
+cudaError_t vloc_prepare_v_plane(const double* v, double* vpl, const int* rev_x, const int* rev_y, int nr1, int nr2,
+                                 int nr3, double scale, cudaStream_t st)
+{
+    const int per = (nr1 * nr2 + 255) / 256;
+    dim3 grid(per < 64 ? per : 64, nr3);
+    k_prepare_v_plane<<<grid, 256, 0, st>>>(v, vpl, rev_x, rev_y, nr1, nr2, nr3, scale);
     return cudaGetLastError();
 }
 

@@ -6,6 +6,9 @@ namespace qeb {
 struct VlocLaunchCfg {
     size_t smem_z, smem_y, smem_x;
     int threads_z, threads_y, threads_x;
+    // fused plane pass (vloc_plane.cuh): used when t.pl_v is set and smem_plane <= max_smem
+    size_t smem_plane = 0, max_smem = 0;
+    int num_sms = 148;
 };
 cudaError_t vloc_init_attrs(size_t max_smem);
 // one batch of nboxes boxes (bands for k, band pairs for Gamma)
@@ -19,4 +22,9 @@ cudaError_t vloc_launch_planes(const VlocTables& t, const VlocLaunchCfg& cfg, in
 // vp[xpos*npos + y*nr3 + z] = v[x = rev_x[xpos] + nr1*(y + nr2*z)] * scale
 cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr1, int nr2, int nr3, double scale,
                            cudaStream_t st);
+// plane-kernel layout of the potential: vpl[(z*nr1 + xpos)*nr2 + ypos] = v[rev_x[xpos] + nr1*(rev_y[ypos] + nr2*z)] * scale
+cudaError_t vloc_prepare_v_plane(const double* v, double* vpl, const int* rev_x, const int* rev_y, int nr1, int nr2,
+                                 int nr3, double scale, cudaStream_t st);
+// true when an instantiated plane kernel exists for these tables' (x,y) plans
+bool vloc_plane_available(const VlocTables& t);
 }  // namespace qeb

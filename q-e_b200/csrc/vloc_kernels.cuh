@@ -55,6 +55,11 @@ struct VlocTables {
     // slab-distributed path uses [z][box][stick] = nboxes*nst with g1_box = nst, so that the z range owned by a
     // peer rank is one contiguous block of the batch)
     size_t g1_zs;
+    // fused plane pass (vloc_plane.cuh), when the (x,y) plane fits in shared memory; pl_v == nullptr: not used
+    const int* pl_ymapT;   // [nr2*nxw] stick id at (y, xa) or -1
+    const int* pl_xact;    // [nxw]     xa -> x
+    const double* pl_v;    // [nr3][nr1 xpos][nr2 ypos] = v(rev_x[xpos], rev_y[ypos], z)/(nr1 nr2 nr3)
+    int pl_ldp;            // row stride of the shared-memory plane (odd, >= nr1)
 };
 
 struct VlocIO {

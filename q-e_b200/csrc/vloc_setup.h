@@ -15,6 +15,7 @@
 #include <vector>
 #include "fft_plan.h"
 #include "vloc_kernels.cuh"
+#include "vloc_plane.cuh"
 
 namespace qeb {
 
@@ -28,6 +29,10 @@ struct HostVlocTables {
     std::vector<int> grp_stick, grp_nl, grp_coef_off, coef_ig, coef_slot, coef_slot2;
     std::vector<FastDiv> grp_div;
     size_t smem_z = 0, smem_y = 0, smem_x = 0;
+    // fused plane pass (vloc_plane.cuh)
+    std::vector<int> pl_ymapT;  // [nr2*nxw] stick id at (y, xa) or -1
+    int pl_ldp = 0;
+    size_t smem_plane = 0;
 };
 
 inline int pick_tile(int n, int lo, int hi)
@@ -62,7 +67,8 @@ inline std::string build_vloc_tables(int nr1, int nr2, int nr3, int npw, const i
     T.nr2 = nr2;
     T.nr3 = nr3;
     T.gamma = nlm != nullptr || gamma_flag;
-    if (!make_host_plan(nr1, T.px) || !make_host_plan(nr2, T.py) || (need_pz && !make_host_plan(nr3, T.pz)))
+    if (!make_host_plan(nr1, T.px, 10, getenv("QEB_XPLAN")) || !make_host_plan(nr2, T.py, 10, getenv("QEB_YPLAN")) ||
+        (need_pz && !make_host_plan(nr3, T.pz, 10, getenv("QEB_ZPLAN"))))
         return "FFT dimension with a prime factor other than 2, 3, 5";
     const int ncol = nr1 * nr2;
     std::vector<int> col_stick(ncol, -1);
@@ -111,6 +117,11 @@ inline std::string build_vloc_tables(int nr1, int nr2, int nr3, int npw, const i
         int xa = T.xmap[T.stick_x[s]];
         T.ymap[(size_t)xa * nr2 + T.stick_y[s]] = s - T.plane_s0[xa];
     }
+    // fused plane pass: transposed stick map, plane row stride (odd)
+    T.pl_ymapT.assign((size_t)nr2 * T.nxw, -1);
+    for (int s = 0; s < T.nst; ++s) T.pl_ymapT[(size_t)T.stick_y[s] * T.nxw + T.xmap[T.stick_x[s]]] = s;
+    T.pl_ldp = nr1 | 1;
+    T.smem_plane = plane_smem_bytes(nr1, nr2, T.nst, T.nxw, T.pl_ldp);
     // tile sizes
     {
         int cap = (int)(smem_cap / (16 * (size_t)nr3));

@@ -8,6 +8,7 @@
 #include "vloc_setup.h"
 #include "fullfft_kernels.cuh"
 #include "vloc_fast.cuh"
+#include "vloc_plane.cuh"
 
 using namespace qeb;
 
@@ -48,7 +49,7 @@ extern "C" int emul_fft1d(int n, int sign, int nlines, const double* in, double*
     return 0;
 }
 
-#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200)
+#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200) X(SP200b)
 typedef void (*zfn)(int, int, int, const VlocTables&, const VlocIO&, int, int, cplx*, const FastTabs&);
 typedef void (*yfn)(int, int, int, const VlocTables&, int, int, int, cplx*, const FastTabs&);
 typedef void (*xfn)(int, int, int, const VlocTables&, int, int, cplx*, const FastTabs&);
@@ -81,6 +82,17 @@ static xfn pick_x(const FftPlan& pl)
     return xfus_g;
 }
 
+// fused plane pass (vloc_plane.cuh): one plane z of one box, stick row in / out through g1
+typedef void (*pfn)(int, int, int, const VlocTables&, int, cplx*, const cplx*, cplx*, const PlaneSm&);
+#define QEB_FOR_PLANES(X) X(SP125, SP64) X(SP25, SP25) X(SP27, SP27) X(SP15, SP15) X(SP64, SP64) X(SP125b, SP64) X(SP125b, SP64b)
+static pfn pick_plane(const VlocTables& t, int* nph)
+{
+#define X(PX, PY) if (PX::matches(t.px) && PY::matches(t.py)) { *nph = plane_nphase<PX, PY>(); return (pfn)plane_phase<PX, PY>; }
+    QEB_FOR_PLANES(X)
+#undef X
+    return nullptr;
+}
+
 extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, const int* nlm, const int* igk, int ngm,
                          int lda, int m, const double* psi, const double* v, const double* g2kin, double* hpsi,
                          int nthr, int batch)
@@ -106,6 +118,17 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
     t.TX = H.TX; t.ntx = H.ntx; t.divTX = make_fastdiv(H.TX);
     { int last = t.npos - (H.ntx - 1) * H.TX; t.divTXlast = make_fastdiv(last); }
     t.nsmax = H.nsmax;
+    t.pl_ymapT = H.pl_ymapT.data(); t.pl_xact = H.plane_x.data(); t.pl_ldp = H.pl_ldp;
+    std::vector<double> vpl((size_t)nr1 * nr2 * nr3);
+    for (int z = 0; z < nr3; ++z)
+        for (int xp = 0; xp < nr1; ++xp)
+            for (int yp = 0; yp < nr2; ++yp)
+                vpl[((size_t)z * nr1 + xp) * nr2 + yp] =
+                    v[H.px.rev[xp] + (size_t)nr1 * (H.py.rev[yp] + (size_t)nr2 * z)] * (1.0 / ((double)nr1 * nr2 * nr3));
+    t.pl_v = vpl.data();
+    int plane_nph = 0;
+    pfn plane_fn = g_fast == 2 ? pick_plane(t, &plane_nph) : nullptr;
+    if (g_fast == 2 && !plane_fn) return 2;  // no instantiated plane kernel for this grid
     // potential: permuted by rev_x and scaled
     std::vector<double> vp((size_t)nr1 * t.npos);
     const double sc = 1.0 / ((double)nr1 * nr2 * nr3);
@@ -139,6 +162,20 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
                 for (int ph = 0; ph < zinv_nphase(t); ++ph)
                     for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
             }
+            if (plane_fn) {
+                const PlaneSm psm{t.px.tw, t.py.tw, t.pl_ymapT, t.xmap, t.pl_xact};
+                std::vector<cplx> P((size_t)nr2 * t.pl_ldp), sin(H.nst), sout(H.nst);
+                const int pthr = ((nthr + 31) / 32) * 32;  // whole warps
+                for (int z = 0; z < nr3; ++z) {
+                    for (auto& x : P) x = nanv;
+                    for (auto& x : sout) x = nanv;
+                    cplx* row = t.g1 + (size_t)box * t.g1_box + (size_t)z * t.g1_zs;
+                    for (int i = 0; i < H.nst; ++i) sin[i] = row[i];
+                    for (int ph = 0; ph < plane_nph; ++ph)
+                        for (int tid = 0; tid < pthr; ++tid) plane_fn(ph, tid, pthr, t, z, P.data(), sin.data(), sout.data(), psm);
+                    for (int i = 0; i < H.nst; ++i) row[i] = sout[i];
+                }
+            } else {
             for (int xa = 0; xa < H.nxw; ++xa)
                 for (int zt = 0; zt < H.nty; ++zt) {
                     for (auto& x : smem) x = nanv;
@@ -156,6 +193,7 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
                     for (int ph = 0; ph < ypass_nphase(t); ++ph)
                         for (int tid = 0; tid < nthr; ++tid) pick_y(t.py, false)(ph, tid, nthr, t, zt, xa, box, smem.data(), FastTabs{t.py.tw, t.ymap + (size_t)xa * t.nr2, t.py.rev, nullptr});
                 }
+            }
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
                 for (int ph = 0; ph < zfwd_nphase(t); ++ph)

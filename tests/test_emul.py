@@ -122,3 +122,45 @@ def test_vloc_fast_phases_full_baseline_grids(emul, name, m):
     assert rc == 0
     assert np.abs(out[:, :n] - ref[:, :n]).max() / np.abs(ref[:, :n]).max() < 1e-13
     emul.emul_set_fast(0)
+
+
+def _run_plane_emul(emul, name, m, nthr, batch):
+    emul.emul_set_fast(2)
+    try:
+        d = D.config_descriptor(name)
+        inp = R.synthetic_inputs(d, m, [4, 4], seed=2)
+        lda, n = inp["lda"], inp["n"]
+        ref = np.zeros((m, lda), complex)
+        (R.vloc_psi_gamma if d.gamma_only else R.vloc_psi_k)(d, lda, n, m, inp["psi"], inp["vrs"], ref)
+        out = np.zeros((m, lda), complex)
+        nl_ = np.ascontiguousarray(d.nl, dtype=np.int32)
+        nlm = np.ascontiguousarray(d.nlm, dtype=np.int32) if d.gamma_only else None
+        igk = None if d.gamma_only else np.ascontiguousarray(d.igk, dtype=np.int32)
+        rc = emul.emul_vloc(d.nr1, d.nr2, d.nr3, n, p(nl_), p(nlm), p(igk), d.ngm, lda, m, p(inp["psi"]),
+                            p(inp["vrs"]), None, p(out), nthr, batch)
+        assert rc == 0
+        assert np.abs(out[:, :n] - ref[:, :n]).max() / np.abs(ref[:, :n]).max() < 1e-13
+    finally:
+        emul.emul_set_fast(0)
+
+
+@pytest.mark.parametrize("name", ["si2_small", "si2_small_gamma", "si2", "al4"])
+@pytest.mark.parametrize("nthr", [32, 96, 512])
+def test_plane_phases_match_oracle(emul, name, nthr):
+    """the fused plane pass (vloc_plane.cuh: y | x*V*x | y on one shared-memory plane) on the small grids with an
+    instantiated (x,y) plan pair, with fewer, as many and more warps than line groups"""
+    _run_plane_emul(emul, name, 3, nthr, 2)
+
+
+def test_plane_phases_ausurf_grid(emul):
+    """BASELINE AUSURF112 grid (125 x 64 plane, 200 planes) through the plane pass with the kernel's 16 warps"""
+    _run_plane_emul(emul, "ausurf112", 1, 512, 1)
+
+
+def test_plane_and_z_low_register_plans_ausurf(emul, monkeypatch):
+    """QEB_XPLAN/QEB_YPLAN/QEB_ZPLAN overrides: 125 = 5x5x5, 64 = 4x4x4, 200 = 8x5x5 (the low-register static
+    plans of fft_static.cuh) through the plane pass and the fast z passes on the AUSURF112 grid"""
+    monkeypatch.setenv("QEB_XPLAN", "5,5,5")
+    monkeypatch.setenv("QEB_YPLAN", "4,4,4")
+    monkeypatch.setenv("QEB_ZPLAN", "8,5,5")
+    _run_plane_emul(emul, "ausurf112", 1, 1024, 1)
