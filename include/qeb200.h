@@ -64,7 +64,7 @@ int qeb_set_grid(qeb_ctx* ctx, int nr1, int nr2, int nr3, int nr1x, int nr2x, in
 /* Per-k-point state: npw = ngk(ik), npwx, igk_k(:,ik) (NULL for gamma_only:
  * igk(i)=i), g2kin(1:npw) (PW/src/g2_kin.f90:37-43), vkb(npwx,nkb)
  * (upflib/init_us_2_acc.f90:10), gstart (Modules/recvec_subs.f90:256-260).
- * vkb may be NULL when nkb == 0. */
+ * vkb may be NULL when nkb == 0, or when qeb_init_us_2 builds it; g2kin may be NULL when qeb_g2_kin builds it. */
 int qeb_set_kpoint(qeb_ctx* ctx, int npw, int npwx, const int* igk, const double* g2kin, const void* vkb, int nkb,
                    int gstart);
 
@@ -131,6 +131,33 @@ int qeb_set_qq(qeb_ctx* ctx, int nat, int nhm, const double* qq_at);
  * beta functions in array becp(nkb,m) (calculated in h_psi or by calbec)"). Without qeb_set_qq it is the copy
  * the reference does for norm-conserving runs (:120 "IF (nkb == 0 .OR. .NOT. okvan) RETURN"). */
 int qeb_s_psi(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* spsi);
+
+/* ---- device-side producers of the per-k-point state --------- */
+/* With these the caller passes NULL for g2kin and/or vkb in qeb_set_kpoint and the arrays are built on the device,
+ * where h_psi consumes them (a k-point change then uploads igk only, not the 16*npwx*nkb bytes of vkb).
+ *
+ * qeb_set_gvectors: gvect::g(3,ngm) in 2pi/alat units and gvect::mill(3,ngm) (Modules/recvec.f90), once per run
+ * (mill may be NULL when only qeb_g2_kin is used). */
+int qeb_set_gvectors(qeb_ctx* ctx, int ngm, const double* g, const int* mill);
+/* g2_kin(ik)  PW/src/g2_kin.f90:10-62: g2kin(i) = |xk + g(:,igk(i))|^2 tpiba2, plus the modified kinetic
+ * functional qcutz (1 + erf((g2kin - ecfixed)/q2sigma)) when qcutz > 0. Uses npw/igk of the last qeb_set_kpoint;
+ * the result becomes the context's g2kin and is also copied to g2kin_out when that is not NULL. */
+int qeb_g2_kin(qeb_ctx* ctx, const double* xk, double tpiba2, double qcutz, double ecfixed, double q2sigma,
+               double* g2kin_out);
+/* uspp / uspp_param / beta_mod module state read by init_us_2 (upflib/init_us_2_acc.f90:22-24, beta_mod.f90:14-28):
+ * nh(nsp); nhtol, nhtolm, indv (nhm,nsp) with the reference's 1-based lm / beta indices; lmaxkb;
+ * tab_beta(nqx,nbetam,nsp) and its spacing dq. Once per run (init_us_1 / init_tab_beta). */
+int qeb_set_beta_tables(qeb_ctx* ctx, int nsp, int nhm, int nbetam, int lmaxkb, const int* nh, const int* nhtol,
+                        const int* nhtolm, const int* indv, int nqx, double dq, const double* tab_beta);
+/* ions_base ityp(nat) (1-based), tau(3,nat) in alat units, and the structure-factor phases
+ * eigts1(-nr1:nr1,nat), eigts2, eigts3 of the DENSE grid (PW/src/struct_fact.f90:60-87); after every ionic step. */
+int qeb_set_structure(qeb_ctx* ctx, int nat, const int* ityp, const double* tau, int nr1, int nr2, int nr3,
+                      const void* eigts1, const void* eigts2, const void* eigts3);
+/* init_us_2(npw,npwx,igk,q,nat,tau,ityp,tpiba,omega,nr1,nr2,nr3,eigts1,eigts2,eigts3,mill,g,vkb)
+ * upflib/init_us_2_acc.f90:10-172 (ylmr2.f90, interp_beta): vkb(npwx,nkb) for k-vector q (2pi/alat) with the
+ * npw/npwx/igk/nkb of the last qeb_set_kpoint; it becomes the context's vkb; vkb_out (host or device, may be NULL)
+ * receives a copy. */
+int qeb_init_us_2(qeb_ctx* ctx, const double* q, double tpiba, void* vkb_out);
 
 /* ---- multi-GPU (one process per GPU) ----------------------------------- */
 /* divide_all(comm, m, m_start, m_end, recv_counts, displs)  UtilXlib/divide.f90:55-106.

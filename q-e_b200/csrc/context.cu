@@ -14,6 +14,7 @@
 #include "distfft.h"
 #include "fullfft.h"
 #include "gemm.h"
+#include "uspp.h"
 #include "vloc.h"
 #include "vloc_setup.h"
 
@@ -73,6 +74,23 @@ struct qeb_ctx {
     bool have_k = false;
     int npw = 0, npwx = 0, nkb = 0, gstart = 1;
     DevBuf g2kin_d, vkb_own;
+    bool have_g2kin = false;
+    std::vector<int> igk_h;  // igk of qeb_set_kpoint (k-points), for qeb_g2_kin / qeb_init_us_2
+    // uspp / beta_mod tables of qeb_set_beta_tables
+    bool have_beta = false;
+    int nsp = 0, us_nhm = 0, nbetam = 0, lmaxkb = -1, nqx = 0;
+    double dq = 0.0;
+    std::vector<int> us_nh;
+    DevBuf us_int_d, tab_beta_d, us_scratch_d, us_in_d;
+    UsppTables US;
+    // G-vector list (qeb_set_gvectors) and structure factors (qeb_set_structure)
+    int gv_ngm = 0;
+    DevBuf gv_g_d, gv_mill_d, igk_dev_d;
+    bool igk_dev_ok = false;
+    int st_nat = 0, st_nr1 = 0, st_nr2 = 0, st_nr3 = 0;
+    std::vector<int> st_ityp;
+    std::vector<double> st_tau;
+    DevBuf st_eig_d, st_int_d;
     const cplx* vkb_d = nullptr;
     // V_loc tables
     HostVlocTables H;
@@ -219,7 +237,8 @@ int qeb_destroy(qeb_ctx* c)
     DevBuf* bufs[] = {&c->g2kin_d, &c->vkb_own, &c->tab_d, &c->plan_d, &c->g1_d, &c->g2_d, &c->v_d, &c->vp_d, &c->vpl_d,
                       &c->revx_d, &c->full_plan_d, &c->nlint_d, &c->deeq_d, &c->becp_d, &c->ps_d, &c->part_d,
                       &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage, &c->tabp_d, &c->planp_d,
-                      &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d};
+                      &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d, &c->qq_d, &c->us_int_d, &c->tab_beta_d, &c->us_scratch_d,
+                      &c->us_in_d, &c->gv_g_d, &c->gv_mill_d, &c->igk_dev_d, &c->st_eig_d, &c->st_int_d};
     for (DevBuf* b : bufs) b->release();
     if ((c->nccl_owned || c->nccl_rg_owned) && nccl_api().ok) {
         if (c->nccl && c->nccl_owned) nccl_api().CommDestroy(c->nccl);
@@ -578,7 +597,8 @@ int qeb_set_kpoint(qeb_ctx* c, int npw, int npwx, const int* igk, const double* 
     if (!c) return 1;
     QEB_CUDA(c, cudaSetDevice(c->device));
     if (!c->have_grid) QEB_FAIL(c, 20, "qeb_set_kpoint: qeb_set_grid has not been called");
-    if (npw < 1 || npwx < npw || nkb < 0 || !g2kin || (nkb > 0 && !vkb)) QEB_FAIL(c, 22, "qeb_set_kpoint: bad arguments");
+    // g2kin == NULL: qeb_g2_kin fills it on the device; vkb == NULL with nkb > 0: qeb_init_us_2 builds it on the device
+    if (npw < 1 || npwx < npw || nkb < 0) QEB_FAIL(c, 22, "qeb_set_kpoint: bad arguments");
     if (c->gamma && igk) {
         for (int i = 0; i < npw; ++i)
             if (igk[i] != i + 1) QEB_FAIL(c, 23, "qeb_set_kpoint: gamma_only expects igk(i) = i");
@@ -597,9 +617,16 @@ int qeb_set_kpoint(qeb_ctx* c, int npw, int npwx, const int* igk, const double* 
     if (rc) return rc;
     if ((rc = c->dist ? size_workspaces_dist(c) : size_workspaces(c))) return rc;
     QEB_CUDA(c, c->g2kin_d.ensure((size_t)npw * 8));
-    QEB_CUDA(c, cudaMemcpyAsync(c->g2kin_d.p, g2kin, (size_t)npw * 8,
-                                is_device_ptr(g2kin) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    if (nkb > 0) {
+    c->have_g2kin = g2kin != nullptr;
+    if (g2kin)
+        QEB_CUDA(c, cudaMemcpyAsync(c->g2kin_d.p, g2kin, (size_t)npw * 8,
+                                    is_device_ptr(g2kin) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    c->igk_h.clear();
+    if (igk) c->igk_h.assign(igk, igk + npw);
+    c->igk_dev_ok = false;
+    if (nkb > 0 && !vkb) {
+        c->vkb_d = nullptr;  // until qeb_init_us_2
+    } else if (nkb > 0) {
         if (is_device_ptr(vkb)) {
             c->vkb_d = (const cplx*)vkb;  // borrowed: the caller keeps it alive (like the reference's module array)
         } else {
@@ -689,6 +716,197 @@ int qeb_set_nonlocal(qeb_ctx* c, int nat, int nhm, const int* nh_of_atom, const 
     return 0;
 }
 
+// ---- device-side producers of the per-k-point state ----------
+int qeb_set_gvectors(qeb_ctx* c, int ngm, const double* g, const int* mill)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (ngm < 1 || !g) QEB_FAIL(c, 80, "qeb_set_gvectors: bad arguments");
+    QEB_CUDA(c, c->gv_g_d.ensure((size_t)ngm * 24));
+    QEB_CUDA(c, cudaMemcpyAsync(c->gv_g_d.p, g, (size_t)ngm * 24,
+                                is_device_ptr(g) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    if (mill) {
+        QEB_CUDA(c, c->gv_mill_d.ensure((size_t)ngm * 12));
+        QEB_CUDA(c, cudaMemcpyAsync(c->gv_mill_d.p, mill, (size_t)ngm * 12,
+                                    is_device_ptr(mill) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    }
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->gv_ngm = ngm;
+    return 0;
+}
+
+static int ensure_igk_dev(qeb_ctx* c)
+{
+    if (c->igk_dev_ok || c->igk_h.empty()) return 0;
+    QEB_CUDA(c, c->igk_dev_d.ensure(c->igk_h.size() * 4));
+    QEB_CUDA(c, cudaMemcpyAsync(c->igk_dev_d.p, c->igk_h.data(), c->igk_h.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->igk_dev_ok = true;
+    return 0;
+}
+
+int qeb_g2_kin(qeb_ctx* c, const double* xk, double tpiba2, double qcutz, double ecfixed, double q2sigma, double* g2kin_out)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_k) QEB_FAIL(c, 81, "qeb_g2_kin: qeb_set_kpoint has not been called");
+    if (!c->gv_ngm) QEB_FAIL(c, 82, "qeb_g2_kin: qeb_set_gvectors has not been called");
+    if (!xk) QEB_FAIL(c, 83, "qeb_g2_kin: null xk");
+    for (int v : c->igk_h)
+        if (v < 1 || v > c->gv_ngm) QEB_FAIL(c, 84, "qeb_g2_kin: igk outside the G-vector list");
+    if (c->igk_h.empty() && c->npw > c->gv_ngm) QEB_FAIL(c, 84, "qeb_g2_kin: npw exceeds the G-vector list");
+    int rc = ensure_igk_dev(c);
+    if (rc) return rc;
+    const int* igk_d = c->igk_h.empty() ? nullptr : (const int*)c->igk_dev_d.p;
+    QEB_CUDA(c, launch_g2_kin(c->npw, igk_d, (const double*)c->gv_g_d.p, xk[0], xk[1], xk[2], tpiba2, qcutz, ecfixed,
+                              q2sigma, (double*)c->g2kin_d.p, c->stream));
+    c->have_g2kin = true;
+    if (g2kin_out)
+        QEB_CUDA(c, cudaMemcpyAsync(g2kin_out, c->g2kin_d.p, (size_t)c->npw * 8,
+                                    is_device_ptr(g2kin_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    if (g2kin_out && !is_device_ptr(g2kin_out)) {
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+int qeb_set_beta_tables(qeb_ctx* c, int nsp, int nhm, int nbetam, int lmaxkb, const int* nh, const int* nhtol,
+                        const int* nhtolm, const int* indv, int nqx, double dq, const double* tab_beta)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (nsp < 1 || nhm < 0 || nbetam < 0 || nqx < 4 || !(dq > 0.0) || !nh) QEB_FAIL(c, 85, "qeb_set_beta_tables: bad arguments");
+    if (lmaxkb > 6) QEB_FAIL(c, 85, "qeb_set_beta_tables: lmaxkb > 6 is not supported");
+    if (nhm > 0 && (!nhtol || !nhtolm || !indv || !tab_beta)) QEB_FAIL(c, 85, "qeb_set_beta_tables: null tables");
+    const int lmax2 = (lmaxkb + 1) * (lmaxkb + 1);
+    for (int t = 0; t < nsp; ++t) {
+        if (nh[t] < 0 || nh[t] > nhm) QEB_FAIL(c, 86, "qeb_set_beta_tables: nh out of range");
+        for (int ih = 0; ih < nh[t]; ++ih) {
+            const int k = t * nhm + ih;
+            if (nhtolm[k] < 1 || nhtolm[k] > lmax2 || indv[k] < 1 || indv[k] > nbetam || nhtol[k] < 0)
+                QEB_FAIL(c, 86, "qeb_set_beta_tables: nhtol/nhtolm/indv out of range");
+        }
+    }
+    const size_t nt = (size_t)nhm * nsp;
+    std::vector<int> host((size_t)nsp + 3 * nt + 4, 0);
+    memcpy(host.data(), nh, (size_t)nsp * 4);
+    if (nt) {
+        memcpy(host.data() + nsp, nhtol, nt * 4);
+        memcpy(host.data() + nsp + nt, nhtolm, nt * 4);
+        memcpy(host.data() + nsp + 2 * nt, indv, nt * 4);
+    }
+    QEB_CUDA(c, c->us_int_d.ensure(host.size() * 4));
+    QEB_CUDA(c, cudaMemcpyAsync(c->us_int_d.p, host.data(), host.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    const size_t ntab = (size_t)nqx * nbetam * nsp;
+    QEB_CUDA(c, c->tab_beta_d.ensure(ntab * 8 + 8));
+    if (ntab)
+        QEB_CUDA(c, cudaMemcpyAsync(c->tab_beta_d.p, tab_beta, ntab * 8,
+                                    is_device_ptr(tab_beta) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const int* b = (const int*)c->us_int_d.p;
+    c->US = UsppTables{nsp, nhm, nbetam, lmaxkb, nqx, dq, b, b + nsp, b + nsp + nt, b + nsp + 2 * nt,
+                       (const double*)c->tab_beta_d.p};
+    c->us_nh.assign(nh, nh + nsp);
+    c->nsp = nsp;
+    c->have_beta = true;
+    return 0;
+}
+
+int qeb_set_structure(qeb_ctx* c, int nat, const int* ityp, const double* tau, int nr1, int nr2, int nr3,
+                      const void* eigts1, const void* eigts2, const void* eigts3)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (nat < 1 || !ityp || !tau || nr1 < 1 || nr2 < 1 || nr3 < 1 || !eigts1 || !eigts2 || !eigts3)
+        QEB_FAIL(c, 87, "qeb_set_structure: bad arguments");
+    const size_t n1 = (size_t)(2 * nr1 + 1) * nat, n2 = (size_t)(2 * nr2 + 1) * nat, n3 = (size_t)(2 * nr3 + 1) * nat;
+    QEB_CUDA(c, c->st_eig_d.ensure((n1 + n2 + n3) * 16));
+    cplx* e = (cplx*)c->st_eig_d.p;
+    const void* src[3] = {eigts1, eigts2, eigts3};
+    const size_t cnt[3] = {n1, n2, n3};
+    size_t off = 0;
+    for (int d = 0; d < 3; ++d) {
+        QEB_CUDA(c, cudaMemcpyAsync(e + off, src[d], cnt[d] * 16,
+                                    is_device_ptr(src[d]) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+        off += cnt[d];
+    }
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->st_nat = nat;
+    c->st_nr1 = nr1;
+    c->st_nr2 = nr2;
+    c->st_nr3 = nr3;
+    c->st_ityp.assign(ityp, ityp + nat);
+    c->st_tau.assign(tau, tau + 3 * (size_t)nat);
+    return 0;
+}
+
+int qeb_init_us_2(qeb_ctx* c, const double* q, double tpiba, void* vkb_out)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_k) QEB_FAIL(c, 88, "qeb_init_us_2: qeb_set_kpoint has not been called");
+    if (!c->have_beta) QEB_FAIL(c, 88, "qeb_init_us_2: qeb_set_beta_tables has not been called");
+    if (!c->st_nat) QEB_FAIL(c, 88, "qeb_init_us_2: qeb_set_structure has not been called");
+    if (!c->gv_ngm || !c->gv_mill_d.p) QEB_FAIL(c, 88, "qeb_init_us_2: qeb_set_gvectors (with mill) has not been called");
+    if (!q) QEB_FAIL(c, 88, "qeb_init_us_2: null q");
+    if (c->US.lmaxkb < 0) return 0;  // init_us_2_acc.f90:73
+    for (int v : c->igk_h)
+        if (v < 1 || v > c->gv_ngm) QEB_FAIL(c, 84, "qeb_init_us_2: igk outside the G-vector list");
+    // column offsets in the reference's order: all atoms of type 1, then type 2, ... (:126-159)
+    const int nat = c->st_nat;
+    std::vector<int> jkb0(nat, 0);
+    int jkb = 0;
+    for (int nt = 1; nt <= c->nsp; ++nt)
+        for (int na = 0; na < nat; ++na) {
+            if (c->st_ityp[na] < 1 || c->st_ityp[na] > c->nsp) QEB_FAIL(c, 89, "qeb_init_us_2: ityp out of range");
+            if (c->st_ityp[na] == nt) {
+                jkb0[na] = jkb;
+                jkb += c->us_nh[nt - 1];
+            }
+        }
+    if (jkb != c->nkb) QEB_FAIL(c, 89, "qeb_init_us_2: sum of nh over atoms differs from the nkb of qeb_set_kpoint");
+    const double tpi = 2.0 * 3.14159265358979323846;
+    std::vector<cplx> qph(nat);
+    for (int na = 0; na < nat; ++na) {
+        const double arg = (q[0] * c->st_tau[3 * na] + q[1] * c->st_tau[3 * na + 1] + q[2] * c->st_tau[3 * na + 2]) * tpi;
+        qph[na] = mk(cos(arg), -sin(arg));
+    }
+    // small per-call arrays: ityp | jkb0 | qphase
+    const size_t ib = ((size_t)2 * nat * 4 + 15) & ~(size_t)15;
+    QEB_CUDA(c, c->st_int_d.ensure(ib + (size_t)nat * 16));
+    std::vector<unsigned char> host(ib + (size_t)nat * 16, 0);
+    memcpy(host.data(), c->st_ityp.data(), (size_t)nat * 4);
+    memcpy(host.data() + (size_t)nat * 4, jkb0.data(), (size_t)nat * 4);
+    memcpy(host.data() + ib, qph.data(), (size_t)nat * 16);
+    QEB_CUDA(c, cudaMemcpyAsync(c->st_int_d.p, host.data(), host.size(), cudaMemcpyHostToDevice, c->stream));
+    int rc = ensure_igk_dev(c);
+    if (rc) return rc;
+    const int* igk_d = c->igk_h.empty() ? nullptr : (const int*)c->igk_dev_d.p;
+    const int npw = c->npw, npwx = c->npwx;
+    const int lmax2 = (c->US.lmaxkb + 1) * (c->US.lmaxkb + 1);
+    const size_t nscr = (size_t)npw * (lmax2 + (size_t)c->US.nsp * c->US.nbetam);
+    QEB_CUDA(c, c->us_scratch_d.ensure(nscr * 8 + 8));
+    double* ylm = (double*)c->us_scratch_d.p;
+    double* vq = ylm + (size_t)npw * lmax2;
+    QEB_CUDA(c, launch_us2_ylm_vq(npw, igk_d, (const double*)c->gv_g_d.p, q[0], q[1], q[2], tpiba, c->US, ylm, vq, c->stream));
+    QEB_CUDA(c, c->vkb_own.ensure((size_t)npwx * c->nkb * 16));
+    const cplx* e1 = (const cplx*)c->st_eig_d.p;
+    const cplx* e2 = e1 + (size_t)(2 * c->st_nr1 + 1) * nat;
+    const cplx* e3 = e2 + (size_t)(2 * c->st_nr2 + 1) * nat;
+    const int* ityp_d = (const int*)c->st_int_d.p;
+    QEB_CUDA(c, launch_us2_vkb(npw, npwx, igk_d, (const int*)c->gv_mill_d.p, nat, ityp_d, ityp_d + nat,
+                               (const cplx*)((const char*)c->st_int_d.p + ib), c->st_nr1, c->st_nr2, c->st_nr3, e1, e2, e3,
+                               c->US, ylm, vq, (cplx*)c->vkb_own.p, c->stream));
+    c->vkb_d = (const cplx*)c->vkb_own.p;
+    c->becp_m = 0;
+    if (vkb_out)
+        QEB_CUDA(c, cudaMemcpyAsync(vkb_out, c->vkb_own.p, (size_t)npwx * c->nkb * 16,
+                                    is_device_ptr(vkb_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));  // host staging vectors go out of scope
+    return 0;
+}
+
 // ---- internal pieces ----------------------------------------------------
 static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hpsi, bool kinetic)
 {
@@ -696,6 +914,7 @@ static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hp
     VlocIO io;
     io.psi = psi;
     io.hpsi = hpsi;
+    if (kinetic && !c->have_g2kin) QEB_FAIL(c, 55, "h_psi: no g2kin in the context (qeb_set_kpoint or qeb_g2_kin)");
     io.g2kin = kinetic ? (const double*)c->g2kin_d.p : nullptr;
     io.lda = lda;
     io.n = n;
@@ -835,6 +1054,7 @@ static int h_psi_cols(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx
     if (kinetic && lda > n)
         QEB_CUDA(c, cudaMemset2DAsync(hpsi_d + n, (size_t)lda * 16, 0, (size_t)(lda - n) * 16, m, c->stream));
     if (do_vloc && (rc = run_vloc(c, lda, n, m, psi_d, hpsi_d, kinetic))) return rc;
+    if (do_nl && c->nkb > 0 && !c->vkb_d) QEB_FAIL(c, 56, "h_psi: no vkb in the context (qeb_set_kpoint or qeb_init_us_2)");
     if (do_nl && c->nkb > 0) {
         if (m_total < 0 && (rc = ensure_becp(c, c->nkb, m))) return rc;
         char* becp = (char*)c->becp_d.p + (size_t)col0 * c->nkb * (c->gamma ? 8 : 16);

@@ -61,6 +61,12 @@ def load_library():
     L.qeb_get_becp.argtypes = [P, P, I]
     L.qeb_set_qq.argtypes = [P, I, I, P]
     L.qeb_s_psi.argtypes = [P, I, I, I, P, P]
+    D = ctypes.c_double
+    L.qeb_set_gvectors.argtypes = [P, I, P, P]
+    L.qeb_g2_kin.argtypes = [P, P, D, D, D, D, P]
+    L.qeb_set_beta_tables.argtypes = [P, I, I, I, I, P, P, P, P, I, D, P]
+    L.qeb_set_structure.argtypes = [P, I, P, P, I, I, I, P, P, P]
+    L.qeb_init_us_2.argtypes = [P, P, D, P]
     L.qeb_divide_all.argtypes = [I, I, I, ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_h_psi_bgrp.argtypes = [P, I, I, I, P, P, I, I]
     L.qeb_set_nccl.argtypes = [P, P, I, I]
@@ -75,7 +81,8 @@ def load_library():
                  "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
-                 "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi"):
+                 "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi", "qeb_set_gvectors", "qeb_g2_kin", "qeb_set_beta_tables",
+                 "qeb_set_structure", "qeb_init_us_2"):
         getattr(L, name).restype = I
     _LIB = L
     return L
@@ -228,6 +235,42 @@ class HPsi:
         """qq_at: Fortran qq_at(nhm,nhm,nat), i.e. numpy shape (nat,nhm,nhm) (upflib/uspp.f90); after set_nonlocal."""
         qq = np.ascontiguousarray(qq_at, dtype=np.float64)
         self._ck(self._L.qeb_set_qq(self._h, qq.shape[0], qq.shape[-1] if qq.size else 0, _ptr(qq)), "qeb_set_qq")
+
+    # -- device-side producers of the per-k-point state (SURVEY 8 f2) -------
+    def set_gvectors(self, g, mill=None):
+        """gvect::g (ngm,3) [= Fortran g(3,ngm)] in 2pi/alat and mill (ngm,3)."""
+        g = np.ascontiguousarray(g, dtype=np.float64)
+        self._ck(self._L.qeb_set_gvectors(self._h, g.shape[0], _ptr(g), _ptr(_i32(mill))), "qeb_set_gvectors")
+
+    def g2_kin(self, xk, tpiba2, qcutz=0.0, ecfixed=0.0, q2sigma=1.0, out=None):
+        """g2_kin(ik) (PW/src/g2_kin.f90:10): fills the context's g2kin on the device; returns it when out is given."""
+        xk = np.ascontiguousarray(xk, dtype=np.float64)
+        self._ck(self._L.qeb_g2_kin(self._h, _ptr(xk), tpiba2, qcutz, ecfixed, q2sigma, _ptr(out)), "qeb_g2_kin")
+        return out
+
+    def set_beta_tables(self, us):
+        """us: dict as oracle.uspp_ref.synthetic_uspp (nh, nhm, nbetam, lmaxkb, nhtol/nhtolm/indv (nsp,nhm), nqx, dq,
+        tab_beta (nsp,nbetam,nqx)) - numpy shapes are the Fortran arrays' memory order."""
+        nh = _i32(us["nh"])
+        a, b, c = _i32(us["nhtol"]), _i32(us["nhtolm"]), _i32(us["indv"])
+        tab = np.ascontiguousarray(us["tab_beta"], dtype=np.float64)
+        self._ck(self._L.qeb_set_beta_tables(self._h, nh.size, int(us["nhm"]), int(us["nbetam"]), int(us["lmaxkb"]),
+                                             _ptr(nh), _ptr(a), _ptr(b), _ptr(c), int(us["nqx"]), float(us["dq"]),
+                                             _ptr(tab)), "qeb_set_beta_tables")
+
+    def set_structure(self, ityp, tau, nr, eigts):
+        """ityp (nat,) 1-based, tau (nat,3) alat units, nr = dense grid dims, eigts = three (nat, 2nr_i+1) arrays."""
+        ityp = _i32(ityp)
+        tau = np.ascontiguousarray(tau, dtype=np.float64)
+        e = [np.ascontiguousarray(x, dtype=np.complex128) for x in eigts]
+        self._ck(self._L.qeb_set_structure(self._h, ityp.size, _ptr(ityp), _ptr(tau), nr[0], nr[1], nr[2], _ptr(e[0]),
+                                           _ptr(e[1]), _ptr(e[2])), "qeb_set_structure")
+
+    def init_us_2(self, q, tpiba, out=None):
+        """init_us_2 (upflib/init_us_2_acc.f90:10): builds the context's vkb on the device; out (nkb,npwx) optional."""
+        q = np.ascontiguousarray(q, dtype=np.float64)
+        self._ck(self._L.qeb_init_us_2(self._h, _ptr(q), tpiba, _ptr(out)), "qeb_init_us_2")
+        return out
 
     # -- reference entry points --------------------------------------------
     def s_psi(self, lda, n, m, psi, spsi):

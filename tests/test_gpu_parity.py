@@ -332,3 +332,73 @@ def test_s_psi_needs_becp(mods):
     h.calbec(inp["n"], None, inp["psi"], out, 3, lda=inp["lda"])
     h.s_psi(inp["lda"], inp["n"], 3, inp["psi"], inp["psi"].copy())
     h.close()
+
+
+@pytest.mark.parametrize("name,nsp,lmaxkb,nat", [("si2_small", 1, 1, 2), ("ortho_small", 2, 2, 3), ("si2", 2, 3, 2),
+                                                 ("ortho_small_gamma", 1, 2, 2)])
+def test_g2_kin_init_us_2_on_device(mods, name, nsp, lmaxkb, nat):
+    """g2_kin (PW/src/g2_kin.f90) and init_us_2 (upflib/init_us_2_acc.f90, ylmr2, interp_beta) built on
+    the device, then consumed by h_psi without any vkb / g2kin upload."""
+    qe, D, R, torch = mods
+    from oracle import uspp_ref as U
+
+    d = D.config_descriptor(name)
+    us = U.synthetic_uspp(nsp, lmaxkb, seed=nat)
+    rng = np.random.default_rng(11)
+    tau = rng.uniform(-0.5, 0.5, (nat, 3))
+    ityp = np.array([(i % nsp) + 1 for i in range(nat)], dtype=np.int32)
+    nr_dense = (d.nr1 + 4, d.nr2 + 2, d.nr3 + 6)  # the dense grid only sizes the eigts tables
+    eig = U.eigts(d.bg, tau, nr_dense)
+    tpiba = 2.0 * np.pi / d.alat
+    n = d.npw
+    npwx = n + 3
+    igk = np.arange(1, n + 1, dtype=np.int32) if d.gamma_only else d.igk
+    vkb_ref = U.init_us_2(n, npwx, igk, d.xk, tau, ityp, tpiba, nr_dense, eig, d.mill, d.g, us)
+    nkb = vkb_ref.shape[0]
+    g2_ref = U.g2_kin(d.g, igk, d.xk, d.tpiba2)
+    h = qe.HPsi()
+    h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
+    h.set_kpoint(n, npwx, None if d.gamma_only else d.igk, None, None, nkb, d.gstart)
+    h.set_gvectors(d.g, d.mill)
+    g2 = np.zeros(n)
+    h.g2_kin(d.xk, d.tpiba2, out=g2)
+    assert relerr(g2, g2_ref) < 1e-15
+    g2m = np.zeros(n)  # modified kinetic functional (qcutz > 0)
+    h.g2_kin(d.xk, d.tpiba2, 20.0, 5.0, 0.7, out=g2m)
+    assert relerr(g2m, U.g2_kin(d.g, igk, d.xk, d.tpiba2, 20.0, 5.0, 0.7)) < 1e-14
+    h.g2_kin(d.xk, d.tpiba2)
+    h.set_beta_tables(us)
+    h.set_structure(ityp, tau, nr_dense, eig)
+    vkb = np.full((nkb, npwx), np.nan + 0j)
+    h.init_us_2(d.xk, tpiba, out=vkb)
+    assert relerr(vkb, vkb_ref) < 1e-13
+    assert np.all(vkb[:, n:] == 0)
+    # h_psi consumes the device-built state
+    m = 3
+    nh_at = [int(us["nh"][t - 1]) for t in sorted(ityp)]  # reference column order: atoms grouped by type
+    inp = R.synthetic_inputs(d, m, nh_at, seed=2, lda=npwx)
+    if d.gamma_only:  # the Gamma trick needs real beta(G=0); the synthetic tables do not guarantee it
+        h.close()
+        return
+    ref, _ = R.h_psi(d, npwx, n, m, inp["psi"], inp["vrs"], vkb_ref, inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    h.set_vloc(inp["vrs"])
+    h.set_nonlocal(inp["nh_at"], inp["ofsbeta"], inp["deeq"])
+    out = np.full((m, npwx), np.nan + 0j)
+    h.h_psi(npwx, n, m, inp["psi"], out)
+    assert relerr(out, ref) < TOL
+    h.close()
+
+
+def test_h_psi_without_state_fails(mods):
+    qe, D, R, torch = mods
+    d = D.config_descriptor("si2_small")
+    inp = R.synthetic_inputs(d, 2, [4, 4], poison=False)
+    h = qe.HPsi()
+    h.set_grid(d.nr1, d.nr2, d.nr3, d.nl)
+    h.set_kpoint(d.npw, inp["lda"], d.igk, None, None, 8, d.gstart)  # neither g2kin nor vkb yet
+    h.set_vloc(inp["vrs"])
+    with pytest.raises(qe.QebError):
+        h.h_psi(inp["lda"], d.npw, 2, inp["psi"], inp["psi"].copy())
+    with pytest.raises(qe.QebError):
+        h.g2_kin(d.xk, d.tpiba2)  # no G-vector list
+    h.close()

@@ -183,3 +183,51 @@ def test_s_psi_restatement_hermitian_and_copy():
             assert abs(dot(a, s[1, :n]) - dot(b, s[0, :n])) < 1e-12
         else:
             assert abs(np.vdot(a, s[1, :n]) - np.conj(np.vdot(b, s[0, :n]))) < 1e-12
+
+
+def test_ylmr2_restatement_matches_scipy():
+    """oracle.uspp_ref.ylmr2 (upflib/ylmr2.f90) against scipy's complex harmonics: m=0 -> Y_l0, m>0 -> sqrt2 Re Y_lm
+    (cos slot) and sqrt2 Im Y_lm (sin slot)."""
+    from scipy import special
+
+    from oracle import uspp_ref as U
+
+    rng = np.random.default_rng(0)
+    g = rng.standard_normal((200, 3))
+    g[0] = [0.0, 0.0, 1.3]
+    g[1] = [0.0, -0.7, 0.2]
+    gg = (g * g).sum(1)
+    lmax = 4
+    y = U.ylmr2((lmax + 1) ** 2, g, gg)
+    theta = np.arccos(g[:, 2] / np.sqrt(gg))
+    phi = np.arctan2(g[:, 1], g[:, 0])
+    sph = getattr(special, "sph_harm_y", None)
+    for l in range(lmax + 1):
+        for m in range(l + 1):
+            Y = sph(l, m, theta, phi) if sph else special.sph_harm(m, l, phi, theta)
+            if m == 0:
+                assert np.abs(y[:, l * l] - Y.real).max() < 1e-13
+            else:
+                assert np.abs(y[:, l * l + 2 * m - 1] - np.sqrt(2.0) * Y.real).max() < 1e-13
+                assert np.abs(y[:, l * l + 2 * m] - np.sqrt(2.0) * Y.imag).max() < 1e-13
+
+
+def test_init_us_2_restatement_translation_phase():
+    """moving an atom by a lattice vector leaves vkb unchanged; moving it by tau multiplies by exp(-i(k+G).tau)."""
+    from oracle import uspp_ref as U
+
+    d = D.config_descriptor("si2_small")
+    us = U.synthetic_uspp(1, 2, seed=1)
+    tpiba = 2.0 * np.pi / d.alat
+    nr = (d.nr1, d.nr2, d.nr3)
+    tau0 = np.array([[0.1, 0.2, -0.05]])
+    shift = np.array([0.03, -0.02, 0.07])
+    vk = []
+    for tau in (tau0, tau0 + d.at[:, 0][None, :], tau0 + shift[None, :]):
+        e = U.eigts(d.bg, tau, nr)
+        vk.append(U.init_us_2(d.npw, d.npw, d.igk, d.xk, tau, [1], tpiba, nr, e, d.mill, d.g, us))
+    assert np.abs(vk[0] - vk[1]).max() < 1e-12 * np.abs(vk[0]).max() * 10
+    kg = d.g[d.igk - 1] + d.xk[None, :]
+    ph = np.exp(-1j * 2.0 * np.pi * (kg @ shift))
+    assert np.abs(vk[2] - vk[0] * ph[None, :]).max() < 1e-12
+    assert np.abs(U.g2_kin(d.g, d.igk, d.xk, d.tpiba2) - d.g2kin).max() == 0.0
