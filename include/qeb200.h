@@ -159,6 +159,28 @@ int qeb_set_structure(qeb_ctx* ctx, int nat, const int* ityp, const double* tau,
  * receives a copy. */
 int qeb_init_us_2(qeb_ctx* ctx, const double* q, double tpiba, void* vkb_out);
 
+/* ---- block-Davidson building blocks ------------------------ */
+/* The work arrays of cegterg/regterg (psi, hpsi, spsi: npwx x nvecx) live on the device in a GPU run; these entry
+ * points take DEVICE pointers for them and host or device pointers for the small reduced matrices. gamma_only and
+ * gstart are those of the context (qeb_set_grid / qeb_set_kpoint).
+ *
+ * g_psi(lda,n,m,npol,psi,e)  PW/src/g_psi.f90:10-70 (TEST_NEW_PRECONDITIONING branch, the one the file defines):
+ * psi(i,k) /= 0.5 (1 + x + sqrt(1 + (x-1)^2)), x = h_diag(i) - e(k) s_diag(i); h_diag/s_diag = g_psi_mod
+ * (set once per k-point with qeb_set_g_psi_diag). */
+int qeb_set_g_psi_diag(qeb_ctx* ctx, int n, const double* h_diag, const double* s_diag);
+int qeb_g_psi(qeb_ctx* ctx, int lda, int n, int m, int npol, void* psi, const double* e);
+/* ew(k) = <a_k|b_k> over n plane waves: MYDDOT(2*npw, a_k, b_k) (cegterg.f90:421); Gamma: 2*dot - a(1)b(1) when
+ * gstart == 2 (regterg.f90:358-361). */
+int qeb_col_dot(qeb_ctx* ctx, int n, int m, const void* a, int lda, const void* b, int ldb, double* out);
+/* hc/sc = psi^H hpsi (ZGEMM 'C','N', cegterg.f90:209-229, 478-499); Gamma: hr = 2 psi^T hpsi - psi(1) hpsi(1)
+ * (DGEMM + DGER, regterg.f90:203-221). C(ka,mb) complex (k) / real (Gamma), leading dimension ldc. */
+int qeb_dav_gemm_cn(qeb_ctx* ctx, int n, const void* A, int lda, int ka, const void* B, int ldb, int mb, void* C,
+                    int ldc);
+/* psi_new = psi vc (ZGEMM 'N','N', cegterg.f90:353-395, 588-632; Gamma: DGEMM with real B on the 2*npwx real view):
+ * C(1:n,1:m) = A(1:n,1:k) B(1:k,1:m) (+ C when accumulate != 0). */
+int qeb_dav_gemm_nn(qeb_ctx* ctx, int n, const void* A, int lda, int k, const void* B, int ldb, int m, void* C,
+                    int ldc, int accumulate);
+
 /* ---- multi-GPU (one process per GPU) ----------------------------------- */
 /* divide_all(comm, m, m_start, m_end, recv_counts, displs)  UtilXlib/divide.f90:55-106.
  * 0-based start/end(exclusive) of group `me` of `nproc`. */

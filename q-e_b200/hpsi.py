@@ -67,6 +67,11 @@ def load_library():
     L.qeb_set_beta_tables.argtypes = [P, I, I, I, I, P, P, P, P, I, D, P]
     L.qeb_set_structure.argtypes = [P, I, P, P, I, I, I, P, P, P]
     L.qeb_init_us_2.argtypes = [P, P, D, P]
+    L.qeb_set_g_psi_diag.argtypes = [P, I, P, P]
+    L.qeb_g_psi.argtypes = [P, I, I, I, I, P, P]
+    L.qeb_col_dot.argtypes = [P, I, I, P, I, P, I, P]
+    L.qeb_dav_gemm_cn.argtypes = [P, I, P, I, I, P, I, I, P, I]
+    L.qeb_dav_gemm_nn.argtypes = [P, I, P, I, I, P, I, I, P, I, I]
     L.qeb_divide_all.argtypes = [I, I, I, ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_h_psi_bgrp.argtypes = [P, I, I, I, P, P, I, I]
     L.qeb_set_nccl.argtypes = [P, P, I, I]
@@ -82,7 +87,8 @@ def load_library():
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
                  "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi", "qeb_set_gvectors", "qeb_g2_kin", "qeb_set_beta_tables",
-                 "qeb_set_structure", "qeb_init_us_2"):
+                 "qeb_set_structure", "qeb_init_us_2", "qeb_set_g_psi_diag", "qeb_g_psi", "qeb_col_dot",
+                 "qeb_dav_gemm_cn", "qeb_dav_gemm_nn"):
         getattr(L, name).restype = I
     _LIB = L
     return L
@@ -271,6 +277,32 @@ class HPsi:
         q = np.ascontiguousarray(q, dtype=np.float64)
         self._ck(self._L.qeb_init_us_2(self._h, _ptr(q), tpiba, _ptr(out)), "qeb_init_us_2")
         return out
+
+    # -- block-Davidson building blocks; big arrays are torch CUDA tensors ---------
+    def set_g_psi_diag(self, h_diag, s_diag):
+        h_diag = np.ascontiguousarray(h_diag, dtype=np.float64)
+        s_diag = np.ascontiguousarray(s_diag, dtype=np.float64)
+        self._ck(self._L.qeb_set_g_psi_diag(self._h, h_diag.size, _ptr(h_diag), _ptr(s_diag)), "qeb_set_g_psi_diag")
+
+    def g_psi(self, lda, n, m, npol, psi, e):
+        """g_psi(lda,n,m,npol,psi,e) (PW/src/g_psi.f90:10): psi (device) is preconditioned in place."""
+        e = np.ascontiguousarray(e, dtype=np.float64) if isinstance(e, np.ndarray) else e
+        self._ck(self._L.qeb_g_psi(self._h, lda, n, m, npol, _ptr(psi), _ptr(e)), "qeb_g_psi")
+        return psi
+
+    def col_dot(self, n, m, a, lda, b, ldb):
+        out = np.zeros(m)
+        self._ck(self._L.qeb_col_dot(self._h, n, m, _ptr(a), lda, _ptr(b), ldb, _ptr(out)), "qeb_col_dot")
+        return out
+
+    def dav_gemm_cn(self, n, A, lda, ka, B, ldb, mb, C, ldc):
+        self._ck(self._L.qeb_dav_gemm_cn(self._h, n, _ptr(A), lda, ka, _ptr(B), ldb, mb, _ptr(C), ldc), "qeb_dav_gemm_cn")
+        return C
+
+    def dav_gemm_nn(self, n, A, lda, k, B, ldb, m, C, ldc, accumulate=False):
+        self._ck(self._L.qeb_dav_gemm_nn(self._h, n, _ptr(A), lda, k, _ptr(B), ldb, m, _ptr(C), ldc, int(accumulate)),
+                 "qeb_dav_gemm_nn")
+        return C
 
     # -- reference entry points --------------------------------------------
     def s_psi(self, lda, n, m, psi, spsi):

@@ -402,3 +402,87 @@ def test_h_psi_without_state_fails(mods):
     with pytest.raises(qe.QebError):
         h.g2_kin(d.xk, d.tpiba2)  # no G-vector list
     h.close()
+
+
+@pytest.mark.parametrize("name", ["ortho_small", "ortho_small_gamma"])
+def test_davidson_building_blocks(mods, name):
+    """the device pieces of cegterg/regterg - reduced matrices psi^H hpsi (cegterg.f90:209, regterg.f90:203-205),
+    basis update psi vc (:353-395), g_psi preconditioner (PW/src/g_psi.f90) and the correction norms (:421) - against
+    numpy, composed into one Rayleigh-Ritz step on the oracle's H."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    nb, notcnv = 7, 3
+    inp = R.synthetic_inputs(d, nb, [8, 8, 8], seed=21, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    qq = R.synthetic_qq([8, 8, 8], seed=21)
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    h.set_qq(qq)
+    psi = inp["psi"].copy()
+    psi[:, n:] = 0
+    psi_t = torch.from_numpy(psi).cuda()
+    hpsi_t, spsi_t = torch.empty_like(psi_t), torch.empty_like(psi_t)
+    h.h_psi(lda, n, nb, psi_t, hpsi_t)
+    h.s_psi(lda, n, nb, psi_t, spsi_t)
+    torch.cuda.synchronize()
+    href, becp = R.h_psi(d, lda, n, nb, psi, inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    sref = R.s_psi(d, lda, n, nb, psi, becp, inp["vkb"], qq, inp["nh_at"], inp["ofsbeta"])
+
+    def proj(a, b):  # reference convention: C(i,j) = <a_i|b_j>, stored Fortran (ka, mb) = numpy (mb, ka)
+        if d.gamma_only:
+            c = 2.0 * (b[:, :n].real @ a[:, :n].real.T + b[:, :n].imag @ a[:, :n].imag.T)
+            if d.gstart == 2:
+                c -= np.outer(b[:, 0].real, a[:, 0].real)
+            return c
+        return b[:, :n] @ np.conj(a[:, :n]).T
+
+    dt = np.float64 if d.gamma_only else np.complex128
+    nvecx = nb + 2  # leading dimension of the reduced matrices, as in cegterg (hc(nvecx,nvecx))
+    hc = np.zeros((nb, nvecx), dtype=dt)
+    sc = np.zeros((nb, nvecx), dtype=dt)
+    h.dav_gemm_cn(n, psi_t, lda, nb, hpsi_t, lda, nb, hc, nvecx)
+    h.dav_gemm_cn(n, psi_t, lda, nb, spsi_t, lda, nb, sc, nvecx)
+    assert relerr(hc[:, :nb], proj(psi, href)) < TOL
+    assert relerr(sc[:, :nb], proj(psi, sref)) < TOL
+    assert np.all(hc[:, nb:] == 0)
+    # Rayleigh-Ritz on the host (cdiaghg / rdiaghg are LAPACK on small matrices), basis update on the device
+    import scipy.linalg as sl
+
+    Hm, Sm = hc[:, :nb].T, sc[:, :nb].T  # numpy (mb,ka) -> matrix [i,j]
+    Hm, Sm = 0.5 * (Hm + Hm.conj().T), 0.5 * (Sm + Sm.conj().T)
+    ew, vc = sl.eigh(Hm, Sm)
+    vcF = np.ascontiguousarray(vc[:, :notcnv].T)  # Fortran vc(nb, notcnv) memory
+    new_t = torch.full((notcnv, lda, 2), float("nan"), device="cuda", dtype=torch.float64)
+    new_t[:, n:] = 7.0
+    h.dav_gemm_nn(n, spsi_t, lda, nb, vcF, nb, notcnv, new_t, lda)
+    torch.cuda.synchronize()
+    got = torch.view_as_complex(new_t).cpu().numpy()
+    want = vc[:, :notcnv].T @ sref[:, :n]
+    assert relerr(got[:, :n], want) < TOL
+    assert np.all(got[:, n:] == 7.0 + 7.0j)  # rows beyond n untouched
+    # psi_corr = hpsi vc - ew spsi vc (cegterg.f90:353-395): accumulate form
+    corr_t = new_t.clone()
+    corr_t[:, :n] *= torch.from_numpy(-ew[:notcnv]).cuda()[:, None, None]
+    h.dav_gemm_nn(n, hpsi_t, lda, nb, vcF, nb, notcnv, corr_t, lda, accumulate=True)
+    torch.cuda.synchronize()
+    wantc = vc[:, :notcnv].T @ href[:, :n] - ew[:notcnv, None] * want
+    gotc = torch.view_as_complex(corr_t).cpu().numpy()
+    assert np.abs(gotc[:, :n] - wantc).max() < 1e-11 * max(np.abs(href).max(), 1.0)
+    # g_psi + norms
+    rng = np.random.default_rng(3)
+    h_diag, s_diag = rng.uniform(0.5, 30.0, n), rng.uniform(0.8, 1.2, n)
+    h.set_g_psi_diag(h_diag, s_diag)
+    before = gotc.copy()
+    h.g_psi(lda, n, notcnv, 1, corr_t, ew[:notcnv].copy())
+    torch.cuda.synchronize()
+    x = h_diag[None, :] - ew[:notcnv, None] * s_diag[None, :]
+    denm = 0.5 * (1.0 + x + np.sqrt(1.0 + (x - 1.0) * (x - 1.0)))
+    after = torch.view_as_complex(corr_t).cpu().numpy()
+    assert relerr(after[:, :n], before[:, :n] / denm) < 1e-14
+    nrm = h.col_dot(n, notcnv, corr_t, lda, corr_t, lda)
+    a = after[:, :n]
+    ref_n = (np.abs(a) ** 2).sum(1)
+    if d.gamma_only:
+        ref_n = 2.0 * ref_n - (a[:, 0].real ** 2 if d.gstart == 2 else 0.0)
+    assert relerr(nrm, ref_n) < 1e-13
+    h.close()
