@@ -159,6 +159,12 @@ int qeb_set_structure(qeb_ctx* ctx, int nat, const int* ityp, const double* tau,
  * receives a copy. */
 int qeb_init_us_2(qeb_ctx* ctx, const double* q, double tpiba, void* vkb_out);
 
+/* sum_band, density part (PW/src/sum_band.f90:326-437 Gamma, :440-647 k; get_rho_k :650-671, get_rho_gamma
+ * :674-696): rho(1:nnr) (INOUT, smooth grid, x fastest) += sum_b w(b) |psi_b(r)|^2 for the m bands of evc(lda,m),
+ * w(b) = wg(b,ik)/omega; Gamma: two bands per transform, w1 Re^2 + w2 Im^2. Uses grid / k-point of the context.
+ * (becsum, the augmentation part, and the k/spin loops stay in the caller.) */
+int qeb_sum_band_rho(qeb_ctx* ctx, int lda, int n, int m, const void* evc, const double* w, double* rho);
+
 /* ---- block-Davidson building blocks ------------------------ */
 /* The work arrays of cegterg/regterg (psi, hpsi, spsi: npwx x nvecx) live on the device in a GPU run; these entry
  * points take DEVICE pointers for them and host or device pointers for the small reduced matrices. gamma_only and

@@ -108,6 +108,39 @@ def vloc_psi_gamma(d: Descriptor, lda: int, n: int, m: int, psi: np.ndarray, v: 
     return hpsi
 
 
+def sum_band_rho(d: Descriptor, lda: int, n: int, m: int, evc: np.ndarray, w: np.ndarray, rho: np.ndarray):
+    """Density part of sum_band: rho (nnr, INOUT) += sum_b w[b] |psi_b(r)|^2, w[b] = wg(b,ik)/omega.
+    k: wave_g2r + get_rho_k per band (PW/src/sum_band.f90:578-593, :650-671); Gamma: two bands per transform,
+    rho += w1 Re^2 + w2 Im^2, w2 = w1 for the odd last band (:376-394, :674-696)."""
+    nr = (d.nr1, d.nr2, d.nr3)
+    if not d.gamma_only:
+        idx = d.nl[d.igk[:n] - 1] - 1
+        for b in range(m):
+            box = np.zeros(d.nnr, dtype=np.complex128)
+            box[idx] = evc[b, :n]
+            box = cfft3ds(box, nr, +1, d.isind, d.iplw)
+            rho += w[b] * (box.real**2 + box.imag**2)
+        return rho
+    inl, inlm = d.nl[:n] - 1, d.nlm[:n] - 1
+    b = 0
+    while b < m:
+        box = np.zeros(d.nnr, dtype=np.complex128)
+        if b + 1 < m:
+            c1, c2 = evc[b, :n], evc[b + 1, :n]
+            box[inl] = c1 + 1j * c2
+            box[inlm] = np.conj(c1 - 1j * c2)
+            w1, w2 = w[b], w[b + 1]
+        else:
+            c1 = evc[b, :n]
+            box[inl] = c1
+            box[inlm] = np.conj(c1)
+            w1 = w2 = w[b]
+        box = cfft3ds(box, nr, +1, d.isind, d.iplw)
+        rho += w1 * box.real**2 + w2 * box.imag**2
+        b += 2
+    return rho
+
+
 # ----------------------------------------------------------------------------
 # Nonlocal
 # ----------------------------------------------------------------------------

@@ -93,7 +93,7 @@ struct qeb_ctx {
     std::vector<double> st_tau;
     DevBuf st_eig_d, st_int_d;
     // g_psi_mod::h_diag / s_diag (qeb_set_g_psi_diag) and small staging of the Davidson helpers
-    DevBuf gpsi_d, dav_small_d;
+    DevBuf gpsi_d, dav_small_d, rho_d, wts_d;
     int gpsi_n = 0;
     const cplx* vkb_d = nullptr;
     // V_loc tables
@@ -242,7 +242,7 @@ int qeb_destroy(qeb_ctx* c)
                       &c->revx_d, &c->full_plan_d, &c->nlint_d, &c->deeq_d, &c->becp_d, &c->ps_d, &c->part_d,
                       &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage, &c->tabp_d, &c->planp_d,
                       &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d, &c->qq_d, &c->us_int_d, &c->tab_beta_d, &c->us_scratch_d,
-                      &c->us_in_d, &c->gv_g_d, &c->gv_mill_d, &c->igk_dev_d, &c->st_eig_d, &c->st_int_d, &c->gpsi_d, &c->dav_small_d};
+                      &c->us_in_d, &c->gv_g_d, &c->gv_mill_d, &c->igk_dev_d, &c->st_eig_d, &c->st_int_d, &c->gpsi_d, &c->dav_small_d, &c->rho_d, &c->wts_d};
     for (DevBuf* b : bufs) b->release();
     if ((c->nccl_owned || c->nccl_rg_owned) && nccl_api().ok) {
         if (c->nccl && c->nccl_owned) nccl_api().CommDestroy(c->nccl);
@@ -909,6 +909,54 @@ int qeb_init_us_2(qeb_ctx* c, const double* q, double tpiba, void* vkb_out)
                                     is_device_ptr(vkb_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
     QEB_CUDA(c, cudaStreamSynchronize(c->stream));  // host staging vectors go out of scope
     return 0;
+}
+
+// sum_band, density part (PW/src/sum_band.f90:326-437 Gamma, :440-647 k): rho(r) += sum_b w_b |psi_b(r)|^2 for the
+// m bands of evc, w_b = wg(b,ik)/omega. The reference loops wave_g2r + get_rho_k/get_rho_gamma per band (group);
+// here: scatter + z pass, y pass, then one kernel that x-transforms every box of a batch and accumulates.
+static int check_call(qeb_ctx* c, int lda, int n, int m, const void* psi, const void* hpsi, const char* who);
+int qeb_sum_band_rho(qeb_ctx* c, int lda, int n, int m, const void* evc, const double* w, double* rho)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, evc, rho, "qeb_sum_band_rho");
+    if (rc) return rc;
+    if (!w) QEB_FAIL(c, 97, "qeb_sum_band_rho: null weights");
+    if (c->dist) QEB_FAIL(c, 97, "qeb_sum_band_rho: the slab-distributed descriptor is not supported yet");
+    if (m == 0) return 0;
+    const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
+    const void* psi_d;
+    if ((rc = stage_in(c, evc, (size_t)lda * m * 16, c->psi_stage, &psi_d))) return rc;
+    const void* w_d;
+    if ((rc = stage_in(c, w, (size_t)m * 8, c->wts_d, &w_d))) return rc;
+    const bool rho_dev = is_device_ptr(rho);
+    double* r = rho;
+    if (!rho_dev) {
+        QEB_CUDA(c, c->rho_d.ensure(nnr * 8));
+        r = (double*)c->rho_d.p;
+        QEB_CUDA(c, cudaMemcpyAsync(r, rho, nnr * 8, cudaMemcpyHostToDevice, c->stream));
+    }
+    VlocIO io;
+    io.psi = (const cplx*)psi_d;
+    io.hpsi = nullptr;
+    io.g2kin = nullptr;
+    io.lda = lda;
+    io.n = n;
+    io.nbands = m;
+    io.gamma = c->gamma ? 1 : 0;
+    const int nboxes = c->gamma ? (m + 1) / 2 : m;
+    for (int b0 = 0; b0 < nboxes; b0 += c->batch) {  // one stream: batches add to the same rho
+        const int nb = std::min(c->batch, nboxes - b0);
+        io.band0 = c->gamma ? 2 * b0 : b0;
+        QEB_CUDA(c, vloc_launch_density(c->T, io, c->cfg, nb, (const double*)w_d, r, c->stream));
+    }
+    if (!rho_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(rho, r, nnr * 8, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    if (!is_device_ptr(evc) || !is_device_ptr(w)) QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return finish(c);
 }
 
 // ---- block-Davidson building blocks ---------------------------

@@ -60,6 +60,25 @@ __global__ void __launch_bounds__(256) k_vloc_xfus(const __grid_constant__ VlocT
 
 
 
+// density accumulation: x inverse of every box of the batch + |psi(r)|^2 weights, one CTA per line tile
+__global__ void __launch_bounds__(256) k_vloc_xacc(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io,
+                                                   const double* __restrict__ w, int nboxes, double* __restrict__ rho)
+{
+    QEB_SMEM;
+    double* racc = reinterpret_cast<double*>(smem + (size_t)t.nr1 * t.TX);
+    int* irev = reinterpret_cast<int*>(racc + (size_t)t.nr1 * t.TX);
+    for (int i = threadIdx.x; i < t.nr1; i += blockDim.x) irev[t.px.rev[i]] = i;
+    xacc_zero_phase(threadIdx.x, blockDim.x, t, racc);
+    __syncthreads();
+    const int np = t.px.npass;
+    for (int box = 0; box < nboxes; ++box)
+        for (int ph = 0; ph < np; ++ph) {
+            xacc_phase(ph, threadIdx.x, blockDim.x, t, io, w, blockIdx.x, box, smem, racc);
+            __syncthreads();
+        }
+    xacc_flush_phase(threadIdx.x, blockDim.x, t, blockIdx.x, irev, racc, rho);
+}
+
 // ---- fast variants (vloc_fast_inst.cuh, instantiated in vloc_fast_<N>.cu) ----
 #define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200) X(SP200b)
 #define X(PL) extern template struct FastLaunch<PL>;
@@ -173,6 +192,7 @@ cudaError_t vloc_init_attrs(size_t max_smem)
     if ((e = cudaFuncSetAttribute(k_vloc_yinv, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
     if ((e = cudaFuncSetAttribute(k_vloc_yfwd, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
     if ((e = cudaFuncSetAttribute(k_vloc_xfus, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
+    if ((e = cudaFuncSetAttribute(k_vloc_xacc, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
 #define X(PL) FastLaunch<PL>::attrs(s);
     QEB_FOR_PLANS(X)
 #undef X
@@ -224,6 +244,20 @@ cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr
 {
     dim3 grid((nr3 + 31) / 32, nr2);
     k_prepare_v<<<grid, 256, (size_t)32 * (nr1 + 1) * 8, st>>>(v, vp, rev_x, nr1, nr2, nr3, scale);
+    return cudaGetLastError();
+}
+
+cudaError_t vloc_launch_density(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
+                                const double* w_dev, double* rho_dev, cudaStream_t st)
+{
+    if (nboxes <= 0 || t.nxw <= 0) return cudaSuccess;
+    cudaError_t e;
+    if ((e = vloc_launch_zpass(true, t, io, cfg, nboxes, st)) != cudaSuccess) return e;
+    if (!launch_y(true, t, cfg, nboxes, st))
+        k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
+    const size_t smem = cfg.smem_x + (size_t)t.nr1 * t.TX * 8 + (size_t)t.nr1 * 4 + 16;
+    if (smem > cfg.max_smem) return cudaErrorInvalidConfiguration;
+    k_vloc_xacc<<<t.ntx, cfg.threads_x, smem, st>>>(t, io, w_dev, nboxes, rho_dev);
     return cudaGetLastError();
 }
 

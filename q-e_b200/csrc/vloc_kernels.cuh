@@ -433,4 +433,74 @@ QEB_HD void xfus_phase(int ph, int tid, int nthr, const VlocTables& t, int tile,
     }
 }
 
+// ---------------------------------------------------------------------------
+// Density accumulation (sum_band, PW/src/sum_band.f90:376-394 Gamma, :578-593 k; get_rho_k :650-671,
+// get_rho_gamma :674-696): P1 and P2 as above, then per line tile the x inverse transform of every box of the batch
+// and rho(r) += w1 |psi(r)|^2 (k) / w1 Re^2 + w2 Im^2 (Gamma, two bands per box), accumulated in shared memory over
+// the boxes and added to rho once per batch. block = line tile. smem: tile nr1*TX complex, racc nr1*TX doubles.
+// ---------------------------------------------------------------------------
+struct RhoAccDst {  // last x-DIF pass: position -> accumulator (each (pos,line) is owned by one thread)
+    double* racc;
+    int ld;
+    double w1, w2;
+    QEB_HD void store(int line, int pos, cplx v) const { racc[pos * ld + line] += w1 * (v.x * v.x) + w2 * (v.y * v.y); }
+};
+
+QEB_HD void xacc_weights(const VlocIO& io, const double* w, int box, double* w1, double* w2)
+{
+    if (!io.gamma) {
+        *w1 = *w2 = w[io.band0 + box];
+    } else {
+        const int b1 = io.band0 + 2 * box;
+        *w1 = w[b1];
+        *w2 = (b1 + 1) < io.nbands ? w[b1 + 1] : w[b1];  // sum_band.f90:385-391
+    }
+}
+
+QEB_HD void xacc_zero_phase(int tid, int nthr, const VlocTables& t, double* racc)
+{
+    for (int i = tid; i < t.nr1 * t.TX; i += nthr) racc[i] = 0.0;
+}
+
+QEB_HD void xacc_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, const double* w, int tile,
+                       int box, cplx* smem, double* racc)
+{
+    const int TX = t.TX;
+    const int p0 = tile * TX;
+    const int nl = (t.npos - p0) < TX ? (t.npos - p0) : TX;
+    const FastDiv dnl = pick_div(nl, TX, t.divTX, t.divTXlast);
+    const int np = t.px.npass;
+    SmemTile wk{smem, TX};
+    G2XSrc g{t.g2 + (size_t)box * t.g2_box, t.xmap, t.npos, p0};
+    NoMid nm;
+    const PassDesc pd = pass_of(t.px, ph);
+    if (ph == np - 1) {
+        RhoAccDst acc{racc, TX, 0.0, 0.0};
+        xacc_weights(io, w, box, &acc.w1, &acc.w2);
+        if (np == 1)
+            fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.px.tw, +1.0, g, acc, nm);
+        else
+            fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.px.tw, +1.0, wk, acc, nm);
+    } else if (ph == 0) {
+        fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.px.tw, +1.0, g, wk, nm);
+    } else {
+        fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.px.tw, +1.0, wk, wk, nm);
+    }
+}
+
+// rho(x, y, z) += racc[pos(x)][line], line p0+l = y*nr3 + z; irev[x] = position holding x after the DIF
+QEB_HD void xacc_flush_phase(int tid, int nthr, const VlocTables& t, int tile, const int* irev, const double* racc,
+                             double* rho)
+{
+    const int TX = t.TX;
+    const int p0 = tile * TX;
+    const int nl = (t.npos - p0) < TX ? (t.npos - p0) : TX;
+    for (int i = tid; i < nl * t.nr1; i += nthr) {
+        const int line = i / t.nr1, x = i - line * t.nr1;
+        const int p = p0 + line;
+        const int y = p / t.nr3, z = p - y * t.nr3;
+        rho[x + (size_t)t.nr1 * (y + (size_t)t.nr2 * z)] += racc[irev[x] * TX + line];
+    }
+}
+
 }  // namespace qeb

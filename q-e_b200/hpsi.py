@@ -67,6 +67,7 @@ def load_library():
     L.qeb_set_beta_tables.argtypes = [P, I, I, I, I, P, P, P, P, I, D, P]
     L.qeb_set_structure.argtypes = [P, I, P, P, I, I, I, P, P, P]
     L.qeb_init_us_2.argtypes = [P, P, D, P]
+    L.qeb_sum_band_rho.argtypes = [P, I, I, I, P, P, P]
     L.qeb_set_g_psi_diag.argtypes = [P, I, P, P]
     L.qeb_g_psi.argtypes = [P, I, I, I, I, P, P]
     L.qeb_col_dot.argtypes = [P, I, I, P, I, P, I, P]
@@ -88,7 +89,7 @@ def load_library():
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
                  "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi", "qeb_set_gvectors", "qeb_g2_kin", "qeb_set_beta_tables",
                  "qeb_set_structure", "qeb_init_us_2", "qeb_set_g_psi_diag", "qeb_g_psi", "qeb_col_dot",
-                 "qeb_dav_gemm_cn", "qeb_dav_gemm_nn"):
+                 "qeb_dav_gemm_cn", "qeb_dav_gemm_nn", "qeb_sum_band_rho"):
         getattr(L, name).restype = I
     _LIB = L
     return L
@@ -277,6 +278,13 @@ class HPsi:
         q = np.ascontiguousarray(q, dtype=np.float64)
         self._ck(self._L.qeb_init_us_2(self._h, _ptr(q), tpiba, _ptr(out)), "qeb_init_us_2")
         return out
+
+    def sum_band_rho(self, lda, n, m, evc, w, rho):
+        """density part of sum_band (PW/src/sum_band.f90:326-647): rho += sum_b w[b] |psi_b(r)|^2, w = wg/omega."""
+        if isinstance(w, np.ndarray):
+            w = np.ascontiguousarray(w, dtype=np.float64)
+        self._ck(self._L.qeb_sum_band_rho(self._h, lda, n, m, _ptr(evc), _ptr(w), _ptr(rho)), "qeb_sum_band_rho")
+        return rho
 
     # -- block-Davidson building blocks (SURVEY 8 f3); big arrays are torch CUDA tensors ---------
     def set_g_psi_diag(self, h_diag, s_diag):

@@ -486,3 +486,50 @@ def test_davidson_building_blocks(mods, name):
         ref_n = 2.0 * ref_n - (a[:, 0].real ** 2 if d.gstart == 2 else 0.0)
     assert relerr(nrm, ref_n) < 1e-13
     h.close()
+
+
+@pytest.mark.parametrize("name", SMALL + ["si2", "al4"])
+@pytest.mark.parametrize("m,batch", [(1, 1), (5, 2), (8, 3)])
+def test_sum_band_rho(mods, name, m, batch):
+    """density part of sum_band (PW/src/sum_band.f90:326-647): rho += sum_b w_b |psi_b(r)|^2; host and device arrays;
+    the integral of rho equals sum_b w_b <psi_b|psi_b> nnr (Parseval, unscaled G->R transform)."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    inp = R.synthetic_inputs(d, m, [4, 4], seed=m, poison=True)
+    lda, n = inp["lda"], inp["n"]
+    rng = np.random.default_rng(m)
+    w = rng.uniform(0.0, 2.0, m)
+    rho0 = rng.uniform(0.0, 1.0, d.nnr)
+    ref = R.sum_band_rho(d, lda, n, m, inp["psi"], w, rho0.copy())
+    h = qe.HPsi(batch=batch)
+    h.setup_from(d, inp)
+    rho = rho0.copy()
+    h.sum_band_rho(lda, n, m, inp["psi"], w, rho)
+    assert relerr(rho, ref) < 1e-12
+    psi = inp["psi"][:, :n]
+    if d.gamma_only:
+        nrm = 2.0 * (np.abs(psi) ** 2).sum(1) - (np.abs(psi[:, 0]) ** 2 if d.gstart == 2 else 0.0)
+    else:
+        nrm = (np.abs(psi) ** 2).sum(1)
+    assert abs((rho - rho0).sum() / d.nnr - (w * nrm).sum()) < 1e-11
+    psi_t = torch.from_numpy(np.nan_to_num(inp["psi"])).cuda()
+    rho_t = torch.from_numpy(rho0.copy()).cuda()
+    h.sum_band_rho(lda, n, m, psi_t, torch.from_numpy(w).cuda(), rho_t)
+    torch.cuda.synchronize()
+    assert relerr(rho_t.cpu().numpy(), ref) < 1e-12
+    h.close()
+
+
+def test_sum_band_rho_ausurf_grid(mods):
+    qe, D, R, torch = mods
+    d = D.config_descriptor("ausurf112")
+    m = 3
+    inp = R.synthetic_inputs(d, m, [4], seed=1, lda=d.npw, poison=False)
+    w = np.array([2.0, 1.5, 0.25])
+    ref = R.sum_band_rho(d, d.npw, d.npw, m, inp["psi"], w, np.zeros(d.nnr))
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    rho = np.zeros(d.nnr)
+    h.sum_band_rho(d.npw, d.npw, m, inp["psi"], w, rho)
+    assert relerr(rho, ref) < 1e-12
+    h.close()

@@ -231,3 +231,21 @@ def test_init_us_2_restatement_translation_phase():
     ph = np.exp(-1j * 2.0 * np.pi * (kg @ shift))
     assert np.abs(vk[2] - vk[0] * ph[None, :]).max() < 1e-12
     assert np.abs(U.g2_kin(d.g, d.igk, d.xk, d.tpiba2) - d.g2kin).max() == 0.0
+
+
+def test_sum_band_rho_restatement_parseval():
+    """oracle sum_band_rho (PW/src/sum_band.f90:326-647): integral of rho = sum_b w_b <psi_b|psi_b> nnr (k and Gamma,
+    odd band count exercises the single-band Gamma transform)."""
+    for name in ("si2_small", "si2_small_gamma"):
+        d = D.config_descriptor(name)
+        m = 3
+        inp = R.synthetic_inputs(d, m, [4, 4], seed=1)
+        n = inp["n"]
+        w = np.array([2.0, 1.0, 0.5])
+        rho = R.sum_band_rho(d, inp["lda"], n, m, inp["psi"], w, np.zeros(d.nnr))
+        assert rho.min() >= 0.0
+        psi = inp["psi"][:, :n]
+        nrm = (np.abs(psi) ** 2).sum(1)
+        if d.gamma_only:
+            nrm = 2.0 * nrm - (np.abs(psi[:, 0]) ** 2 if d.gstart == 2 else 0.0)
+        assert abs(rho.sum() / d.nnr - (w * nrm).sum()) < 1e-12
