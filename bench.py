@@ -168,7 +168,7 @@ def run_reference(args):
         return
     d, c, nh = workload(args.workload)
     cores = os.cpu_count() or 1
-    m_s = args.cpu_sample_bands or 16
+    m_s = args.cpu_sample_bands or min(int(c.get("nbnd", 128)), 800)
     times = []
     kind = "port"
     for i in range(args.warmup + args.steps):
@@ -349,9 +349,21 @@ def run_ours(args):
                          "ms_projector_section": ms_nl,
                          "peak_source": "148 SMs x 64 FP64 FMA/clk x %.0f MHz (FP64 tensor = FP64 vector rate on B200); "
                                         "cuBLAS DGEMM 4096^3 in this run: %.1f TFLOP/s" % (sm_mhz, dgemm_tf)}
+    # DRAM traffic of the same launches from the committed `ncu --set full` capture (dram__bytes_read+write, per launch)
+    if roofline_gemm and args.workload == "ausurf112" and mm == 800 and three_m:
+        roofline_gemm["traffic"] = 9.337911e9 + 0.174068e9 + 5.360086e9 + 1.208370e9
+        roofline_gemm["traffic_source"] = ("profiles/r1q_gemm_m800_ncu_full.csv: k_calbec3m 9.34+0.17 GB, k_addvus3m 5.36+1.21 GB "
+                                           "per launch at m=800 (algorithmic operands: vkb 3.08 GB + psi/hpsi 1.22 GB each, per kernel)")
+    if args.workload == "ausurf112" and st["batch"] == 15:
+        roofline_vloc["traffic"] = (23.70e6 + 19.23e6 + 84.56e6 + 21.48e6 + 95.52e6 + 8.47e6) / 15 * mm
+        roofline_vloc["traffic_source"] = ("profiles/r1q_vloc_b15_ncu_full.csv: zinv 42.9 MB, plane 106.0 MB, zfwd 104.0 MB per "
+                                           "batch of 15 boxes, scaled to the bands of the section")
     # `roofline` = the kernel family with the largest share of the step
     roofline = roofline_gemm if (roofline_gemm and ms_nl >= ms_vloc) else roofline_vloc
-    launches_step = nbatches * 5 + (4 if nkb else 0) + 1
+    kpb = h.vloc_kernels_per_batch()  # 3 with the fused plane kernel (zinv, plane, zfwd), else 5
+    launches_step = nbatches * kpb + (4 if nkb else 0) + 1
+    roofline_vloc["kernel"] = ("V_loc pass pipeline (3 kernels/batch: zinv, fused plane y|x*V*x|y, zfwd)" if kpb == 3 else
+                               "V_loc pass pipeline (5 kernels/batch: zinv,yinv,xfus,yfwd,zfwd)")
 
     # ---- end to end through the public API with HOST (pinned) buffers ----
     e2e = None
@@ -397,7 +409,7 @@ def run_ours(args):
             line["e2e"] = e2e
         if not args.no_cpu_baseline and world == 1:
             cores = os.cpu_count() or 1
-            m_s = args.cpu_sample_bands or 8
+            m_s = args.cpu_sample_bands or min(int(c.get("nbnd", 128)), 400)
             dt, kind = cpu_reference_run(d, c, nh, m_s, cores)
             line["cpu_baseline"] = {"value": m_s / dt, "unit": "band-applications/s", "cores": cores, "kind": kind,
                                     "sample": f"{m_s} bands of the same h_psi (V_loc: reference C FFT engine, OpenMP "

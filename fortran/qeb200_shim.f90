@@ -72,6 +72,44 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_s_psi(ctx, lda, n, m, psi, spsi) BIND(C, name='qeb_s_psi')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, spsi; INTEGER(C_INT), VALUE :: lda, n, m
     END FUNCTION
+    ! --- device-side producers of the per-k-point state (SURVEY 8 f2) ---
+    INTEGER(C_INT) FUNCTION qeb_set_gvectors(ctx, ngm, g, mill) BIND(C, name='qeb_set_gvectors')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, g, mill; INTEGER(C_INT), VALUE :: ngm
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_g2_kin(ctx, xk, tpiba2, qcutz, ecfixed, q2sigma, g2kin_out) BIND(C, name='qeb_g2_kin')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, xk, g2kin_out; REAL(C_DOUBLE), VALUE :: tpiba2, qcutz, ecfixed, q2sigma
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_beta_tables(ctx, nsp, nhm, nbetam, lmaxkb, nh, nhtol, nhtolm, indv, nqx, dq, tab_beta) &
+        BIND(C, name='qeb_set_beta_tables')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, nh, nhtol, nhtolm, indv, tab_beta
+      INTEGER(C_INT), VALUE :: nsp, nhm, nbetam, lmaxkb, nqx; REAL(C_DOUBLE), VALUE :: dq
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_structure(ctx, nat, ityp, tau, nr1, nr2, nr3, eigts1, eigts2, eigts3) &
+        BIND(C, name='qeb_set_structure')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, ityp, tau, eigts1, eigts2, eigts3; INTEGER(C_INT), VALUE :: nat, nr1, nr2, nr3
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_init_us_2(ctx, q, tpiba, vkb_out) BIND(C, name='qeb_init_us_2')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, q, vkb_out; REAL(C_DOUBLE), VALUE :: tpiba
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_sum_band_rho(ctx, lda, n, m, evc, w, rho) BIND(C, name='qeb_sum_band_rho')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, evc, w, rho; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
+    ! --- block-Davidson building blocks (SURVEY 8 f3) ---
+    INTEGER(C_INT) FUNCTION qeb_set_g_psi_diag(ctx, n, h_diag, s_diag) BIND(C, name='qeb_set_g_psi_diag')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, h_diag, s_diag; INTEGER(C_INT), VALUE :: n
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_g_psi(ctx, lda, n, m, npol, psi, e) BIND(C, name='qeb_g_psi')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, e; INTEGER(C_INT), VALUE :: lda, n, m, npol
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_col_dot(ctx, n, m, a, lda, b, ldb, res) BIND(C, name='qeb_col_dot')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, a, b, res; INTEGER(C_INT), VALUE :: n, m, lda, ldb
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_dav_gemm_cn(ctx, n, a, lda, ka, b, ldb, mb, c, ldc) BIND(C, name='qeb_dav_gemm_cn')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, a, b, c; INTEGER(C_INT), VALUE :: n, lda, ka, ldb, mb, ldc
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_dav_gemm_nn(ctx, n, a, lda, k, b, ldb, m, c, ldc, accumulate) BIND(C, name='qeb_dav_gemm_nn')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, a, b, c; INTEGER(C_INT), VALUE :: n, lda, k, ldb, m, ldc, accumulate
+    END FUNCTION
   END INTERFACE
 END MODULE qeb200_c
 
@@ -164,6 +202,30 @@ CONTAINS
       END IF
     END IF
     spin_loaded = current_spin
+  END SUBROUTINE
+  SUBROUTINE qeb200_sync_uspp(structure_changed)
+    !! Pushes the run-constant inputs of init_us_2 / g2_kin (G-vector list, beta interpolation tables: once) and the
+    !! structure-factor phases (after every struc_fact, PW/src/hinit0.f90 / hinit1.f90).
+    USE gvect,      ONLY: ngm, g, mill, eigts1, eigts2, eigts3
+    USE fft_base,   ONLY: dfftp
+    USE ions_base,  ONLY: nat, ityp, tau, nsp
+    USE uspp,       ONLY: nhtol, nhtolm, indv
+    USE uspp_param, ONLY: nh, nhm, nbetam, lmaxkb
+    USE beta_mod,   ONLY: tab_beta, dq, nqx
+    LOGICAL, INTENT(IN) :: structure_changed
+    LOGICAL, SAVE :: tables_loaded = .FALSE.
+    IF (.NOT. C_ASSOCIATED(ctx)) CALL qeb200_sync_state()
+    IF (.NOT. tables_loaded) THEN
+      CALL qeb200_check(qeb_set_gvectors(ctx, ngm, C_LOC(g), C_LOC(mill)), 'qeb_set_gvectors')
+      CALL qeb200_check(qeb_set_beta_tables(ctx, nsp, nhm, nbetam, lmaxkb, C_LOC(nh), C_LOC(nhtol), C_LOC(nhtolm), &
+                        C_LOC(indv), nqx, dq, C_LOC(tab_beta)), 'qeb_set_beta_tables')
+      tables_loaded = .TRUE.
+    END IF
+    IF (structure_changed) THEN
+      CALL qeb200_check(qeb_set_structure(ctx, nat, C_LOC(ityp), C_LOC(tau), dfftp%nr1, dfftp%nr2, dfftp%nr3, &
+                        C_LOC(eigts1), C_LOC(eigts2), C_LOC(eigts3)), 'qeb_set_structure')
+      k_set = -1
+    END IF
   END SUBROUTINE
 END MODULE qeb200_state
 
@@ -324,6 +386,47 @@ SUBROUTINE s_psi_qeb(lda, n, m, psi, spsi)
   CALL qeb200_sync_state()
   CALL qeb200_check(qeb_s_psi(ctx, lda, n, m, C_LOC(psi), C_LOC(spsi)), 's_psi')
 END SUBROUTINE s_psi_qeb
+
+!----------------------------------------------------------------------------
+SUBROUTINE g_psi_qeb(lda, n, m, npol, psi, e)
+  !! g_psi(lda,n,m,npol,psi,e) (PW/src/g_psi.f90:10): the g_psi_ptr of cegterg/regterg (cegterg.f90:110-118,407).
+  !! h_diag/s_diag (g_psi_mod) are pushed once per k-point by the caller with qeb_set_g_psi_diag (c_bands.f90 fills
+  !! them right before the solver call). psi must be device data (!$acc host_data use_device(psi) in the caller).
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds, ONLY: DP
+  USE qeb200_c
+  USE qeb200_state
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n, m, npol
+  COMPLEX(DP), INTENT(INOUT), TARGET :: psi(lda, npol, m)
+  REAL(DP), INTENT(IN), TARGET :: e(m)
+  IF (npol /= 1) THEN
+    CALL g_psi(lda, n, m, npol, psi, e)
+    RETURN
+  END IF
+  CALL qeb200_check(qeb_g_psi(ctx, lda, n, m, npol, C_LOC(psi), C_LOC(e)), 'g_psi')
+END SUBROUTINE g_psi_qeb
+
+!----------------------------------------------------------------------------
+SUBROUTINE init_us_2_qeb(npw_, igk_, q_, vkb_)
+  !! init_us_2(npw,igk,q,vkb) (upflib/uspp_init / init_us_2_acc.f90:10) for the k-point the context holds: vkb is built
+  !! on the device and stays there for h_psi; vkb_ (module uspp::vkb) receives a copy for the routines outside the
+  !! library (forces, stress, sum_bec). qeb_set_beta_tables / qeb_set_gvectors are pushed once per run and
+  !! qeb_set_structure after every struc_fact by qeb200_sync_uspp (module qeb200_state).
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds,     ONLY: DP
+  USE cell_base, ONLY: tpiba
+  USE wvfct,     ONLY: npwx
+  USE uspp,      ONLY: nkb
+  USE qeb200_c
+  USE qeb200_state
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: npw_, igk_(npw_)
+  REAL(DP), INTENT(IN), TARGET :: q_(3)
+  COMPLEX(DP), INTENT(OUT), TARGET :: vkb_(npwx, nkb)
+  CALL qeb200_sync_state()
+  CALL qeb200_check(qeb_init_us_2(ctx, C_LOC(q_), tpiba, C_LOC(vkb_)), 'init_us_2')
+END SUBROUTINE init_us_2_qeb
 
 !----------------------------------------------------------------------------
 SUBROUTINE invfft_qeb(fft_kind, f, howmany)

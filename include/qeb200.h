@@ -273,6 +273,9 @@ int qeb_desc_get(const qeb_desc* d, int what, int rank, void* out);
  * 16*(4*nst*nr3 + 4*nxw*nr2*nr3)[/2 Gamma] + 60*npw, and the table sizes */
 int qeb_get_stats(qeb_ctx* ctx, double* vloc_bytes_per_band, double* gemm_flops_per_band, int* nst, int* nxw,
                   int* nboxes_batch);
+/* kernels launched per V_loc batch with the current grid / potential: 3 when the fused plane kernel is active
+ * (scatter+z, plane, z+gather), 5 otherwise; 7 on the slab-distributed path (pack / unpack around the exchange). */
+int qeb_vloc_kernels_per_batch(qeb_ctx* ctx);
 /* FP64 DMMA GEMM self-test entry used by the benchmark to time the projector
  * kernels alone: runs calbec + add_vuspsi on the context's vkb for m bands of
  * a device psi/hpsi. */

@@ -1629,6 +1629,15 @@ int qeb_h_psi_bgrp(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hps
     return finish(c);
 }
 
+int qeb_vloc_kernels_per_batch(qeb_ctx* c)
+{
+    if (!c) return 0;
+    if (c->dist) return 7;
+    const char* e = getenv("QEB_PLANE");
+    const bool off = (e && atoi(e) == 0) || (getenv("QEB_GENERIC") && atoi(getenv("QEB_GENERIC")));
+    return (c->T.pl_v && !off) ? 3 : 5;
+}
+
 int qeb_get_stats(qeb_ctx* c, double* vloc_bytes_per_band, double* gemm_flops_per_band, int* nst, int* nxw, int* nboxes)
 {
     if (!c || !c->have_k) return 1;

@@ -83,6 +83,7 @@ def load_library():
     L.qeb_get_stats.argtypes = [P, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
                                 ctypes.POINTER(I), ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_nonlocal_only.argtypes = [P, I, I, I, P, P]
+    L.qeb_vloc_kernels_per_batch.argtypes = [P]
     for name in ("qeb_create", "qeb_destroy", "qeb_set_pipeline", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
                  "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
@@ -366,6 +367,9 @@ class HPsi:
 
     def nonlocal_only(self, lda, n, m, psi, hpsi):
         self._ck(self._L.qeb_nonlocal_only(self._h, lda, n, m, _ptr(psi), _ptr(hpsi)), "qeb_nonlocal_only")
+
+    def vloc_kernels_per_batch(self):
+        return int(self._L.qeb_vloc_kernels_per_batch(self._h))
 
     def stats(self):
         vb, gf = ctypes.c_double(), ctypes.c_double()
