@@ -42,6 +42,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="--mode rg: stick<->plane exchange as peer-to-peer copy-engine writes (default) or NCCL send/recv")
     return ap.parse_args()
 
 
@@ -255,6 +257,8 @@ def run_ours(args):
             h.nccl_init(qe_b200.COMM_RG)
         h.set_kpoint(n, lda, None if d.gamma_only else rk.igk, rk.g2kin, vkb, nkb, rk.gstart)
         h.set_vloc(rng.uniform(-1.0, 0.0, d.nr1 * d.nr2 * int(d.nr3p[rank])))
+        if world > 1 and args.exchange == "p2p":
+            h.p2p_setup()
     else:
         h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
         h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
@@ -396,7 +400,7 @@ def run_ours(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak" if pools else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "grid": [d.nr1, d.nr2, d.nr3], "npw": n, "bands_per_step": m_total,
-                       "nkb": nkb, "gamma_only": bool(d.gamma_only), "parallelism": {"pools": "k-pools", "bgrp": "band-groups", "rg": "R&G slab FFT"}[args.mode] + f" x{world}",
+                       "nkb": nkb, "gamma_only": bool(d.gamma_only), "parallelism": {"pools": "k-pools", "bgrp": "band-groups", "rg": "R&G slab FFT (" + args.exchange + " exchange)"}[args.mode] + f" x{world}",
                        "vloc_batch_boxes": st["batch"], "l2": "inputs larger than L2 (psi+hpsi+vkb = %.1f GB)" % ((2 * m_total * lda * 16 + nkb * lda * 16) / 1e9)},
             "roofline": roofline,
             "roofline_vloc": roofline_vloc,

@@ -231,6 +231,16 @@ int qeb_set_grid_dist(qeb_ctx* ctx, int nr1, int nr2, int nr3, int nproc, int my
                       const int* iss, const int* ismap, int nismap, int ngm, const int* nl, const int* nlm,
                       int gamma_only);
 
+/* Peer-to-peer form of the R&G exchange (one process per GPU of one NVLink/NVSwitch box): after qeb_set_grid_dist +
+ * qeb_set_kpoint every rank calls qeb_p2p_export (publishes cudaIpc handles of its exchange buffers and flag words in
+ * a QEB_P2P_BLOB_BYTES blob), the caller all-gathers the blobs in rank order (MPI_Allgather in a Fortran host,
+ * torch.distributed in the Python mirror), every rank calls qeb_p2p_import, then a barrier. From then on
+ * fft_scatter (fft_scatter_2d.f90:123,226) runs as copy-engine writes into the peers' buffers plus flag words, without
+ * NCCL kernels; the becp all-reduce still uses the QEB_COMM_RG communicator. QEB_P2P=0 keeps the NCCL exchange. */
+#define QEB_P2P_BLOB_BYTES 256
+int qeb_p2p_export(qeb_ctx* ctx, void* blob);
+int qeb_p2p_import(qeb_ctx* ctx, const void* blobs, int nranks);
+
 /* ---- host-side descriptor builder (no GPU needed) ------------------------ */
 /* For hosts that do not run the reference's own setup (benchmark, Python mirror, tests): the data of
  * fft_type_init + ggen + fft_set_nl + gk_sort + g2_kin for one k-point, and the slab distribution of the grid.

@@ -150,6 +150,11 @@ struct qeb_ctx {
     VlocLaunchCfg cfgp;
     DevBuf tabp_d, planp_d, dist_tab_d, sbuf_d, rbuf_d;
     DistDev DD;
+    // peer-to-peer exchange (qeb_p2p_export / qeb_p2p_import)
+    P2PState P2P;
+    DevBuf p2p_flags_d, p2p_ptrs_d;
+    bool p2p_exported = false;
+    std::vector<void*> p2p_opened;  // cudaIpcOpenMemHandle mappings to close
 };
 
 #define QEB_FAIL(ctx, code, msg)   \
@@ -243,7 +248,11 @@ int qeb_destroy(qeb_ctx* c)
                       &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage, &c->tabp_d, &c->planp_d,
                       &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d, &c->qq_d, &c->us_int_d, &c->tab_beta_d, &c->us_scratch_d,
                       &c->us_in_d, &c->gv_g_d, &c->gv_mill_d, &c->igk_dev_d, &c->st_eig_d, &c->st_int_d, &c->gpsi_d, &c->dav_small_d, &c->rho_d, &c->wts_d};
+    for (void* m : c->p2p_opened) cudaIpcCloseMemHandle(m);
+    c->p2p_opened.clear();
     for (DevBuf* b : bufs) b->release();
+    c->p2p_flags_d.release();
+    c->p2p_ptrs_d.release();
     if ((c->nccl_owned || c->nccl_rg_owned) && nccl_api().ok) {
         if (c->nccl && c->nccl_owned) nccl_api().CommDestroy(c->nccl);
         if (c->nccl_rg && c->nccl_rg_owned) nccl_api().CommDestroy(c->nccl_rg);
@@ -576,13 +585,20 @@ static int size_workspaces_dist(qeb_ctx* c)
     if (nb <= 0) {
         // enough boxes per launch to fill the SMs (measured: throughput saturates from ~8 boxes of a large grid,
         // L2 residency of the planes matters less), bounded by workspace memory
+        // from the largest slab, so that every rank of the group picks the same batch (the exchange needs it)
+        int nzmax = 1;
+        for (int z : D.nr3p) nzmax = std::max(nzmax, z);
         const size_t target = (size_t)192 << 20;
-        nb = (int)(target / (tp.g2_box * 16 + 1));
+        nb = (int)(target / ((size_t)tp.nxw * c->nr2 * nzmax * 16 + 1));
         if (nb < 8) nb = 8;
         if (nb > 64) nb = 64;
     }
-    c->batch = nb;
     const size_t ns = (size_t)c->vloc_nstreams;
+    if (c->p2p_exported && (nb != c->batch || nst_me * c->nr3 * 16 * nb * ns > c->sbuf_d.cap ||
+                            tp.g1_box * 16 * nb * ns > c->rbuf_d.cap))
+        QEB_FAIL(c, 27, "qeb_set_kpoint: the exchange buffers were exported to the peers (qeb_p2p_export) and cannot "
+                        "change size; export after the k-point with the largest npw / before changing the batch");
+    c->batch = nb;
     QEB_CUDA(c, c->sbuf_d.ensure(std::max<size_t>(16, nst_me * c->nr3 * 16 * nb * ns)));
     QEB_CUDA(c, c->rbuf_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb * ns)));
     QEB_CUDA(c, c->g1_d.ensure(std::max<size_t>(16, tp.g1_box * 16 * nb * ns)));
@@ -1066,6 +1082,89 @@ int qeb_dav_gemm_nn(qeb_ctx* c, int n, const void* A, int lda, int k, const void
     return finish(c);
 }
 
+// ---- peer-to-peer stick <-> plane exchange over NVLink (cudaIpc) ------------
+struct P2PBlob {  // what one rank publishes to the others (fits QEB_P2P_BLOB_BYTES)
+    cudaIpcMemHandle_t s, r, f;
+    unsigned long long s_bytes, r_bytes;
+    int batch, nslots, rank, nproc;
+};
+
+int qeb_p2p_export(qeb_ctx* c, void* blob)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->dist || !c->have_k) QEB_FAIL(c, 98, "qeb_p2p_export: call after qeb_set_grid_dist + qeb_set_kpoint (the buffers must exist)");
+    if (!blob) QEB_FAIL(c, 98, "qeb_p2p_export: null blob");
+    static_assert(sizeof(P2PBlob) <= 256, "QEB_P2P_BLOB_BYTES");
+    const DistHost& D = c->DH;
+    const int ns = c->vloc_nstreams;
+    QEB_CUDA(c, c->p2p_flags_d.ensure((size_t)2 * ns * D.nproc * 4 + 64));
+    QEB_CUDA(c, cudaMemsetAsync(c->p2p_flags_d.p, 0, c->p2p_flags_d.cap, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    P2PBlob b;
+    memset(&b, 0, sizeof(b));
+    QEB_CUDA(c, cudaIpcGetMemHandle(&b.s, c->sbuf_d.p));
+    QEB_CUDA(c, cudaIpcGetMemHandle(&b.r, c->rbuf_d.p));
+    QEB_CUDA(c, cudaIpcGetMemHandle(&b.f, c->p2p_flags_d.p));
+    b.s_bytes = c->sbuf_d.cap;
+    b.r_bytes = c->rbuf_d.cap;
+    b.batch = c->batch;
+    b.nslots = ns;
+    b.rank = D.me;
+    b.nproc = D.nproc;
+    memset(blob, 0, 256);
+    memcpy(blob, &b, sizeof(b));
+    c->p2p_exported = true;
+    c->P2P = P2PState();
+    return 0;
+}
+
+int qeb_p2p_import(qeb_ctx* c, const void* blobs, int nranks)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->p2p_exported) QEB_FAIL(c, 99, "qeb_p2p_import: qeb_p2p_export first");
+    const DistHost& D = c->DH;
+    if (!blobs || nranks != D.nproc) QEB_FAIL(c, 99, "qeb_p2p_import: one blob per rank of the R&G group expected");
+    P2PState& P = c->P2P;
+    P = P2PState();
+    P.nslots = c->vloc_nstreams;
+    P.batch = c->batch;
+    P.peer_S.assign(nranks, nullptr);
+    P.peer_R.assign(nranks, nullptr);
+    P.peer_flags.assign(nranks, nullptr);
+    for (int q = 0; q < nranks; ++q) {
+        P2PBlob b;
+        memcpy(&b, (const char*)blobs + (size_t)q * 256, sizeof(b));
+        if (b.rank != q || b.nproc != nranks) QEB_FAIL(c, 99, "qeb_p2p_import: blobs are not ordered by rank");
+        if (b.batch != c->batch || b.nslots != P.nslots) QEB_FAIL(c, 99, "qeb_p2p_import: ranks disagree on batch / streams");
+        if (q == D.me) {
+            P.peer_S[q] = (cplx*)c->sbuf_d.p;
+            P.peer_R[q] = (cplx*)c->rbuf_d.p;
+            P.peer_flags[q] = (unsigned*)c->p2p_flags_d.p;
+            continue;
+        }
+        void *ps = nullptr, *pr = nullptr, *pf = nullptr;
+        QEB_CUDA(c, cudaIpcOpenMemHandle(&ps, b.s, cudaIpcMemLazyEnablePeerAccess));
+        c->p2p_opened.push_back(ps);
+        QEB_CUDA(c, cudaIpcOpenMemHandle(&pr, b.r, cudaIpcMemLazyEnablePeerAccess));
+        c->p2p_opened.push_back(pr);
+        QEB_CUDA(c, cudaIpcOpenMemHandle(&pf, b.f, cudaIpcMemLazyEnablePeerAccess));
+        c->p2p_opened.push_back(pf);
+        P.peer_S[q] = (cplx*)ps;
+        P.peer_R[q] = (cplx*)pr;
+        P.peer_flags[q] = (unsigned*)pf;
+    }
+    QEB_CUDA(c, c->p2p_ptrs_d.ensure((size_t)nranks * sizeof(void*)));
+    QEB_CUDA(c, cudaMemcpyAsync(c->p2p_ptrs_d.p, P.peer_flags.data(), (size_t)nranks * sizeof(void*), cudaMemcpyHostToDevice,
+                                c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    P.peer_flags_dev = (unsigned**)c->p2p_ptrs_d.p;
+    const char* e = getenv("QEB_P2P");
+    P.ok = !(e && atoi(e) == 0);
+    return 0;
+}
+
 // ---- internal pieces ----------------------------------------------------
 static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hpsi, bool kinetic)
 {
@@ -1083,7 +1182,8 @@ static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hp
     if (c->dist) {
         // cft_1z | fft_scatter | cft_2xy * V * cft_2xy | fft_scatter | cft_1z  (fft_parallel_2d.f90:36-204)
         const DistHost& D = c->DH;
-        if (D.nproc > 1 && !c->nccl_rg) QEB_FAIL(c, 53, "V_loc: no NCCL communicator for the R&G group (qeb_nccl_init)");
+        if (D.nproc > 1 && !c->nccl_rg && !c->P2P.ok)
+            QEB_FAIL(c, 53, "V_loc: no NCCL communicator (qeb_nccl_init) or peer mapping (qeb_p2p_import) for the R&G group");
         // batches alternate between the V_loc streams (own S/R/G1/G2 slices): the exchange of one batch overlaps
         // the FFT passes of the other. Every rank issues the collectives in the same order.
         const int nbatches_d = (nboxes + c->batch - 1) / c->batch;
@@ -1112,11 +1212,16 @@ static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hp
             const char* msg = "";
             int rc;
             QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
-            if ((rc = dist_exchange(D, c->nccl_rg, true, S, R, nb, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            const bool p2p = c->P2P.ok && D.nproc > 1;
+            if ((rc = p2p ? dist_exchange_p2p(D, c->P2P, true, si, S, R, nb, c->nr3, st, &msg)
+                          : dist_exchange(D, c->nccl_rg, true, S, R, nb, st, &msg)))
+                QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
             QEB_CUDA(c, dist_unpack(c->DD, R, tp.g1, nb, st));
             QEB_CUDA(c, vloc_launch_planes(tp, c->cfgp, nb, st));
             QEB_CUDA(c, dist_pack(c->DD, tp.g1, R, nb, st));
-            if ((rc = dist_exchange(D, c->nccl_rg, false, S, R, nb, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            if ((rc = p2p ? dist_exchange_p2p(D, c->P2P, false, si, S, R, nb, c->nr3, st, &msg)
+                          : dist_exchange(D, c->nccl_rg, false, S, R, nb, st, &msg)))
+                QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
             QEB_CUDA(c, vloc_launch_zpass(false, tz, io, c->cfg, nb, st));
         }
         for (int s = 1; s < nsd; ++s) {

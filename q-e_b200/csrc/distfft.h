@@ -32,4 +32,20 @@ cudaError_t dist_pack(const DistDev& d, const cplx* g1p, cplx* R, int nb, cudaSt
 int dist_exchange(const DistHost& h, NcclComm comm, bool forward, cplx* S, cplx* R, int nb, cudaStream_t st,
                   const char** msg);
 
+// Peer-to-peer form of the same exchange (one process per GPU, buffers shared with cudaIpc*): every rank WRITES its
+// blocks straight into the peers' R (forward) / S (backward) buffers with copy-engine transfers over NVLink, then
+// raises a flag word in each peer's memory; the consumer's stream waits on its own flag words. No NCCL kernel and no
+// SM is used for the transfer, and the copies of one batch overlap the FFT kernels of the other V_loc stream.
+struct P2PState {
+    bool ok = false;
+    int nslots = 0, batch = 0;
+    std::vector<cplx*> peer_S, peer_R;      // base of each rank's sbuf / rbuf (own entries: local pointers)
+    std::vector<unsigned*> peer_flags;      // base of each rank's flag words [2 dirs][nslots][nproc]
+    unsigned** peer_flags_dev = nullptr;    // device copy of peer_flags
+    unsigned epoch[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+};
+// slot: V_loc stream index (each has its own S/R slice); batch_cap: boxes per slice (the same on every rank)
+int dist_exchange_p2p(const DistHost& h, P2PState& p, bool forward, int slot, cplx* S, cplx* R, int nb, int nr3,
+                      cudaStream_t st, const char** msg);
+
 }  // namespace qeb

@@ -68,6 +68,8 @@ def load_library():
     L.qeb_set_structure.argtypes = [P, I, P, P, I, I, I, P, P, P]
     L.qeb_init_us_2.argtypes = [P, P, D, P]
     L.qeb_sum_band_rho.argtypes = [P, I, I, I, P, P, P]
+    L.qeb_p2p_export.argtypes = [P, P]
+    L.qeb_p2p_import.argtypes = [P, P, I]
     L.qeb_set_g_psi_diag.argtypes = [P, I, P, P]
     L.qeb_g_psi.argtypes = [P, I, I, I, I, P, P]
     L.qeb_col_dot.argtypes = [P, I, I, P, I, P, I, P]
@@ -90,7 +92,7 @@ def load_library():
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
                  "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi", "qeb_set_gvectors", "qeb_g2_kin", "qeb_set_beta_tables",
                  "qeb_set_structure", "qeb_init_us_2", "qeb_set_g_psi_diag", "qeb_g_psi", "qeb_col_dot",
-                 "qeb_dav_gemm_cn", "qeb_dav_gemm_nn", "qeb_sum_band_rho"):
+                 "qeb_dav_gemm_cn", "qeb_dav_gemm_nn", "qeb_sum_band_rho", "qeb_p2p_export", "qeb_p2p_import"):
         getattr(L, name).restype = I
     _LIB = L
     return L
@@ -217,6 +219,25 @@ class HPsi:
         dist.broadcast(t, src=src, group=group)
         raw = bytes(t.cpu().numpy().tobytes())
         self._ck(self._L.qeb_nccl_init(self._h, role, ctypes.c_char_p(raw), world, rank), "qeb_nccl_init")
+
+    def p2p_setup(self, group=None):
+        """Peer-to-peer R&G exchange: export this rank's buffer handles, all-gather them over torch.distributed (a
+        Fortran host would MPI_Allgather), import the peers', barrier. Call after set_grid_dist + set_kpoint."""
+        import torch
+        import torch.distributed as dist
+
+        world = dist.get_world_size(group)
+        blob = (ctypes.c_char * 256)()
+        self._ck(self._L.qeb_p2p_export(self._h, blob), "qeb_p2p_export")
+        mine = torch.frombuffer(bytearray(blob.raw), dtype=torch.uint8).clone()
+        on_gpu = dist.get_backend(group) == "nccl"
+        if on_gpu:
+            mine = mine.cuda()
+        allb = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allb, mine, group=group)
+        raw = b"".join(bytes(t.cpu().numpy().tobytes()) for t in allb)
+        self._ck(self._L.qeb_p2p_import(self._h, ctypes.c_char_p(raw), world), "qeb_p2p_import")
+        dist.barrier(group=group)
 
     def set_kpoint(self, npw, npwx, igk, g2kin, vkb=None, nkb=0, gstart=1):
         igk = _i32(igk)

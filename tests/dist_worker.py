@@ -63,6 +63,20 @@ def main():
         ok = ok and e1 < TOL and e2 < TOL and np.all(out[:, rk.npw:] == 0)
         print(f"rank {rank} R&G batch={batch}: hpsi err {e1:.2e} becp err {e2:.2e}", flush=True)
     h.close()
+    # ---- the same path with the peer-to-peer exchange (cudaIpc buffers, copy-engine puts, flag words) ----
+    hp = qe_b200.HPsi(device=local, batch=2)  # m > batch: several batches alternate between the two slots
+    hp.nccl_init(qe_b200.COMM_RG)             # becp all-reduce
+    lda = setup_rank(hp, d, dd, rank, inp, pad=3)
+    hp.p2p_setup()
+    psi_l = X.split_rows(dd, inp["psi"][:, :n], pad=3, fill=np.nan)[rank]
+    for rep in range(3):  # repeated calls: epochs keep counting
+        out = np.full((m, lda), np.nan + 1j * np.nan)
+        hp.h_psi(lda, rk.npw, m, psi_l, out)
+        e1 = np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max() / np.abs(ref).max()
+        ok = ok and e1 < TOL and np.all(out[:, rk.npw:] == 0)
+    print(f"rank {rank} R&G p2p exchange: hpsi err {e1:.2e}", flush=True)
+    dist.barrier()
+    hp.close()
     # ---- band groups: replicated data, column blocks, NCCL all-gather inside the library ----
     hb = qe_b200.HPsi(device=local)
     hb.nccl_init(qe_b200.COMM_BGRP)
