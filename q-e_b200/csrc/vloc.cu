@@ -256,7 +256,16 @@ cudaError_t vloc_launch_density(const VlocTables& t, const VlocIO& io, const Vlo
     if (!launch_y(true, t, cfg, nboxes, st))
         k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
     const size_t smem = cfg.smem_x + (size_t)t.nr1 * t.TX * 8 + (size_t)t.nr1 * 4 + 16;
-    if (smem > cfg.max_smem) return cudaErrorInvalidConfiguration;
+    if (smem + (size_t)t.nr1 * 20 > cfg.max_smem) return cudaErrorInvalidConfiguration;
+    if (t.TX <= QEB_TL && !env_int("QEB_GENERIC", 0)) {
+#define X(PL)                                                          \
+    if (PL::matches(t.px)) {                                           \
+        FastLaunch<PL>::xacc(t, io, cfg, nboxes, w_dev, rho_dev, st);  \
+        return cudaGetLastError();                                     \
+    }
+        QEB_FOR_PLANS(X)
+#undef X
+    }
     k_vloc_xacc<<<t.ntx, cfg.threads_x, smem, st>>>(t, io, w_dev, nboxes, rho_dev);
     return cudaGetLastError();
 }

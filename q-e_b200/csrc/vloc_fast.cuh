@@ -178,4 +178,41 @@ QEB_HD void xfus_fast_phase(int ph, int tid, int nthr, const VlocTables& t, int 
     }
 }
 
+// ---------------------------------------------------------------------------
+// density accumulation fast: x inverse of one box of the tile + |psi(r)|^2 weights into the lane-mapped accumulator
+// (vloc_kernels.cuh::xacc_phase with a compile-time plan)
+// ---------------------------------------------------------------------------
+struct RhoAccLane {  // racc[pos*ld + lane]
+    double* racc;
+    int ld;
+    double w1, w2;
+    QEB_HD void store(int lane, int pos, cplx v) const { racc[pos * ld + lane] += w1 * (v.x * v.x) + w2 * (v.y * v.y); }
+};
+
+template <class PL>
+QEB_HD void xacc_fast_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, const double* w, int tile,
+                            int box, cplx* smem, double* racc, const FastTabs& ft)
+{
+    constexpr int np = PL::NP;
+    const int TX = t.TX;
+    const int p0 = tile * TX;
+    const int nl = (t.npos - p0) < TX ? (t.npos - p0) : TX;
+    const int warp = tid / QEB_TL, lane = tid % QEB_TL, nwarps = nthr / QEB_TL;
+    LaneTile wk{smem, TX};
+    G2XSrc g{t.g2 + (size_t)box * t.g2_box, ft.map, t.npos, p0};
+    NoMid nm;
+    if (ph == np - 1) {
+        RhoAccLane acc{racc, TX, 0.0, 0.0};
+        xacc_weights(io, w, box, &acc.w1, &acc.w2);
+        if (np == 1)
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, g, acc, nm);
+        else
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, wk, acc, nm);
+    } else if (ph == 0) {
+        SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, g, wk, nm);
+    } else {
+        SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, wk, wk, nm);
+    }
+}
+
 }  // namespace qeb

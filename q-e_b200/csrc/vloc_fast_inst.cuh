@@ -98,6 +98,36 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xfus_f(const __gri
     }
 }
 
+// density accumulation (sum_band): block = (line tile, box chunk); the CTA x-transforms its boxes of the batch one after
+// the other and accumulates w|psi(r)|^2 in shared memory, then adds the tile to rho (atomically when the batch is
+// split over several chunks)
+template <class PL>
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xacc_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io,
+                                                                   const double* __restrict__ w, int nboxes, int bpc,
+                                                                   double* __restrict__ rho)
+{
+    QEB_SMEM;
+    double* racc = reinterpret_cast<double*>(smem + (size_t)t.nr1 * t.TX);
+    cplx* twS = reinterpret_cast<cplx*>(racc + (size_t)t.nr1 * t.TX);
+    int* tabS = reinterpret_cast<int*>(twS + PL::N);
+    int* irev = tabS + PL::N;
+    for (int i = threadIdx.x; i < PL::N; i += blockDim.x) {
+        twS[i] = t.px.tw[i];
+        tabS[i] = t.xmap[i];
+        irev[t.px.rev[i]] = i;
+    }
+    xacc_zero_phase(threadIdx.x, blockDim.x, t, racc);
+    const FastTabs ft{twS, tabS, nullptr, nullptr};
+    __syncthreads();
+    const int b0 = blockIdx.y * bpc;
+    const int b1 = (b0 + bpc) < nboxes ? (b0 + bpc) : nboxes;
+    for (int box = b0; box < b1; ++box)
+        for (int ph = 0; ph < PL::NP; ++ph) {
+            xacc_fast_phase<PL>(ph, threadIdx.x, blockDim.x, t, io, w, blockIdx.x, box, smem, racc, ft);
+            __syncthreads();
+        }
+    xacc_flush_phase(threadIdx.x, blockDim.x, t, blockIdx.x, irev, racc, rho, gridDim.y > 1);
+}
 
 // warps per CTA for a plan: the count in [lo,hi] that wastes the fewest warp-rounds over the passes
 template <class PL>
@@ -133,6 +163,8 @@ struct FastLaunch {
     static void z(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st);
     static void y(bool inv, const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st);
     static void x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st);
+    static void xacc(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, const double* w,
+                     double* rho, cudaStream_t st);
 };
 
 #ifdef QEB_FAST_INSTANTIATE
@@ -144,6 +176,7 @@ void FastLaunch<PL>::attrs(int s)
     cudaFuncSetAttribute(k_vloc_yinv_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_yfwd_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_xfus_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_xacc_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
 }
 template <class PL>
 void FastLaunch<PL>::z(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
@@ -171,6 +204,23 @@ void FastLaunch<PL>::x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes
     const dim3 grid(t.ntx, nboxes);
     const int nw = env_int("QEB_NWX", pick_warps<PL>(4, 10));
     k_vloc_xfus_f<PL><<<grid, nw * 32, cfg.smem_x + PL::N * 20 + 16, st>>>(t);
+}
+template <class PL>
+void FastLaunch<PL>::xacc(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, const double* w,
+                          double* rho, cudaStream_t st)
+{
+    const int nw = env_int("QEB_NWX", pick_warps<PL>(4, 10));
+    const size_t smem = cfg.smem_x + (size_t)t.nr1 * t.TX * 8 + PL::N * 24 + 16;
+    // box chunks: enough CTAs for ~4 waves of the resident slots
+    int per_sm = (int)(cfg.max_smem / smem);
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 2048 / (nw * 32)) per_sm = 2048 / (nw * 32);
+    int chunks = (int)((4L * cfg.num_sms * per_sm + t.ntx - 1) / t.ntx);
+    if (chunks > nboxes) chunks = nboxes;
+    if (chunks < 1) chunks = 1;
+    const int bpc = (nboxes + chunks - 1) / chunks;
+    const dim3 grid(t.ntx, (nboxes + bpc - 1) / bpc);
+    k_vloc_xacc_f<PL><<<grid, nw * 32, smem, st>>>(t, io, w, nboxes, bpc, rho);
 }
 #endif
 

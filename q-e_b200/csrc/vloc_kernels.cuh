@@ -490,7 +490,7 @@ QEB_HD void xacc_phase(int ph, int tid, int nthr, const VlocTables& t, const Vlo
 
 // rho(x, y, z) += racc[pos(x)][line], line p0+l = y*nr3 + z; irev[x] = position holding x after the DIF
 QEB_HD void xacc_flush_phase(int tid, int nthr, const VlocTables& t, int tile, const int* irev, const double* racc,
-                             double* rho)
+                             double* rho, bool shared_tile = false)
 {
     const int TX = t.TX;
     const int p0 = tile * TX;
@@ -499,7 +499,14 @@ QEB_HD void xacc_flush_phase(int tid, int nthr, const VlocTables& t, int tile, c
         const int line = i / t.nr1, x = i - line * t.nr1;
         const int p = p0 + line;
         const int y = p / t.nr3, z = p - y * t.nr3;
-        rho[x + (size_t)t.nr1 * (y + (size_t)t.nr2 * z)] += racc[irev[x] * TX + line];
+        double* r = rho + x + (size_t)t.nr1 * (y + (size_t)t.nr2 * z);
+        const double v = racc[irev[x] * TX + line];
+#if defined(__CUDA_ARCH__)
+        if (shared_tile)  // several CTAs (box chunks) own this tile: order of the additions is not fixed
+            atomicAdd(r, v);
+        else
+#endif
+            *r += v;
     }
 }
 
