@@ -1370,12 +1370,33 @@ static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* ps
     const size_t col = (size_t)lda * 16;
     int mc = c->pipeline_chunk;
     if (mc <= 0) {
-        mc = ((m + 7) / 8 + 63) / 64 * 64;  // ~8 chunks, whole GEMM band tiles
+        // whole band tiles of BOTH projector kernels (calbec: 48 bands, add_vuspsi: 64): multiples of 192; measured at
+        // AUSURF112 m=800 (tools/e2e_sweep.py): 96 -> 101.0, 128 -> 95.7, 192 -> 93.1, 256 -> 100.0, 400 -> 112.9 ms
+        mc = m >= 384 ? 192 : ((m + 7) / 8 + 63) / 64 * 64;
         if (mc < 64) mc = 64;
     }
     if (mc > m) mc = m;
     if (mc & 1) ++mc;  // Gamma: band pairs stay together
-    const int nch = (m + mc - 1) / mc;
+    // chunk schedule: the first copy-in and the last copy-out are the only transfers nothing overlaps, so in the
+    // automatic schedule the first and the last chunk are short (64 columns = one GEMM band tile)
+    std::vector<int> sizes;
+    {
+        int rem = m;
+        // (measured: no gain at AUSURF112, 96.9 vs 95.7 ms, because the short chunks run the GEMMs less efficiently;
+        // kept behind QEB_PIPE_RAMP for hosts with slower links)
+        const bool ramp = getenv("QEB_PIPE_RAMP") && c->pipeline_chunk <= 0 && m >= 4 * 64 && mc > 64;
+        if (ramp) {
+            sizes.push_back(64);
+            rem -= 128;  // first + last
+        }
+        while (rem > 0) {
+            const int t = std::min(mc, rem);
+            sizes.push_back(t);
+            rem -= t;
+        }
+        if (ramp) sizes.push_back(64);
+    }
+    const int nch = (int)sizes.size();
     if (!c->s_in) QEB_CUDA(c, cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
     if (!c->s_out) QEB_CUDA(c, cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
     while ((int)c->ev.size() < 2 * nch) {
@@ -1395,8 +1416,9 @@ static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* ps
     char* hh = (char*)hpsi;
     char* pd = (char*)c->psi_stage.p;
     char* hd = (char*)c->hpsi_stage.p;
-    for (int i = 0; i < nch; ++i) {
-        const int c0 = i * mc, mm = std::min(mc, m - c0);
+    int c0 = 0;
+    for (int i = 0; i < nch; c0 += sizes[i], ++i) {
+        const int mm = sizes[i];
         QEB_CUDA(c, cudaMemcpyAsync(pd + col * c0, ph + col * c0, col * mm, cudaMemcpyHostToDevice, c->s_in));
         QEB_CUDA(c, cudaEventRecord(c->ev[2 * i], c->s_in));
         QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev[2 * i], 0));
