@@ -240,7 +240,7 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
   USE becmod,           ONLY: becp
   USE uspp,             ONLY: nkb
   USE control_flags,    ONLY: gamma_only
-  USE noncollin_module, ONLY: npol, noncolin
+  USE noncollin_module, ONLY: npol, noncolin, domag, lspinorb
   USE realus,           ONLY: real_space
   USE fft_base,         ONLY: dffts
   USE ldaU,             ONLY: lda_plus_u
@@ -255,13 +255,23 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
   INTEGER :: m_start, m_end, column_type
   INTEGER, ALLOCATABLE :: recv_counts(:), displs(:)
   !
-  IF (noncolin .OR. real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. &
-      exx_is_active() .OR. xclib_dft_is('meta') .OR. dffts%lpara) THEN
+  IF (real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. exx_is_active() .OR. &
+      xclib_dft_is('meta') .OR. dffts%lpara .OR. (noncolin .AND. (domag .OR. lspinorb))) THEN
     CALL h_psi(lda, n, m, psi, hpsi)      ! original Fortran path
     RETURN
   END IF
   CALL start_clock('h_psi')
   CALL qeb200_sync_state()
+  IF (noncolin) THEN
+    ! Non-magnetic spinors without spin-orbit: both components see the same g2kin, the same scalar V(r)
+    ! (vloc_psi_nc with domag = .FALSE., vloc_psi_acc.f90:269-369) and deeq_nc(:,:,na,1) = deeq_nc(:,:,na,4) = deeq,
+    ! deeq_nc(:,:,na,2:3) = 0 (newd), so H acts on psi(lda*npol, m) exactly as on 2*m columns of leading dimension lda;
+    ! becp%nc(nkb,npol,m) has the memory layout of becp(nkb, 2*m).
+    CALL qeb200_check(qeb_h_psi(ctx, lda, n, npol*m, C_LOC(psi), C_LOC(hpsi)), 'h_psi')
+    IF (nkb > 0) CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%nc), npol*m), 'h_psi')
+    CALL stop_clock('h_psi')
+    RETURN
+  END IF
   IF (use_bgrp_in_hpsi .AND. nbgrp > 1 .AND. m > 1) THEN
     ! band groups, h_psi.f90:53-67: own columns on this rank's GPU, then the reference's own all-gather
     ALLOCATE(recv_counts(mp_size(inter_bgrp_comm)), displs(mp_size(inter_bgrp_comm)))
