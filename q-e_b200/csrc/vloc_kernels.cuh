@@ -101,7 +101,25 @@ QEB_HD void zinv_scatter_phase(int ph, int tid, int nthr, const VlocTables& t, c
         const int c0 = t.grp_coef_off[grp], c1 = t.grp_coef_off[grp + 1];
         if (!io.gamma) {
             const cplx* p = io.psi + (size_t)(io.band0 + box) * io.lda;
-            for (int c = c0 + tid; c < c1; c += nthr) smem[t.coef_slot[c]] = p[t.coef_ig[c]];
+            // four coefficients per thread in flight: the index loads, then the dependent psi gathers, then the stores
+            // (one global round trip per stage instead of one per coefficient)
+            constexpr int U = 4;
+            for (int c = c0 + tid; c < c1; c += U * nthr) {
+                int ig[U], sl[U];
+                cplx v[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int cc = c + u * nthr;
+                    ig[u] = cc < c1 ? t.coef_ig[cc] : -1;
+                    sl[u] = cc < c1 ? t.coef_slot[cc] : 0;
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    if (ig[u] >= 0) v[u] = p[ig[u]];
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    if (ig[u] >= 0) smem[sl[u]] = v[u];
+            }
         } else {
             const int b1 = io.band0 + 2 * box;
             const bool pair = (b1 + 1) < io.nbands;
@@ -183,19 +201,34 @@ QEB_HD void zfwd_gather_phase(int tid, int nthr, const VlocTables& t, const Vloc
     const int c0 = t.grp_coef_off[grp], c1 = t.grp_coef_off[grp + 1];
     if (!io.gamma) {
         const size_t off = (size_t)(io.band0 + box) * io.lda;
-        for (int c = c0 + tid; c < c1; c += nthr) {
-            const int ig = t.coef_ig[c];
-            const cplx v = smem[t.coef_slot[c]];
-            cplx h;
-            if (io.g2kin) {
-                const cplx p = io.psi[off + ig];
-                const double g2 = io.g2kin[ig];
-                h = mk(g2 * p.x + v.x, g2 * p.y + v.y);
-            } else {
-                const cplx h0 = io.hpsi[off + ig];
-                h = h0 + v;
+        constexpr int U = 4;  // as in the scatter: index loads, dependent loads and stores in three stages
+        for (int c = c0 + tid; c < c1; c += U * nthr) {
+            int ig[U], sl[U];
+            cplx a[U];
+            double g2[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int cc = c + u * nthr;
+                ig[u] = cc < c1 ? t.coef_ig[cc] : -1;
+                sl[u] = cc < c1 ? t.coef_slot[cc] : 0;
             }
-            io.hpsi[off + ig] = h;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (ig[u] < 0) continue;
+                if (io.g2kin) {
+                    a[u] = io.psi[off + ig[u]];
+                    g2[u] = io.g2kin[ig[u]];
+                } else {
+                    a[u] = io.hpsi[off + ig[u]];
+                    g2[u] = 1.0;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (ig[u] < 0) continue;
+                const cplx v = smem[sl[u]];
+                io.hpsi[off + ig[u]] = io.g2kin ? mk(g2[u] * a[u].x + v.x, g2[u] * a[u].y + v.y) : a[u] + v;
+            }
         }
     } else {
         const int b1 = io.band0 + 2 * box;
