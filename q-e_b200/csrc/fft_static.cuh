@@ -49,7 +49,9 @@ constexpr bool QEB_VPF = true;
 QEB_HD cplx stw(const cplx* tw, int j, double sgn) { return mk(tw[j].x, sgn * tw[j].y); }
 
 // One radix pass P of plan PL over the tile; see fft_core.cuh::fft_pass_r for the math.
-template <class PL, int P, bool DIT, bool FUSE2, class Src, class Dst, class Mid>
+// PF: software-pipelined input (the loads of the next butterfly are issued before the current one is computed) for
+// passes whose source is global memory, where each warp otherwise exposes one L2/DRAM round trip per butterfly
+template <class PL, int P, bool DIT, bool FUSE2, bool PF = false, class Src, class Dst, class Mid>
 QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double sgn, Src& src, Dst& dst, Mid& mid)
 {
     constexpr int R = PL::r(P);
@@ -59,6 +61,7 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
     constexpr int NJ = PL::N / R;
     if (lane >= nl) return;
     double fnext[FUSE2 ? R : 1];
+    cplx vnext[PF ? R : 1];
     if (FUSE2 && QEB_VPF && warp < NJ) {  // pointwise factor of the first butterfly (software pipeline, see below)
         const int blk = warp / A;
         const int base = blk * L + (warp - blk * A);
@@ -71,6 +74,21 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
         const int base = blk * L + a;
         cplx v[R];
         double f[FUSE2 ? R : 1];
+        if (PF) {
+            if (j == warp) {
+#pragma unroll
+                for (int b = 0; b < R; ++b) vnext[b] = src.load(lane, base + A * b);
+            }
+#pragma unroll
+            for (int b = 0; b < R; ++b) v[b] = vnext[b];
+            const int jn = j + nwarps;
+            if (jn < NJ) {
+                const int blkn = jn / A;
+                const int basen = blkn * L + (jn - blkn * A);
+#pragma unroll
+                for (int b = 0; b < R; ++b) vnext[b] = src.load(lane, basen + A * b);
+            }
+        }
         if (FUSE2) {  // the factor of this butterfly was fetched one iteration ago; fetch the next one now so that
                       // its L2 latency hides behind this butterfly
 #pragma unroll
@@ -83,8 +101,10 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
                 for (int d = 0; d < R; ++d) fnext[d] = mid.fetch(lane, basen + d);
             }
         }
+        if (!PF) {
 #pragma unroll
-        for (int b = 0; b < R; ++b) v[b] = src.load(lane, base + A * b);
+            for (int b = 0; b < R; ++b) v[b] = src.load(lane, base + A * b);
+        }
         if (DIT && A > 1) {
             const int st = a * NB;
 #pragma unroll
@@ -107,16 +127,16 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
 }
 
 // run pass number `p` (runtime, warp-uniform) of plan PL: expands to a switch over the NP passes
-template <class PL, bool DIT, bool FUSE2, int P = 0>
+template <class PL, bool DIT, bool FUSE2, int P = 0, bool PF = false>
 struct SPassSel {
     template <class Src, class Dst, class Mid>
     QEB_HD static void run(int p, int warp, int nwarps, int lane, int nl, const cplx* tw, double sgn, Src& src, Dst& dst,
                            Mid& mid)
     {
         if (p == P)
-            spass<PL, P, DIT, FUSE2>(warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
+            spass<PL, P, DIT, FUSE2, PF>(warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
         else if constexpr (P + 1 < PL::NP)
-            SPassSel<PL, DIT, FUSE2, P + 1>::run(p, warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
+            SPassSel<PL, DIT, FUSE2, P + 1, PF>::run(p, warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
     }
 };
 

@@ -12,6 +12,14 @@
 
 namespace qeb {
 
+// software-pipelined loads in the global-source (first DIT) passes: measured SLOWER (zfwd 66 -> 81 us per 15 boxes at
+// AUSURF112, Si512 25.8 -> 28.8 us/band: the extra live butterfly spills at the 128-register budget); off by default
+#ifdef QEB_USE_GPF
+constexpr bool QEB_GPF = true;
+#else
+constexpr bool QEB_GPF = false;
+#endif
+
 // small per-CTA tables the fast kernels stage in shared memory (in the CPU emulation they point at the
 // global tables): twiddles of the pass direction, the x/y pruning map, the digit-reversal table, the
 // stick list of the z group
@@ -72,7 +80,7 @@ QEB_HD void zfwd_fast_phase(int ph, int tid, int nthr, const VlocTables& t, cons
     NoMid nm;
     if (ph == 0) {
         G1Dst g{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.g1_zs};
-        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, g, s, nm);
+        SPassSel<PL, true, false, 0, QEB_GPF>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, g, s, nm);
     } else {
         SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, s, s, nm);
     }
@@ -136,7 +144,7 @@ QEB_HD void yfwd_fast_phase(int ph, int tid, int nthr, const VlocTables& t, int 
     if (np == 1)
         SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, gs, cd, nm);
     else if (ph == 0)
-        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, gs, w, nm);
+        SPassSel<PL, true, false, 0, QEB_GPF>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, gs, w, nm);
     else if (p == 0)
         SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, w, cd, nm);
     else
