@@ -533,3 +533,32 @@ def test_sum_band_rho_ausurf_grid(mods):
     h.sum_band_rho(d.npw, d.npw, m, inp["psi"], w, rho)
     assert relerr(rho, ref) < 1e-12
     h.close()
+
+
+@pytest.mark.parametrize("name", ["si2_small", "si2_small_gamma"])
+def test_edge_cases_empty_and_tight(mods, name):
+    """m = 0 is a no-op for every entry point (the reference's loops simply do not execute); lda == n (no pad rows);
+    a batch larger than the number of bands; a single band on the Gamma path (odd remainder, vloc_psi_acc.f90:93-99)."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    m = 3
+    inp = R.synthetic_inputs(d, m, [4, 4], seed=8, lda=d.npw, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    assert lda == n
+    h = qe.HPsi(batch=16)
+    h.setup_from(d, inp)
+    sentinel = np.full((m, lda), 3.0 + 4.0j)
+    out = sentinel.copy()
+    h.h_psi(lda, n, 0, inp["psi"], out)
+    h.s_psi(lda, n, 0, inp["psi"], out)
+    (h.vloc_psi_gamma if d.gamma_only else h.vloc_psi_k)(lda, n, 0, inp["psi"], None, out)
+    rho = np.ones(d.nnr)
+    h.sum_band_rho(lda, n, 0, inp["psi"], np.zeros(1), rho)
+    assert np.array_equal(out, sentinel) and np.all(rho == 1.0)
+    ref, _ = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    h.h_psi(lda, n, m, inp["psi"], out)
+    assert relerr(out, ref) < TOL
+    one = np.zeros((1, lda), dtype=complex)
+    h.h_psi(lda, n, 1, inp["psi"][:1].copy(), one)
+    assert relerr(one, ref[:1]) < TOL
+    h.close()
