@@ -209,6 +209,10 @@ k_calbec3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi,
     const int g_beg = blockIdx.z * gchunk;
     const int g_end = min(n, g_beg + gchunk);
     const int nkt = (g_end - g_beg + C3_KG - 1) / C3_KG;
+    // valid 8x8 blocks of this warp's tile (edge tiles of the projector / band dimensions)
+    const int miv = max(0, min(MI, (nkb - (i0 + wm * 8 * MI) + 7) / 8));
+    const int njv = max(0, min(3, (m - (j0 + wn * 24) + 7) / 8));
+    const bool full = miv == MI && njv == 3;
 
     double p1[MI][3][2], p2[MI][3][2], p3[MI][3][2];
 #pragma unroll
@@ -274,17 +278,29 @@ k_calbec3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ psi,
                 bi[nj] = b.y;
                 bd[nj] = b.y - b.x;
             }
+            if (full) {
 #pragma unroll
-            for (int nj = 0; nj < 3; ++nj)
+                for (int nj = 0; nj < 3; ++nj)
 #pragma unroll
-                for (int mi = 0; mi < MI; ++mi) {
-                    dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], br[nj]);
-                    dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], bi[nj]);
-                }
+                    for (int mi = 0; mi < MI; ++mi) {
+                        dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], br[nj]);
+                        dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], bi[nj]);
+                    }
 #pragma unroll
-            for (int nj = 0; nj < 3; ++nj)
+                for (int nj = 0; nj < 3; ++nj)
 #pragma unroll
-                for (int mi = 0; mi < MI; ++mi) dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bd[nj]);
+                    for (int mi = 0; mi < MI; ++mi) dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bd[nj]);
+            } else {  // edge tile: 8x8 blocks without a valid projector row or band column are skipped (warp-uniform)
+#pragma unroll
+                for (int nj = 0; nj < 3; ++nj)
+#pragma unroll
+                    for (int mi = 0; mi < MI; ++mi)
+                        if (nj < njv && mi < miv) {
+                            dmma(p1[mi][nj][0], p1[mi][nj][1], ar[mi], br[nj]);
+                            dmma(p2[mi][nj][0], p2[mi][nj][1], ai[mi], bi[nj]);
+                            dmma(p3[mi][nj][0], p3[mi][nj][1], as[mi], bd[nj]);
+                        }
+            }
         }
     }
     cp_async_wait<0>();
@@ -524,9 +540,12 @@ k_addvus3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ ps, 
     cplx* sm = reinterpret_cast<cplx*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NTHR = 1024 / MI, WM = 8 / MI;  // warps along the band dimension
-    const int wm = warp % WM, wn = warp / WM;
+    // consecutive warps (= the four SM sub-partitions) share one band slice: when the last band tile is only partly
+    // populated, the warps that still have bands are spread over all four tensor units and the others skip their MMAs
+    const int wm = warp / 4, wn = warp % 4;
     const int r = lane >> 2, k = lane & 3;
     const int j0 = blockIdx.x * A3_BT, g0 = blockIdx.y * A3_GT;
+    const bool has_bands = (j0 + wm * 8 * MI) < m;
     const int nkt = (nkb + A3_KI - 1) / A3_KI;
 
     double p1[MI][3][2], p2[MI][3][2], p3[MI][3][2];
@@ -575,6 +594,7 @@ k_addvus3m(const cplx* __restrict__ vkb, int npwx, const cplx* __restrict__ ps, 
         const cplx* Vs = Ps + (size_t)A3_BT * A3_LDP;
         const cplx* Aw = Ps + (size_t)(wm * 8 * MI + r) * A3_LDP + k;   // A[band][i]
         const cplx* Bw = Vs + (size_t)k * A3_LDV + wn * 24 + r;     // B[i][g]
+        if (has_bands)
 #pragma unroll
         for (int kk = 0; kk < A3_KI; kk += 4) {
             double ar[MI], ai[MI], as[MI];
