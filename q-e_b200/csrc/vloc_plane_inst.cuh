@@ -9,6 +9,14 @@
 namespace qeb {
 
 
+// named barriers over one line group between passes of the same direction: measured SLOWER than CTA barriers
+// (V_loc 26.97 -> 27.86 us/band at AUSURF112); off unless QEB_USE_PLANE_GROUPBAR is defined
+#ifdef QEB_USE_PLANE_GROUPBAR
+constexpr bool QEB_PLANE_GROUPBAR = true;
+#else
+constexpr bool QEB_PLANE_GROUPBAR = false;
+#endif
+
 QEB_D void pl_cp_async16(void* smem_dst, const void* gsrc)
 {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -54,7 +62,19 @@ __global__ void __launch_bounds__(MAXT) k_vloc_plane_f(const __grid_constant__ V
 #pragma unroll 1
         for (int ph = 0; ph < nph; ++ph) {
             plane_phase<PLX, PLY>(ph, tid, nthr, t, z, P, stin, stout, sm);
-            __syncthreads();
+            // Between two passes of the same direction only the warps of one line group exchange data (group g = warp
+            // % ng owns lines 32g..32g+31 in both passes): a named barrier over that group replaces the CTA barrier.
+            // ph == 0 keeps the CTA barrier: the prefetch below overwrites stin, which every group reads in phase 0.
+            const bool ycur = ph < PLY::NP || ph >= PLY::NP + 2 * PLX::NP - 1;
+            const bool ynxt = (ph + 1) < PLY::NP || (ph + 1) >= PLY::NP + 2 * PLX::NP - 1;
+            const int ng = ((ycur ? nxw : t.nr2) + QEB_TL - 1) / QEB_TL;
+            const int nwt = nthr / QEB_TL;
+            if (QEB_PLANE_GROUPBAR && ph > 0 && ph + 1 < nph && ycur == ynxt && ng > 1 && ng <= 15 && nwt % ng == 0) {
+                const int g = (tid / QEB_TL) % ng;
+                asm volatile("bar.sync %0, %1;" ::"r"(1 + g), "r"((nwt / ng) * QEB_TL) : "memory");
+            } else {
+                __syncthreads();
+            }
             if (ph == 0 && b + 1 < b1) {  // stin is consumed: fetch the next box's row behind the remaining phases
                 const cplx* row = t.g1 + (size_t)(b + 1) * t.g1_box + (size_t)z * t.g1_zs;
                 for (int i = tid; i < nst; i += nthr) pl_cp_async16(stin + i, row + i);
