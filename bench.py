@@ -353,18 +353,18 @@ def run_ours(args):
                          "ms_projector_section": ms_nl,
                          "peak_source": "148 SMs x 64 FP64 FMA/clk x %.0f MHz (FP64 tensor = FP64 vector rate on B200); "
                                         "cuBLAS DGEMM 4096^3 in this run: %.1f TFLOP/s" % (sm_mhz, dgemm_tf)}
+    kpb = h.vloc_kernels_per_batch()  # 3 with the fused plane kernel (zinv, plane, zfwd), else 5
     # DRAM traffic of the same launches from the committed `ncu --set full` capture (dram__bytes_read+write, per launch)
     if roofline_gemm and args.workload == "ausurf112" and mm == 800 and three_m:
         roofline_gemm["traffic"] = 9.337911e9 + 0.174068e9 + 5.360086e9 + 1.208370e9
         roofline_gemm["traffic_source"] = ("profiles/r1q_gemm_m800_ncu_full.csv: k_calbec3m 9.34+0.17 GB, k_addvus3m 5.36+1.21 GB "
                                            "per launch at m=800 (algorithmic operands: vkb 3.08 GB + psi/hpsi 1.22 GB each, per kernel)")
-    if args.workload == "ausurf112" and st["batch"] == 15:
+    if args.workload == "ausurf112" and kpb == 3:
         roofline_vloc["traffic"] = (23.70e6 + 19.23e6 + 84.56e6 + 21.48e6 + 95.52e6 + 8.47e6) / 15 * mm
         roofline_vloc["traffic_source"] = ("profiles/r1q_vloc_b15_ncu_full.csv: zinv 42.9 MB, plane 106.0 MB, zfwd 104.0 MB per "
-                                           "batch of 15 boxes, scaled to the bands of the section")
+                                           "batch of 15 boxes (per-box figures scaled to the bands of the section)")
     # `roofline` = the kernel family with the largest share of the step
     roofline = roofline_gemm if (roofline_gemm and ms_nl >= ms_vloc) else roofline_vloc
-    kpb = h.vloc_kernels_per_batch()  # 3 with the fused plane kernel (zinv, plane, zfwd), else 5
     launches_step = nbatches * kpb + (4 if nkb else 0) + 1
     roofline_vloc["kernel"] = ("V_loc pass pipeline (3 kernels/batch: zinv, fused plane y|x*V*x|y, zfwd)" if kpb == 3 else
                                "V_loc pass pipeline (5 kernels/batch: zinv,yinv,xfus,yfwd,zfwd)")
