@@ -333,7 +333,6 @@ QEB_HD void yinv_phase(int ph, int tid, int nthr, const VlocTables& t, int ztile
     const int TY = t.TY, ldc = TY + 1;
     const int z0 = ztile * TY;
     const int nl = (t.nr3 - z0) < TY ? (t.nr3 - z0) : TY;
-    const int ns = t.plane_ns[xa], s0 = t.plane_s0[xa];
     cplx* C = smem;
     cplx* W = smem + (size_t)t.nsmax * ldc;
     const int np = t.py.npass;
@@ -368,7 +367,6 @@ QEB_HD void yfwd_phase(int ph, int tid, int nthr, const VlocTables& t, int ztile
     const int TY = t.TY, ldc = TY + 1;
     const int z0 = ztile * TY;
     const int nl = (t.nr3 - z0) < TY ? (t.nr3 - z0) : TY;
-    const int ns = t.plane_ns[xa], s0 = t.plane_s0[xa];
     cplx* C = smem;
     cplx* W = smem + (size_t)t.nsmax * ldc;
     const int np = t.py.npass;

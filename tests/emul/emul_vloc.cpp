@@ -204,6 +204,80 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
     return 0;
 }
 
+// sum_band density loop: zinv + yinv phases as in emul_vloc, then the xacc phases (generic, or the static-plan variant
+// when g_fast is set) with the accumulator flushed into rho once per batch. rho (nnr, x fastest) is INOUT.
+extern "C" int emul_sumband(int nr1, int nr2, int nr3, int npw, const int* nl, const int* nlm, const int* igk, int ngm,
+                            int lda, int m, const double* psi, const double* w, double* rho, int nthr, int batch)
+{
+    HostVlocTables H;
+    std::string err = build_vloc_tables(nr1, nr2, nr3, npw, nl, nlm, igk, ngm, H);
+    if (!err.empty()) return 1;
+    VlocTables t;
+    memset(&t, 0, sizeof(t));
+    t.nr1 = nr1; t.nr2 = nr2; t.nr3 = nr3;
+    t.nst = H.nst; t.nxw = H.nxw; t.npos = nr2 * nr3;
+    upload_plan(H.px, t.px); upload_plan(H.py, t.py); upload_plan(H.pz, t.pz);
+    t.xmap = H.xmap.data(); t.plane_s0 = H.plane_s0.data(); t.plane_ns = H.plane_ns.data(); t.ymap = H.ymap.data();
+    t.TZ = H.TZ; t.ngrp = H.ngrp;
+    t.grp_stick = H.grp_stick.data(); t.grp_nl = H.grp_nl.data(); t.grp_div = H.grp_div.data();
+    t.grp_coef_off = H.grp_coef_off.data(); t.coef_ig = H.coef_ig.data(); t.coef_slot = H.coef_slot.data();
+    t.coef_slot2 = H.gamma ? H.coef_slot2.data() : nullptr;
+    t.TY = H.TY; t.nty = H.nty; t.divTY = make_fastdiv(H.TY);
+    { int last = nr3 - (H.nty - 1) * H.TY; t.divTYlast = make_fastdiv(last); }
+    t.TX = H.TX; t.ntx = H.ntx; t.divTX = make_fastdiv(H.TX);
+    { int last = t.npos - (H.ntx - 1) * H.TX; t.divTXlast = make_fastdiv(last); }
+    t.nsmax = H.nsmax;
+    t.g1_box = (size_t)H.nst * nr3; t.g1_zs = (size_t)H.nst; t.g2_box = (size_t)H.nxw * t.npos;
+    std::vector<cplx> g1(t.g1_box * batch), g2(t.g2_box * batch);
+    t.g1 = g1.data(); t.g2 = g2.data();
+    const cplx nanv = mk(0.0 / 0.0, 0.0 / 0.0);
+    std::vector<cplx> smem(std::max(std::max(H.smem_z, H.smem_y), H.smem_x) / 16 + 16);
+    std::vector<double> racc((size_t)nr1 * H.TX);
+    std::vector<int> irev(nr1);
+    for (int i = 0; i < nr1; ++i) irev[H.px.rev[i]] = i;
+    VlocIO io;
+    io.psi = (const cplx*)psi; io.hpsi = nullptr; io.g2kin = nullptr; io.lda = lda; io.n = npw; io.nbands = m; io.gamma = H.gamma;
+    const int nboxes_total = H.gamma ? (m + 1) / 2 : m;
+    const int pthr = ((nthr + 31) / 32) * 32;
+    for (int bx0 = 0; bx0 < nboxes_total; bx0 += batch) {
+        const int nb = std::min(batch, nboxes_total - bx0);
+        io.band0 = H.gamma ? 2 * bx0 : bx0;
+        for (auto& x : g1) x = nanv;
+        for (auto& x : g2) x = nanv;
+        for (int box = 0; box < nb; ++box) {
+            for (int g = 0; g < H.ngrp; ++g) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < zinv_nphase(t); ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+            }
+            for (int xa = 0; xa < H.nxw; ++xa)
+                for (int zt = 0; zt < H.nty; ++zt) {
+                    for (auto& x : smem) x = nanv;
+                    for (int ph = 0; ph < ypass_nphase(t); ++ph)
+                        for (int tid = 0; tid < nthr; ++tid) pick_y(t.py, true)(ph, tid, nthr, t, zt, xa, box, smem.data(), FastTabs{t.py.tw, t.ymap + (size_t)xa * t.nr2, t.py.rev, nullptr});
+                }
+        }
+        for (int tile = 0; tile < H.ntx; ++tile) {
+            for (int tid = 0; tid < pthr; ++tid) xacc_zero_phase(tid, pthr, t, racc.data());
+            for (int box = 0; box < nb; ++box) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < t.px.npass; ++ph)
+                    for (int tid = 0; tid < pthr; ++tid) {
+                        bool done = false;
+                        if (g_fast) {
+#define X(PL) if (!done && PL::matches(t.px)) { xacc_fast_phase<PL>(ph, tid, pthr, t, io, w, tile, box, smem.data(), racc.data(), FastTabs{t.px.tw, t.xmap, nullptr, nullptr}); done = true; }
+                            QEB_FOR_PLANS(X)
+#undef X
+                        }
+                        if (!done) xacc_phase(ph, tid, pthr, t, io, w, tile, box, smem.data(), racc.data());
+                    }
+            }
+            for (int tid = 0; tid < pthr; ++tid) xacc_flush_phase(tid, pthr, t, tile, irev.data(), racc.data(), rho);
+        }
+    }
+    return 0;
+}
+
 extern "C" int emul_fullfft(int nr1, int nr2, int nr3, int howmany, int sign, double* f, int nthr)
 {
     HostPlan hx, hy, hz;

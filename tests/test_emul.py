@@ -164,3 +164,31 @@ def test_plane_and_z_low_register_plans_ausurf(emul, monkeypatch):
     monkeypatch.setenv("QEB_YPLAN", "4,4,4")
     monkeypatch.setenv("QEB_ZPLAN", "8,5,5")
     _run_plane_emul(emul, "ausurf112", 1, 1024, 1)
+
+
+@pytest.mark.parametrize("name", ["si2_small", "si2_small_gamma", "si2", "ortho_small"])
+@pytest.mark.parametrize("fast", [0, 1])
+def test_sum_band_density_phases(emul, name, fast):
+    """the density-accumulation phases of qeb_sum_band_rho (vloc_kernels.cuh xacc_*, vloc_fast.cuh xacc_fast_phase) on
+    the CPU against the oracle restatement of the sum_band loop (PW/src/sum_band.f90:326-647)"""
+    emul.emul_sumband.argtypes = [ctypes.c_int] * 4 + [ctypes.c_void_p] * 3 + [ctypes.c_int] * 3 + [ctypes.c_void_p] * 3 + [ctypes.c_int] * 2
+    emul.emul_set_fast(fast)
+    try:
+        d = D.config_descriptor(name)
+        m = 5
+        inp = R.synthetic_inputs(d, m, [4, 4], seed=3)
+        lda, n = inp["lda"], inp["n"]
+        rng = np.random.default_rng(1)
+        w = np.ascontiguousarray(rng.uniform(0.0, 2.0, m))
+        rho0 = rng.uniform(0.0, 1.0, d.nnr)
+        ref = R.sum_band_rho(d, lda, n, m, inp["psi"], w, rho0.copy())
+        rho = rho0.copy()
+        nl_ = np.ascontiguousarray(d.nl, dtype=np.int32)
+        nlm = np.ascontiguousarray(d.nlm, dtype=np.int32) if d.gamma_only else None
+        igk = None if d.gamma_only else np.ascontiguousarray(d.igk, dtype=np.int32)
+        rc = emul.emul_sumband(d.nr1, d.nr2, d.nr3, n, p(nl_), p(nlm), p(igk), d.ngm, lda, m, p(inp["psi"]), p(w), p(rho),
+                               96 if fast else 37, 2)
+        assert rc == 0
+        assert np.abs(rho - ref).max() / np.abs(ref).max() < 1e-13
+    finally:
+        emul.emul_set_fast(0)
