@@ -51,6 +51,9 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_vloc_psi_k(ctx, lda, n, m, psi, v, hpsi) BIND(C, name='qeb_vloc_psi_k')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, v, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_vloc_psi_nc(ctx, lda, n, m, psi, v4, hpsi) BIND(C, name='qeb_vloc_psi_nc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, v4, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
     INTEGER(C_INT) FUNCTION qeb_vloc_psi_gamma(ctx, lda, n, m, psi, v, hpsi) BIND(C, name='qeb_vloc_psi_gamma')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, v, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
     END FUNCTION
@@ -326,6 +329,38 @@ SUBROUTINE vloc_psi_gamma_qeb(lda, n, m, psi, v, hpsi)
   CALL qeb200_sync_state()
   CALL qeb200_check(qeb_vloc_psi_gamma(ctx, lda, n, m, C_LOC(psi), C_LOC(v), C_LOC(hpsi)), 'vloc_psi_gamma')
   vloc_loaded = -2
+END SUBROUTINE
+
+SUBROUTINE vloc_psi_nc_qeb(lda, n, m, psi, v, hpsi)
+  !! vloc_psi_nc (PW/src/vloc_psi_acc.f90:269): noncollinear V_loc. domag: the 2x2 product on the device
+  !! (qeb_vloc_psi_nc); otherwise v(:,1) on npol*m columns of leading dimension lda (qeb_vloc_psi_k).
+  !! v is declared (dfftp%nnr,4) by the reference but only its first dffts%nnr rows are used (:291,:331-347): the four
+  !! columns are packed before they go to the library.
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds, ONLY: DP
+  USE qeb200_c; USE qeb200_state
+  USE fft_base, ONLY: dffts, dfftp
+  USE noncollin_module, ONLY: npol, domag
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n, m
+  COMPLEX(DP), INTENT(IN), TARGET :: psi(lda*npol, m)
+  COMPLEX(DP), INTENT(INOUT), TARGET :: hpsi(lda, npol, m)
+  REAL(DP), INTENT(IN), TARGET :: v(dfftp%nnr, 4)
+  REAL(DP), ALLOCATABLE, TARGET :: v4(:, :)
+  IF (dffts%has_task_groups .OR. dffts%lpara) THEN
+    CALL vloc_psi_nc(lda, n, m, psi, v, hpsi)   ! reference routine
+    RETURN
+  END IF
+  CALL qeb200_sync_state()
+  IF (domag) THEN
+    ALLOCATE (v4(dffts%nnr, 4))
+    v4(:, :) = v(1:dffts%nnr, 1:4)
+    CALL qeb200_check(qeb_vloc_psi_nc(ctx, lda, n, m, C_LOC(psi), C_LOC(v4), C_LOC(hpsi)), 'vloc_psi_nc')
+    DEALLOCATE (v4)
+  ELSE
+    CALL qeb200_check(qeb_vloc_psi_k(ctx, lda, n, npol*m, C_LOC(psi), C_LOC(v), C_LOC(hpsi)), 'vloc_psi_nc')
+    vloc_loaded = -2
+  END IF
 END SUBROUTINE
 
 !----------------------------------------------------------------------------

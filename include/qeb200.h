@@ -91,6 +91,13 @@ int qeb_h_psi(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* hpsi);
 int qeb_vloc_psi_k(qeb_ctx* ctx, int lda, int n, int m, const void* psi, const double* v, void* hpsi);
 /* vloc_psi_gamma(lda,n,m,psi,v,hpsi) PW/src/vloc_psi_acc.f90:9-145 */
 int qeb_vloc_psi_gamma(qeb_ctx* ctx, int lda, int n, int m, const void* psi, const double* v, void* hpsi);
+/* vloc_psi_nc(lda,n,m,psi,v,hpsi)    PW/src/vloc_psi_acc.f90:269-369, domag branch (:329-341)   
+ * Noncollinear spinors with magnetisation: psi(lda*2,m), hpsi(lda,2,m) INOUT, v(dffts%nnr,4):
+ *   hpsi_up += F[ psi_up(r) (v1+v4) + psi_dn(r) (v2 - i v3) ],  hpsi_dn += F[ psi_dn(r) (v1-v4) + psi_up(r) (v2 + i v3) ].
+ * v == NULL: the potential of qeb_set_vloc_nc. Serial k-point descriptor only. The non-magnetic branch (:342-348,
+ * v(:,1) on both components) is qeb_vloc_psi_k on 2m columns of leading dimension lda. */
+int qeb_set_vloc_nc(qeb_ctx* ctx, const double* v4);
+int qeb_vloc_psi_nc(qeb_ctx* ctx, int lda, int n, int m, const void* psi, const double* v4, void* hpsi);
 
 /* invfft / fwfft (kind, f, dfft, howmany)  FFTXlib/src/fft_interfaces.f90:19-80,
  * fft_fwinv.f90:10-216: in-place 3-D transform of howmany boxes f(nnr*howmany).

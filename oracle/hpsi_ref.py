@@ -108,6 +108,29 @@ def vloc_psi_gamma(d: Descriptor, lda: int, n: int, m: int, psi: np.ndarray, v: 
     return hpsi
 
 
+def vloc_psi_nc(d: Descriptor, lda: int, n: int, m: int, psi: np.ndarray, v: np.ndarray, hpsi: np.ndarray, domag=True):
+    """Noncollinear V_loc, PW/src/vloc_psi_acc.f90:269-369. psi, hpsi: (m, 2*lda) complex = Fortran psi(lda*npol, m) /
+    hpsi(lda, npol, m) memory (component ipol of band b at [b, ipol*lda : ipol*lda + n]); v: (4, nnr) = Fortran v(nnr,4)
+    memory. hpsi is INOUT. domag: the 2x2 product of :330-340, else v(:,1) on both components (:342-348)."""
+    nr = (d.nr1, d.nr2, d.nr3)
+    idx = d.nl[d.igk[:n] - 1] - 1
+    for b in range(m):
+        r = []
+        for ipol in range(2):
+            box = np.zeros(d.nnr, dtype=np.complex128)
+            box[idx] = psi[b, ipol * lda:ipol * lda + n]
+            r.append(cfft3ds(box, nr, +1, d.isind, d.iplw))
+        if domag:
+            sup = r[0] * (v[0] + v[3]) + r[1] * (v[1] - 1j * v[2])
+            sdwn = r[1] * (v[0] - v[3]) + r[0] * (v[1] + 1j * v[2])
+        else:
+            sup, sdwn = r[0] * v[0], r[1] * v[0]
+        for ipol, box in enumerate((sup, sdwn)):
+            box = cfft3ds(box, nr, -1, d.isind, d.iplw)
+            hpsi[b, ipol * lda:ipol * lda + n] += box[idx]
+    return hpsi
+
+
 def sum_band_rho(d: Descriptor, lda: int, n: int, m: int, evc: np.ndarray, w: np.ndarray, rho: np.ndarray):
     """Density part of sum_band: rho (nnr, INOUT) += sum_b w[b] |psi_b(r)|^2, w[b] = wg(b,ik)/omega.
     k: wave_g2r + get_rho_k per band (PW/src/sum_band.f90:578-593, :650-671); Gamma: two bands per transform,

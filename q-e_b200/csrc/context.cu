@@ -112,6 +112,8 @@ struct qeb_ctx {
     // potential
     bool have_v = false;
     DevBuf v_d, vp_d, vpl_d;
+    DevBuf vnc_d;  // noncollinear 2x2 potential, four arrays in the vp layout
+    bool have_vnc = false;
     DevBuf revx_d;
     // full-box FFT plans
     DevBuf full_plan_d;
@@ -698,6 +700,36 @@ int qeb_set_vloc(qeb_ctx* c, const double* vrs)
     if (!c->have_grid) QEB_FAIL(c, 30, "qeb_set_vloc: qeb_set_grid has not been called");
     if (!vrs) QEB_FAIL(c, 31, "qeb_set_vloc: null potential");
     int rc = prepare_v(c, vrs);
+    if (rc) return rc;
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// v(dffts%nnr, 4) of vloc_psi_nc (PW/src/vloc_psi_acc.f90:291): four consecutive arrays, each permuted like vp
+static int prepare_v_nc(qeb_ctx* c, const double* v4)
+{
+    const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
+    const void* vd = nullptr;
+    int rc = stage_in(c, v4, 4 * nnr * 8, c->v_d, &vd);
+    if (rc) return rc;
+    QEB_CUDA(c, c->vnc_d.ensure(4 * nnr * 8));
+    const double scale = 1.0 / ((double)c->nr1 * c->nr2 * c->nr3);
+    for (int k = 0; k < 4; ++k)
+        QEB_CUDA(c, vloc_prepare_v((const double*)vd + k * nnr, (double*)c->vnc_d.p + k * nnr, c->fpx.rev, c->nr1, c->nr2,
+                                   c->nr3, scale, c->stream));
+    c->T.vnc = (const double*)c->vnc_d.p;
+    c->have_vnc = true;
+    return 0;
+}
+
+int qeb_set_vloc_nc(qeb_ctx* c, const double* v4)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_grid) QEB_FAIL(c, 30, "qeb_set_vloc_nc: qeb_set_grid has not been called");
+    if (!v4) QEB_FAIL(c, 31, "qeb_set_vloc_nc: null potential");
+    if (c->dist || c->gamma) QEB_FAIL(c, 32, "qeb_set_vloc_nc: serial k-point descriptor only (noncollinear has no gamma tricks)");
+    int rc = prepare_v_nc(c, v4);
     if (rc) return rc;
     QEB_CUDA(c, cudaStreamSynchronize(c->stream));
     return 0;
@@ -1486,6 +1518,47 @@ static int vloc_entry(qeb_ctx* c, int lda, int n, int m, const void* psi, const 
     if ((rc = h_psi_cols(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true, false, false))) return rc;
     if (!out_dev) {
         QEB_CUDA(c, cudaMemcpyAsync(hpsi, hpsi_d, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+// vloc_psi_nc with domag (PW/src/vloc_psi_acc.f90:269-369): psi(lda*2, m), hpsi(lda, 2, m) INOUT. The two components of a
+// band are columns 2b, 2b+1 of leading dimension lda, i.e. boxes 2b, 2b+1 of the batch.
+int qeb_vloc_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v4, void* hpsi)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_vloc_psi_nc");
+    if (rc) return rc;
+    if (c->dist || c->gamma) QEB_FAIL(c, 63, "qeb_vloc_psi_nc: serial k-point descriptor only");
+    if (m == 0) return 0;
+    if (v4 && (rc = prepare_v_nc(c, v4))) return rc;
+    if (!c->have_vnc) QEB_FAIL(c, 50, "qeb_vloc_psi_nc: no 2x2 potential set (qeb_set_vloc_nc)");
+    if (2 * c->cfg.smem_x > c->max_smem) QEB_FAIL(c, 64, "qeb_vloc_psi_nc: x tile of this grid does not fit twice in shared memory");
+    const size_t bytes = (size_t)lda * 2 * m * 16;
+    const void* psi_d;
+    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
+    const bool out_dev = is_device_ptr(hpsi);
+    const void* hin;
+    if ((rc = stage_in(c, hpsi, bytes, c->hpsi_stage, &hin))) return rc;  // INOUT
+    VlocIO io;
+    io.psi = (const cplx*)psi_d;
+    io.hpsi = (cplx*)hin;
+    io.g2kin = nullptr;
+    io.lda = lda;
+    io.n = n;
+    io.nbands = 2 * m;
+    io.gamma = 0;
+    const int bands_per_batch = std::max(1, c->batch / 2);
+    for (int b0 = 0; b0 < m; b0 += bands_per_batch) {
+        const int nb = std::min(bands_per_batch, m - b0);
+        io.band0 = 2 * b0;
+        QEB_CUDA(c, vloc_launch_batch_nc(c->T, io, c->cfg, nb, c->stream));
+    }
+    if (!out_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hin, bytes, cudaMemcpyDeviceToHost, c->stream));
         QEB_CUDA(c, cudaStreamSynchronize(c->stream));
         return 0;
     }

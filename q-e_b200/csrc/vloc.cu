@@ -60,6 +60,17 @@ __global__ void __launch_bounds__(256) k_vloc_xfus(const __grid_constant__ VlocT
 
 
 
+// spinor x pass (noncollinear 2x2 potential): block = (line tile, band), two shared-memory tiles
+__global__ void __launch_bounds__(256) k_vloc_xspin(const __grid_constant__ VlocTables t)
+{
+    QEB_SMEM;
+    const int nph = xspin_nphase(t);
+    for (int ph = 0; ph < nph; ++ph) {
+        xspin_phase(ph, threadIdx.x, blockDim.x, t, blockIdx.x, blockIdx.y, smem);
+        __syncthreads();
+    }
+}
+
 // density accumulation: x inverse of every box of the batch + |psi(r)|^2 weights, one CTA per line tile
 __global__ void __launch_bounds__(256) k_vloc_xacc(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io,
                                                    const double* __restrict__ w, int nboxes, double* __restrict__ rho)
@@ -193,6 +204,7 @@ cudaError_t vloc_init_attrs(size_t max_smem)
     if ((e = cudaFuncSetAttribute(k_vloc_yfwd, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
     if ((e = cudaFuncSetAttribute(k_vloc_xfus, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
     if ((e = cudaFuncSetAttribute(k_vloc_xacc, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
+    if ((e = cudaFuncSetAttribute(k_vloc_xspin, cudaFuncAttributeMaxDynamicSharedMemorySize, s))) return e;
 #define X(PL) FastLaunch<PL>::attrs(s);
     QEB_FOR_PLANS(X)
 #undef X
@@ -236,6 +248,25 @@ cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocL
     cudaError_t e;
     if ((e = vloc_launch_zpass(true, t, io, cfg, nboxes, st)) != cudaSuccess) return e;
     if ((e = vloc_launch_planes(t, cfg, nboxes, st)) != cudaSuccess) return e;
+    return vloc_launch_zpass(false, t, io, cfg, nboxes, st);
+}
+
+cudaError_t vloc_launch_batch_nc(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nbands,
+                                 cudaStream_t st)
+{
+    if (nbands <= 0) return cudaSuccess;
+    if (!t.vnc || 2 * cfg.smem_x > cfg.max_smem) return cudaErrorInvalidConfiguration;
+    const int nboxes = 2 * nbands;
+    cudaError_t e;
+    if ((e = vloc_launch_zpass(true, t, io, cfg, nboxes, st)) != cudaSuccess) return e;
+    if (t.nxw > 0 && t.npos > 0) {
+        if (!launch_y(true, t, cfg, nboxes, st))
+            k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
+        k_vloc_xspin<<<dim3(t.ntx, nbands), cfg.threads_x, 2 * cfg.smem_x, st>>>(t);
+        if (!launch_y(false, t, cfg, nboxes, st))
+            k_vloc_yfwd<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
     return vloc_launch_zpass(false, t, io, cfg, nboxes, st);
 }
 

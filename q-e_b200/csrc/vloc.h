@@ -14,6 +14,10 @@ cudaError_t vloc_init_attrs(size_t max_smem);
 // one batch of nboxes boxes (bands for k, band pairs for Gamma)
 cudaError_t vloc_launch_batch(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
                               cudaStream_t st);
+// noncollinear batch of nbands spinors (2*nbands boxes: components of band b are boxes 2b, 2b+1 = columns 2b, 2b+1 of
+// io.psi / io.hpsi with leading dimension lda) through the 2x2 potential t.vnc: z | y | spinor x pass | y | z
+cudaError_t vloc_launch_batch_nc(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nbands,
+                                 cudaStream_t st);
 // the pieces of a batch, used separately by the slab-distributed path (an exchange sits between them):
 // z pass (inv: scatter + z inverse -> G1; !inv: G1 -> z forward + gather) and the three plane passes (y, fused x, y)
 cudaError_t vloc_launch_zpass(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,

@@ -60,6 +60,9 @@ struct VlocTables {
     const int* pl_xact;    // [nxw]     xa -> x
     const double* pl_v;    // [nr3][nr1 xpos][nr2 ypos] = v(rev_x[xpos], rev_y[ypos], z)/(nr1 nr2 nr3)
     int pl_ldp;            // row stride of the shared-memory plane (odd, >= nr1)
+    // noncollinear 2x2 potential (vloc_psi_nc): four arrays in the vp layout, consecutive, nr1*npos doubles each:
+    // v(:,1) .. v(:,4) of PW/src/vloc_psi_acc.f90:291, each /(nr1 nr2 nr3); nullptr: not set
+    const double* vnc;
 };
 
 struct VlocIO {
@@ -461,6 +464,60 @@ QEB_HD void xfus_phase(int ph, int tid, int nthr, const VlocTables& t, int tile,
             fft_pass<true, false>(tid, nthr, nl, dnl, pd, t.px.tw, -1.0, w, g, nm);
         else
             fft_pass<true, false>(tid, nthr, nl, dnl, pd, t.px.tw, -1.0, w, w, nm);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// P3 for spinors (noncollinear with magnetisation, PW/src/vloc_psi_acc.f90:315-341): the two components of a band are
+// boxes 2*pair and 2*pair+1 of the batch. block = (line tile, pair); both components are x-transformed into two
+// shared-memory tiles, mixed point by point with the 2x2 potential
+//   sup  = psi_up (v1+v4) + psi_dn (v2 - i v3),   sdwn = psi_dn (v1-v4) + psi_up (v2 + i v3)
+// and transformed back. Phases: np DIF passes | mix | np DIT passes. smem: 2*nr1*TX complex.
+// ---------------------------------------------------------------------------
+QEB_HD int xspin_nphase(const VlocTables& t) { return 2 * t.px.npass + 1; }
+
+QEB_HD void xspin_phase(int ph, int tid, int nthr, const VlocTables& t, int tile, int pair, cplx* smem)
+{
+    const int TX = t.TX;
+    const int p0 = tile * TX;
+    const int nl = (t.npos - p0) < TX ? (t.npos - p0) : TX;
+    const FastDiv dnl = pick_div(nl, TX, t.divTX, t.divTXlast);
+    const int np = t.px.npass;
+    const size_t tile_el = (size_t)t.nr1 * TX;
+    NoMid nm;
+    if (ph == np) {  // 2x2 mix in position order (the four potentials are permuted like vp)
+        const size_t vs = (size_t)t.nr1 * t.npos;
+        for (int i = tid; i < t.nr1 * nl; i += nthr) {
+            const int xpos = i / nl, line = i - xpos * nl;
+            const size_t iv = (size_t)xpos * t.npos + p0 + line;
+            const double v1 = t.vnc[iv], v2 = t.vnc[vs + iv], v3 = t.vnc[2 * vs + iv], v4 = t.vnc[3 * vs + iv];
+            cplx* pu = smem + xpos * TX + line;
+            cplx* pd = pu + tile_el;
+            const cplx u = *pu, d = *pd;
+            const double a = v1 + v4, b = v1 - v4;
+            // d*(v2 - i v3) = (d.x v2 + d.y v3) + i (d.y v2 - d.x v3);  u*(v2 + i v3) = (u.x v2 - u.y v3) + i (u.y v2 + u.x v3)
+            *pu = mk(u.x * a + (d.x * v2 + d.y * v3), u.y * a + (d.y * v2 - d.x * v3));
+            *pd = mk(d.x * b + (u.x * v2 - u.y * v3), d.y * b + (u.y * v2 + u.x * v3));
+        }
+        return;
+    }
+    for (int comp = 0; comp < 2; ++comp) {
+        SmemTile w{smem + comp * tile_el, TX};
+        G2XSrc g{t.g2 + (size_t)(2 * pair + comp) * t.g2_box, t.xmap, t.npos, p0};
+        if (ph < np) {  // DIF pass ph
+            const PassDesc pd = pass_of(t.px, ph);
+            if (ph == 0)
+                fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.px.tw, +1.0, g, w, nm);
+            else
+                fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.px.tw, +1.0, w, w, nm);
+        } else {  // DIT pass np-1 .. 0
+            const int p = 2 * np - ph;
+            const PassDesc pd = pass_of(t.px, p);
+            if (p == 0)
+                fft_pass<true, false>(tid, nthr, nl, dnl, pd, t.px.tw, -1.0, w, g, nm);
+            else
+                fft_pass<true, false>(tid, nthr, nl, dnl, pd, t.px.tw, -1.0, w, w, nm);
+        }
     }
 }
 

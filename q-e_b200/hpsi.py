@@ -55,6 +55,8 @@ def load_library():
     L.qeb_h_psi.argtypes = [P, I, I, I, P, P]
     L.qeb_vloc_psi_k.argtypes = [P, I, I, I, P, P, P]
     L.qeb_vloc_psi_gamma.argtypes = [P, I, I, I, P, P, P]
+    L.qeb_set_vloc_nc.argtypes = [P, P]
+    L.qeb_vloc_psi_nc.argtypes = [P, I, I, I, P, P, P]
     L.qeb_fft.argtypes = [P, I, I, P, I]
     L.qeb_calbec.argtypes = [P, I, P, I, P, I, I, P]
     L.qeb_add_vuspsi.argtypes = [P, I, I, I, P, P]
@@ -87,7 +89,7 @@ def load_library():
     L.qeb_nonlocal_only.argtypes = [P, I, I, I, P, P]
     L.qeb_vloc_kernels_per_batch.argtypes = [P]
     for name in ("qeb_create", "qeb_destroy", "qeb_set_pipeline", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
-                 "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_fft",
+                 "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_set_vloc_nc", "qeb_vloc_psi_nc", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
                  "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi", "qeb_set_gvectors", "qeb_g2_kin", "qeb_set_beta_tables",
@@ -354,6 +356,15 @@ class HPsi:
 
     def vloc_psi_gamma(self, lda, n, m, psi, v, hpsi):
         self._ck(self._L.qeb_vloc_psi_gamma(self._h, lda, n, m, _ptr(psi), _ptr(v), _ptr(hpsi)), "qeb_vloc_psi_gamma")
+        return hpsi
+
+    def set_vloc_nc(self, v4):
+        """the 2x2 potential v(dffts%nnr, 4) of the noncollinear magnetic case (vloc_psi_acc.f90:291)"""
+        self._ck(self._L.qeb_set_vloc_nc(self._h, _ptr(v4)), "qeb_set_vloc_nc")
+
+    def vloc_psi_nc(self, lda, n, m, psi, v, hpsi):
+        """vloc_psi_nc(lda, n, m, psi, v, hpsi), domag branch: psi(lda*2, m), hpsi(lda, 2, m) INOUT, v(nnr, 4) or None"""
+        self._ck(self._L.qeb_vloc_psi_nc(self._h, lda, n, m, _ptr(psi), _ptr(v), _ptr(hpsi)), "qeb_vloc_psi_nc")
         return hpsi
 
     def invfft(self, kind, f, howmany=1):

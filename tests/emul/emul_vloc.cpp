@@ -278,6 +278,88 @@ extern "C" int emul_sumband(int nr1, int nr2, int nr3, int npw, const int* nl, c
     return 0;
 }
 
+// noncollinear V_loc with the 2x2 potential: zinv / yinv phases on the 2m component boxes, the spinor x pass
+// (xspin_phase) per band, yfwd / zfwd. psi, hpsi: 2m columns of lda; v4: (4, nnr) x fastest. hpsi INOUT.
+extern "C" int emul_vloc_nc(int nr1, int nr2, int nr3, int npw, const int* nl, const int* igk, int ngm, int lda, int m,
+                            const double* psi, const double* v4, double* hpsi, int nthr, int batch_bands)
+{
+    HostVlocTables H;
+    std::string err = build_vloc_tables(nr1, nr2, nr3, npw, nl, nullptr, igk, ngm, H);
+    if (!err.empty()) return 1;
+    VlocTables t;
+    memset(&t, 0, sizeof(t));
+    t.nr1 = nr1; t.nr2 = nr2; t.nr3 = nr3;
+    t.nst = H.nst; t.nxw = H.nxw; t.npos = nr2 * nr3;
+    upload_plan(H.px, t.px); upload_plan(H.py, t.py); upload_plan(H.pz, t.pz);
+    t.xmap = H.xmap.data(); t.plane_s0 = H.plane_s0.data(); t.plane_ns = H.plane_ns.data(); t.ymap = H.ymap.data();
+    t.TZ = H.TZ; t.ngrp = H.ngrp;
+    t.grp_stick = H.grp_stick.data(); t.grp_nl = H.grp_nl.data(); t.grp_div = H.grp_div.data();
+    t.grp_coef_off = H.grp_coef_off.data(); t.coef_ig = H.coef_ig.data(); t.coef_slot = H.coef_slot.data();
+    t.TY = H.TY; t.nty = H.nty; t.divTY = make_fastdiv(H.TY);
+    { int last = nr3 - (H.nty - 1) * H.TY; t.divTYlast = make_fastdiv(last); }
+    t.TX = H.TX; t.ntx = H.ntx; t.divTX = make_fastdiv(H.TX);
+    { int last = t.npos - (H.ntx - 1) * H.TX; t.divTXlast = make_fastdiv(last); }
+    t.nsmax = H.nsmax;
+    const int batch = 2 * batch_bands;
+    t.g1_box = (size_t)H.nst * nr3; t.g1_zs = (size_t)H.nst; t.g2_box = (size_t)H.nxw * t.npos;
+    std::vector<cplx> g1(t.g1_box * batch), g2(t.g2_box * batch);
+    t.g1 = g1.data(); t.g2 = g2.data();
+    const size_t nnr = (size_t)nr1 * nr2 * nr3;
+    const double scale = 1.0 / (double)nnr;
+    std::vector<double> vnc(4 * nnr);
+    for (int k = 0; k < 4; ++k)
+        for (int xp = 0; xp < nr1; ++xp)
+            for (int y = 0; y < nr2; ++y)
+                for (int z = 0; z < nr3; ++z)
+                    vnc[k * nnr + (size_t)xp * t.npos + (size_t)y * nr3 + z] =
+                        v4[k * nnr + H.px.rev[xp] + (size_t)nr1 * (y + (size_t)nr2 * z)] * scale;
+    t.vnc = vnc.data();
+    const cplx nanv = mk(0.0 / 0.0, 0.0 / 0.0);
+    std::vector<cplx> smem(std::max(std::max(H.smem_z, H.smem_y), 2 * H.smem_x) / 16 + 16);
+    VlocIO io;
+    io.psi = (const cplx*)psi; io.hpsi = (cplx*)hpsi; io.g2kin = nullptr; io.lda = lda; io.n = npw; io.nbands = 2 * m; io.gamma = 0;
+    for (int b0 = 0; b0 < m; b0 += batch_bands) {
+        const int nbands = std::min(batch_bands, m - b0);
+        const int nb = 2 * nbands;
+        io.band0 = 2 * b0;
+        for (auto& x : g1) x = nanv;
+        for (auto& x : g2) x = nanv;
+        for (int box = 0; box < nb; ++box) {
+            for (int g = 0; g < H.ngrp; ++g) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < zinv_nphase(t); ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+            }
+            for (int xa = 0; xa < H.nxw; ++xa)
+                for (int zt = 0; zt < H.nty; ++zt) {
+                    for (auto& x : smem) x = nanv;
+                    for (int ph = 0; ph < ypass_nphase(t); ++ph)
+                        for (int tid = 0; tid < nthr; ++tid) pick_y(t.py, true)(ph, tid, nthr, t, zt, xa, box, smem.data(), FastTabs{t.py.tw, t.ymap + (size_t)xa * t.nr2, t.py.rev, nullptr});
+                }
+        }
+        for (int pair = 0; pair < nbands; ++pair)
+            for (int tile = 0; tile < H.ntx; ++tile) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < xspin_nphase(t); ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) xspin_phase(ph, tid, nthr, t, tile, pair, smem.data());
+            }
+        for (int box = 0; box < nb; ++box) {
+            for (int xa = 0; xa < H.nxw; ++xa)
+                for (int zt = 0; zt < H.nty; ++zt) {
+                    for (auto& x : smem) x = nanv;
+                    for (int ph = 0; ph < ypass_nphase(t); ++ph)
+                        for (int tid = 0; tid < nthr; ++tid) pick_y(t.py, false)(ph, tid, nthr, t, zt, xa, box, smem.data(), FastTabs{t.py.tw, t.ymap + (size_t)xa * t.nr2, t.py.rev, nullptr});
+                }
+            for (int g = 0; g < H.ngrp; ++g) {
+                for (auto& x : smem) x = nanv;
+                for (int ph = 0; ph < zfwd_nphase(t); ++ph)
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, false)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+            }
+        }
+    }
+    return 0;
+}
+
 extern "C" int emul_fullfft(int nr1, int nr2, int nr3, int howmany, int sign, double* f, int nthr)
 {
     HostPlan hx, hy, hz;

@@ -192,3 +192,36 @@ def test_sum_band_density_phases(emul, name, fast):
         assert np.abs(rho - ref).max() / np.abs(ref).max() < 1e-13
     finally:
         emul.emul_set_fast(0)
+
+
+@pytest.mark.parametrize("name", ["si2_small", "si2", "ortho_small"])
+@pytest.mark.parametrize("fast", [0, 1])
+def test_vloc_nc_phases(emul, name, fast):
+    """the spinor x pass (vloc_kernels.cuh xspin_phase: x DIF | 2x2 mix | x DIT on both components) inside the pass
+    pipeline, on the CPU, against the oracle restatement of vloc_psi_nc (PW/src/vloc_psi_acc.f90:269-369, domag)"""
+    emul.emul_vloc_nc.argtypes = [ctypes.c_int] * 4 + [ctypes.c_void_p] * 2 + [ctypes.c_int] * 3 + [ctypes.c_void_p] * 3 + [ctypes.c_int] * 2
+    emul.emul_set_fast(fast)
+    try:
+        d = D.config_descriptor(name)
+        m = 3
+        inp = R.synthetic_inputs(d, 2 * m, [4, 4], seed=5)
+        lda, n = inp["lda"], inp["n"]
+        rng = np.random.default_rng(11)
+        v4 = np.ascontiguousarray(rng.uniform(-1.0, 1.0, (4, d.nnr)))
+        psi = np.ascontiguousarray(inp["psi"]).reshape(m, 2 * lda)
+        h0 = (rng.standard_normal((m, 2 * lda)) + 1j * rng.standard_normal((m, 2 * lda)))
+        ref = R.vloc_psi_nc(d, lda, n, m, psi, v4, h0.copy())
+        out = np.ascontiguousarray(h0.copy())
+        nl_ = np.ascontiguousarray(d.nl, dtype=np.int32)
+        igk = np.ascontiguousarray(d.igk, dtype=np.int32)
+        rc = emul.emul_vloc_nc(d.nr1, d.nr2, d.nr3, n, p(nl_), p(igk), d.ngm, lda, m, p(psi), p(v4), p(out),
+                               96 if fast else 37, 2)
+        assert rc == 0
+        for b in range(m):
+            for ipol in range(2):
+                sl = slice(ipol * lda, ipol * lda + n)
+                assert np.abs(out[b, sl] - ref[b, sl]).max() / np.abs(ref[b, sl]).max() < 1e-13
+                pad = slice(ipol * lda + n, (ipol + 1) * lda)
+                assert np.array_equal(out[b, pad], h0[b, pad])
+    finally:
+        emul.emul_set_fast(0)

@@ -104,6 +104,49 @@ def test_vloc_psi(mods, name, m):
     h.close()
 
 
+@pytest.mark.parametrize("name", ["si2_small", "ortho_small", "si2", "al4"])
+@pytest.mark.parametrize("m", [1, 2, 5])
+def test_vloc_psi_nc(mods, name, m):
+    """noncollinear spinors through the 2x2 potential (vloc_psi_nc, domag): qeb_vloc_psi_nc against the oracle
+    restatement of PW/src/vloc_psi_acc.f90:269-369"""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    inp = R.synthetic_inputs(d, 2 * m, [4, 4], seed=m)
+    lda, n = inp["lda"], inp["n"]
+    rng = np.random.default_rng(17)
+    v4 = np.ascontiguousarray(rng.uniform(-1.0, 1.0, (4, d.nnr)))
+    psi = np.ascontiguousarray(inp["psi"]).reshape(m, 2 * lda)
+    h0 = rng.standard_normal((m, 2 * lda)) + 1j * rng.standard_normal((m, 2 * lda))
+    ref = R.vloc_psi_nc(d, lda, n, m, psi, v4, h0.copy())
+    h = qe.HPsi(batch=3)  # odd batch: one spinor per launch
+    h.setup_from(d, inp)
+    out = h0.copy()
+    h.vloc_psi_nc(lda, n, m, psi, v4, out)
+    live = np.zeros(2 * lda, bool)
+    live[:n] = live[lda:lda + n] = True
+    assert relerr(out[:, live], ref[:, live]) < TOL
+    assert np.array_equal(out[:, ~live], h0[:, ~live])  # rows beyond n of both components untouched
+    # device pointers, potential from the context, larger batch
+    h2 = qe.HPsi(batch=8)
+    h2.setup_from(d, inp)
+    h2.set_vloc_nc(v4)
+    psi_t = torch.from_numpy(np.nan_to_num(psi)).cuda()
+    out_t = torch.from_numpy(h0.copy()).cuda()
+    h2.vloc_psi_nc(lda, n, m, psi_t, None, out_t)
+    torch.cuda.synchronize()
+    assert relerr(out_t.cpu().numpy()[:, live], ref[:, live]) < TOL
+    # v2 = v3 = v4 = 0 reduces to the scalar path on 2m columns (the non-magnetic branch, :342-348)
+    v1 = np.zeros_like(v4)
+    v1[0] = inp["vrs"]
+    a = h0.copy()
+    h.vloc_psi_nc(lda, n, m, psi, v1, a)
+    b = h0.copy().reshape(2 * m, lda)
+    h.vloc_psi_k(lda, n, 2 * m, psi.reshape(2 * m, lda), inp["vrs"], b)
+    assert relerr(a.reshape(2 * m, lda)[:, :n], b[:, :n]) < TOL
+    h.close()
+    h2.close()
+
+
 @pytest.mark.parametrize("name", SMALL + ["si2", "al4"])
 @pytest.mark.parametrize("m", [1, 3, 4, 10])
 def test_h_psi(mods, name, m):

@@ -249,3 +249,28 @@ def test_sum_band_rho_restatement_parseval():
         if d.gamma_only:
             nrm = 2.0 * nrm - (np.abs(psi[:, 0]) ** 2 if d.gstart == 2 else 0.0)
         assert abs(rho.sum() / d.nnr - (w * nrm).sum()) < 1e-12
+
+
+def test_vloc_psi_nc_reduces_to_scalar_and_is_hermitian():
+    """vloc_psi_nc (vloc_psi_acc.f90:269-369): with v2=v3=v4=0 it is vloc_psi_k on both components; with a general
+    real v(:,1:4) the 2x2 operator is Hermitian: <phi|V psi> = conj(<psi|V phi>) on the sphere."""
+    d = D.config_descriptor("si2_small")
+    m = 2
+    inp = R.synthetic_inputs(d, 2 * m, [4, 4], seed=2, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    psi = np.ascontiguousarray(inp["psi"]).reshape(m, 2 * lda)
+    v4 = np.zeros((4, d.nnr))
+    v4[0] = inp["vrs"]
+    a = R.vloc_psi_nc(d, lda, n, m, psi, v4, np.zeros((m, 2 * lda), complex))
+    b = R.vloc_psi_k(d, lda, n, 2 * m, psi.reshape(2 * m, lda), inp["vrs"], np.zeros((2 * m, lda), complex))
+    assert np.abs(a.reshape(2 * m, lda) - b).max() < 1e-13
+    c = R.vloc_psi_nc(d, lda, n, m, psi, v4, np.zeros((m, 2 * lda), complex), domag=False)
+    assert np.abs(c - a).max() < 1e-13
+    rng = np.random.default_rng(0)
+    v4 = rng.uniform(-1, 1, (4, d.nnr))
+    hv = R.vloc_psi_nc(d, lda, n, m, psi, v4, np.zeros((m, 2 * lda), complex))
+    live = np.zeros(2 * lda, bool)
+    live[:n] = live[lda:lda + n] = True
+    x01 = np.vdot(psi[0, live], hv[1, live])
+    x10 = np.vdot(psi[1, live], hv[0, live])
+    assert abs(x01 - np.conj(x10)) < 1e-12 * max(1.0, abs(x01))
