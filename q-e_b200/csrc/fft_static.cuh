@@ -126,6 +126,36 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
     }
 }
 
+// Spinor form of the fused middle pass: last DIF pass (A = 1, no twiddles) of BOTH components of a spinor, the 2x2
+// pointwise mix (mix.apply(lane, pos, up, dn)), first DIT pass of both. 2*R complex values live per thread.
+template <class PL, class SrcU, class SrcD, class Mix>
+QEB_HD void spass_spin(int warp, int nwarps, int lane, int nl, double sgn, SrcU& su, SrcD& sd, Mix& mix)
+{
+    constexpr int R = PL::r(PL::NP - 1);
+    constexpr int NJ = PL::N / R;
+    if (lane >= nl) return;
+    for (int j = warp; j < NJ; j += nwarps) {
+        const int base = j * R;
+        cplx u[R], d[R];
+#pragma unroll
+        for (int b = 0; b < R; ++b) {
+            u[b] = su.load(lane, base + b);
+            d[b] = sd.load(lane, base + b);
+        }
+        Bfly<R>::run(u, sgn);
+        Bfly<R>::run(d, sgn);
+#pragma unroll
+        for (int k = 0; k < R; ++k) mix.apply(lane, base + k, u[k], d[k]);
+        Bfly<R>::run(u, -sgn);
+        Bfly<R>::run(d, -sgn);
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            su.store(lane, base + k, u[k]);
+            sd.store(lane, base + k, d[k]);
+        }
+    }
+}
+
 // run pass number `p` (runtime, warp-uniform) of plan PL: expands to a switch over the NP passes
 template <class PL, bool DIT, bool FUSE2, int P = 0, bool PF = false>
 struct SPassSel {

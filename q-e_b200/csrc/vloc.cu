@@ -262,7 +262,18 @@ cudaError_t vloc_launch_batch_nc(const VlocTables& t, const VlocIO& io, const Vl
     if (t.nxw > 0 && t.npos > 0) {
         if (!launch_y(true, t, cfg, nboxes, st))
             k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
-        k_vloc_xspin<<<dim3(t.ntx, nbands), cfg.threads_x, 2 * cfg.smem_x, st>>>(t);
+        // static-plan kernel for the multi-pass plans (a single-pass plan would hold 2*N complex values per thread)
+        bool done = false;
+        if (t.TX <= QEB_TL && !env_int("QEB_GENERIC", 0) && 2 * cfg.smem_x + (size_t)t.nr1 * 20 + 16 <= cfg.max_smem) {
+#define X(PL)                                            \
+    if (!done && PL::NP > 1 && PL::matches(t.px)) {      \
+        FastLaunch<PL>::xspin(t, cfg, nbands, st);       \
+        done = true;                                     \
+    }
+            QEB_FOR_PLANS(X)
+#undef X
+        }
+        if (!done) k_vloc_xspin<<<dim3(t.ntx, nbands), cfg.threads_x, 2 * cfg.smem_x, st>>>(t);
         if (!launch_y(false, t, cfg, nboxes, st))
             k_vloc_yfwd<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;

@@ -187,6 +187,71 @@ QEB_HD void xfus_fast_phase(int ph, int tid, int nthr, const VlocTables& t, int 
 }
 
 // ---------------------------------------------------------------------------
+// P3 fast for spinors (vloc_kernels.cuh::xspin_phase with a compile-time plan): the mix stays in registers between the
+// last DIF and the first DIT butterflies of the two components (fft_static.cuh::spass_spin), so the phase list is the
+// scalar one (2*NP-1) with two tiles.
+// ---------------------------------------------------------------------------
+struct SpinMix {
+    const double* vnc;  // four arrays in the vp layout
+    size_t vs;          // nr1*npos
+    int npos, p0;
+    QEB_HD void apply(int line, int xpos, cplx& u, cplx& d) const
+    {
+        const size_t iv = (size_t)xpos * npos + p0 + line;
+#if defined(__CUDA_ARCH__)
+        const double v1 = __ldg(vnc + iv), v2 = __ldg(vnc + vs + iv), v3 = __ldg(vnc + 2 * vs + iv), v4 = __ldg(vnc + 3 * vs + iv);
+#else
+        const double v1 = vnc[iv], v2 = vnc[vs + iv], v3 = vnc[2 * vs + iv], v4 = vnc[3 * vs + iv];
+#endif
+        const double a = v1 + v4, b = v1 - v4;
+        const cplx nu = mk(u.x * a + (d.x * v2 + d.y * v3), u.y * a + (d.y * v2 - d.x * v3));
+        const cplx nd = mk(d.x * b + (u.x * v2 - u.y * v3), d.y * b + (u.y * v2 + u.x * v3));
+        u = nu;
+        d = nd;
+    }
+};
+
+template <class PL>
+QEB_HD void xspin_fast_phase(int ph, int tid, int nthr, const VlocTables& t, int tile, int pair, cplx* smem,
+                             const FastTabs& ft)
+{
+    constexpr int np = PL::NP;
+    const int TX = t.TX;
+    const int p0 = tile * TX;
+    const int nl = (t.npos - p0) < TX ? (t.npos - p0) : TX;
+    const int warp = tid / QEB_TL, lane = tid % QEB_TL, nwarps = nthr / QEB_TL;
+    const size_t tile_el = (size_t)t.nr1 * TX;
+    LaneTile wu{smem, TX}, wd{smem + tile_el, TX};
+    G2XSrc gu{t.g2 + (size_t)(2 * pair) * t.g2_box, ft.map, t.npos, p0};
+    G2XSrc gd{t.g2 + (size_t)(2 * pair + 1) * t.g2_box, ft.map, t.npos, p0};
+    NoMid nm;
+    if (ph == np - 1) {
+        SpinMix mix{t.vnc, (size_t)t.nr1 * t.npos, t.npos, p0};
+        if (np == 1)
+            spass_spin<PL>(warp, nwarps, lane, nl, +1.0, gu, gd, mix);
+        else
+            spass_spin<PL>(warp, nwarps, lane, nl, +1.0, wu, wd, mix);
+    } else if (ph < np - 1) {
+        if (ph == 0) {
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, gu, wu, nm);
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, gd, wd, nm);
+        } else {
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, wu, wu, nm);
+            SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, nl, ft.tw, +1.0, wd, wd, nm);
+        }
+    } else {
+        const int p = 2 * np - 2 - ph;
+        if (p == 0) {
+            SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, wu, gu, nm);
+            SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, wd, gd, nm);
+        } else {
+            SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, wu, wu, nm);
+            SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, wd, wd, nm);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
 // density accumulation fast: x inverse of one box of the tile + |psi(r)|^2 weights into the lane-mapped accumulator
 // (vloc_kernels.cuh::xacc_phase with a compile-time plan)
 // ---------------------------------------------------------------------------

@@ -98,6 +98,23 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xfus_f(const __gri
     }
 }
 
+// spinor x pass: block = (line tile, band); two tiles
+template <class PL>
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xspin_f(const __grid_constant__ VlocTables t)
+{
+    QEB_SMEM;
+    cplx* twS = smem + 2 * ((size_t)t.nr1 * t.TX);
+    int* tabS = reinterpret_cast<int*>(twS + PL::N);
+    for (int i = threadIdx.x; i < PL::N; i += blockDim.x) twS[i] = t.px.tw[i];
+    for (int i = threadIdx.x; i < PL::N; i += blockDim.x) tabS[i] = t.xmap[i];
+    const FastTabs ft{twS, tabS, nullptr, nullptr};
+    __syncthreads();
+    for (int ph = 0; ph < 2 * PL::NP - 1; ++ph) {
+        xspin_fast_phase<PL>(ph, threadIdx.x, blockDim.x, t, blockIdx.x, blockIdx.y, smem, ft);
+        __syncthreads();
+    }
+}
+
 // density accumulation (sum_band): block = (line tile, box chunk); the CTA x-transforms its boxes of the batch one after
 // the other and accumulates w|psi(r)|^2 in shared memory, then adds the tile to rho (atomically when the batch is
 // split over several chunks)
@@ -165,6 +182,7 @@ struct FastLaunch {
     static void x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st);
     static void xacc(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, const double* w,
                      double* rho, cudaStream_t st);
+    static void xspin(const VlocTables& t, const VlocLaunchCfg& cfg, int nbands, cudaStream_t st);
 };
 
 #ifdef QEB_FAST_INSTANTIATE
@@ -177,6 +195,7 @@ void FastLaunch<PL>::attrs(int s)
     cudaFuncSetAttribute(k_vloc_yfwd_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_xfus_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_xacc_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_xspin_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
 }
 template <class PL>
 void FastLaunch<PL>::z(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
@@ -204,6 +223,16 @@ void FastLaunch<PL>::x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes
     const dim3 grid(t.ntx, nboxes);
     const int nw = env_int("QEB_NWX", pick_warps<PL>(4, 10));
     k_vloc_xfus_f<PL><<<grid, nw * 32, cfg.smem_x + PL::N * 20 + 16, st>>>(t);
+}
+template <class PL>
+void FastLaunch<PL>::xspin(const VlocTables& t, const VlocLaunchCfg& cfg, int nbands, cudaStream_t st)
+{
+    const dim3 grid(t.ntx, nbands);
+    // two tiles: one CTA per SM at the large grids, so the CTA carries all the warps the register file allows
+    // (AUSURF112, 400 spinors: 10 warps 33.5 ms, 16 warps 31.0 ms)
+    const size_t smem = 2 * cfg.smem_x + PL::N * 20 + 16;
+    const int nw = env_int("QEB_NWS", 2 * smem > cfg.max_smem ? QEB_FAST_MAXTHREADS / 32 : pick_warps<PL>(4, 10));
+    k_vloc_xspin_f<PL><<<grid, nw * 32, 2 * cfg.smem_x + PL::N * 20 + 16, st>>>(t);
 }
 template <class PL>
 void FastLaunch<PL>::xacc(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, const double* w,

@@ -340,8 +340,18 @@ extern "C" int emul_vloc_nc(int nr1, int nr2, int nr3, int npw, const int* nl, c
         for (int pair = 0; pair < nbands; ++pair)
             for (int tile = 0; tile < H.ntx; ++tile) {
                 for (auto& x : smem) x = nanv;
-                for (int ph = 0; ph < xspin_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) xspin_phase(ph, tid, nthr, t, tile, pair, smem.data());
+                bool done = false;
+                if (g_fast) {
+#define X(PL) if (!done && PL::matches(t.px)) { \
+                    for (int ph = 0; ph < 2 * PL::NP - 1; ++ph) \
+                        for (int tid = 0; tid < nthr; ++tid) xspin_fast_phase<PL>(ph, tid, nthr, t, tile, pair, smem.data(), FastTabs{t.px.tw, t.xmap, nullptr, nullptr}); \
+                    done = true; }
+                    QEB_FOR_PLANS(X)
+#undef X
+                }
+                if (!done)
+                    for (int ph = 0; ph < xspin_nphase(t); ++ph)
+                        for (int tid = 0; tid < nthr; ++tid) xspin_phase(ph, tid, nthr, t, tile, pair, smem.data());
             }
         for (int box = 0; box < nb; ++box) {
             for (int xa = 0; xa < H.nxw; ++xa)

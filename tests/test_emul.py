@@ -194,16 +194,15 @@ def test_sum_band_density_phases(emul, name, fast):
         emul.emul_set_fast(0)
 
 
-@pytest.mark.parametrize("name", ["si2_small", "si2", "ortho_small"])
-@pytest.mark.parametrize("fast", [0, 1])
-def test_vloc_nc_phases(emul, name, fast):
+@pytest.mark.parametrize("name,fast,m", [("si2_small", 0, 3), ("si2", 0, 3), ("ortho_small", 0, 3), ("si2_small", 1, 3),
+                                         ("si2", 1, 3), ("ortho_small", 1, 3), ("ausurf112", 1, 1)])
+def test_vloc_nc_phases(emul, name, fast, m):
     """the spinor x pass (vloc_kernels.cuh xspin_phase: x DIF | 2x2 mix | x DIT on both components) inside the pass
     pipeline, on the CPU, against the oracle restatement of vloc_psi_nc (PW/src/vloc_psi_acc.f90:269-369, domag)"""
     emul.emul_vloc_nc.argtypes = [ctypes.c_int] * 4 + [ctypes.c_void_p] * 2 + [ctypes.c_int] * 3 + [ctypes.c_void_p] * 3 + [ctypes.c_int] * 2
     emul.emul_set_fast(fast)
     try:
         d = D.config_descriptor(name)
-        m = 3
         inp = R.synthetic_inputs(d, 2 * m, [4, 4], seed=5)
         lda, n = inp["lda"], inp["n"]
         rng = np.random.default_rng(11)
@@ -215,7 +214,7 @@ def test_vloc_nc_phases(emul, name, fast):
         nl_ = np.ascontiguousarray(d.nl, dtype=np.int32)
         igk = np.ascontiguousarray(d.igk, dtype=np.int32)
         rc = emul.emul_vloc_nc(d.nr1, d.nr2, d.nr3, n, p(nl_), p(igk), d.ngm, lda, m, p(psi), p(v4), p(out),
-                               96 if fast else 37, 2)
+                               (160 if d.nr1 > 30 else 96) if fast else 37, 2)
         assert rc == 0
         for b in range(m):
             for ipol in range(2):

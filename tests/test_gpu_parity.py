@@ -147,6 +147,32 @@ def test_vloc_psi_nc(mods, name, m):
     h2.close()
 
 
+@pytest.mark.parametrize("generic", [0, 1])
+def test_vloc_psi_nc_full_grid_ausurf(mods, generic, monkeypatch):
+    """the spinor x pass at the AUSURF112 grid (125 = 25*5: the in-register mix between the last DIF and the first DIT
+    butterflies of both components, k_vloc_xspin_f) and the runtime-plan kernel (QEB_GENERIC=1) against the oracle"""
+    qe, D, R, torch = mods
+    if generic:
+        monkeypatch.setenv("QEB_GENERIC", "1")
+    d = D.config_descriptor("ausurf112")
+    m = 2
+    inp = R.synthetic_inputs(d, 2 * m, [4], seed=4, lda=d.npw + 3)
+    lda, n = inp["lda"], inp["n"]
+    rng = np.random.default_rng(23)
+    v4 = np.ascontiguousarray(rng.uniform(-1.0, 1.0, (4, d.nnr)))
+    psi = np.ascontiguousarray(inp["psi"]).reshape(m, 2 * lda)
+    h0 = np.zeros((m, 2 * lda), complex)
+    ref = R.vloc_psi_nc(d, lda, n, m, psi, v4, h0.copy())
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    out = h0.copy()
+    h.vloc_psi_nc(lda, n, m, psi, v4, out)
+    live = np.zeros(2 * lda, bool)
+    live[:n] = live[lda:lda + n] = True
+    assert relerr(out[:, live], ref[:, live]) < TOL
+    h.close()
+
+
 @pytest.mark.parametrize("name", SMALL + ["si2", "al4"])
 @pytest.mark.parametrize("m", [1, 3, 4, 10])
 def test_h_psi(mods, name, m):

@@ -100,4 +100,11 @@ e = torch.linspace(-1, 1, m, device=dev, dtype=torch.float64)
 h.set_g_psi_diag(np.ascontiguousarray(d.g2kin + 1.0), np.ones(n))
 ms = timed(lambda: h.g_psi(lda, n, m, 1, spsi, e))
 out(item="g_psi preconditioner", ms=ms, gbs=32e-9 * n * m / (ms * 1e-3))
+# noncollinear V_loc with the 2x2 potential: the 800 columns as 400 spinors; the scalar path on the same columns beside it
+v4 = torch.randn((4, d.nnr), generator=g, device=dev, dtype=torch.float64)
+h.set_vloc_nc(v4)
+ms = timed(lambda: h.vloc_psi_nc(lda, n, m // 2, psi, None, hpsi))
+ms_k = timed(lambda: h.vloc_psi_k(lda, n, m, psi, None, hpsi))
+out(item="vloc_psi_nc (400 spinors = 800 component FFT pairs, spinor x pass)", ms=ms, us_per_component=1e3 * ms / m,
+    scalar_vloc_psi_k_same_columns_ms=ms_k)
 h.close()
