@@ -69,6 +69,15 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_get_becp(ctx, becp, m) BIND(C, name='qeb_get_becp')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, becp; INTEGER(C_INT), VALUE :: m
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_vloc_nc(ctx, v4) BIND(C, name='qeb_set_vloc_nc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, v4
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_nonlocal_nc(ctx, deeq_nc) BIND(C, name='qeb_set_nonlocal_nc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, deeq_nc
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_h_psi_nc(ctx, lda, n, m, psi, hpsi) BIND(C, name='qeb_h_psi_nc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
     INTEGER(C_INT) FUNCTION qeb_set_qq(ctx, nat, nhm, qq_at) BIND(C, name='qeb_set_qq')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, qq_at; INTEGER(C_INT), VALUE :: nat, nhm
     END FUNCTION
@@ -133,6 +142,8 @@ MODULE qeb200_state
   INTEGER :: deeq_loaded = -2
   INTEGER :: spin_loaded = -1
   LOGICAL :: qq_loaded = .FALSE.   ! qq_at is filled once per run (upflib/init_us_1.f90)
+  INTEGER :: vnc_loaded = -2       ! vloc_version the context's 2x2 potential belongs to
+  INTEGER :: dnc_loaded = -2       ! deeq_version the context's deeq_nc belongs to
 CONTAINS
   SUBROUTINE qeb200_check(rc, routine)
     INTEGER(C_INT), INTENT(IN) :: rc
@@ -206,6 +217,30 @@ CONTAINS
     END IF
     spin_loaded = current_spin
   END SUBROUTINE
+  SUBROUTINE qeb200_sync_state_nc()
+    !! Magnetic / spin-orbit spinors: the 2x2 potential vrs(:,1:4) (only vrs(:,1) without domag, vloc_psi_acc.f90:329-348)
+    !! and deeq_nc (newd_nc / newd_so, PW/src/newd.f90) on top of qeb200_sync_state.
+    USE kinds,            ONLY: DP
+    USE fft_base,         ONLY: dffts
+    USE scf,              ONLY: vrs
+    USE uspp,             ONLY: nkb, deeq_nc
+    USE noncollin_module, ONLY: domag
+    REAL(DP), ALLOCATABLE, TARGET :: v4(:, :)
+    CALL qeb200_sync_state()
+    IF (vnc_loaded /= vloc_version) THEN
+      ALLOCATE (v4(dffts%nnr, 4))
+      v4 = 0.0_DP
+      v4(:, 1) = vrs(1:dffts%nnr, 1)
+      IF (domag) v4(:, 2:4) = vrs(1:dffts%nnr, 2:4)
+      CALL qeb200_check(qeb_set_vloc_nc(ctx, C_LOC(v4)), 'qeb_set_vloc_nc')
+      DEALLOCATE (v4)
+      vnc_loaded = vloc_version
+    END IF
+    IF (nkb > 0 .AND. dnc_loaded /= deeq_version) THEN
+      CALL qeb200_check(qeb_set_nonlocal_nc(ctx, C_LOC(deeq_nc)), 'qeb_set_nonlocal_nc')
+      dnc_loaded = deeq_version
+    END IF
+  END SUBROUTINE
   SUBROUTINE qeb200_sync_uspp(structure_changed)
     !! Pushes the run-constant inputs of init_us_2 / g2_kin (G-vector list, beta interpolation tables: once) and the
     !! structure-factor phases (after every struc_fact, PW/src/hinit0.f90 / hinit1.f90).
@@ -259,11 +294,19 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
   INTEGER, ALLOCATABLE :: recv_counts(:), displs(:)
   !
   IF (real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. exx_is_active() .OR. &
-      xclib_dft_is('meta') .OR. dffts%lpara .OR. (noncolin .AND. (domag .OR. lspinorb))) THEN
+      xclib_dft_is('meta') .OR. dffts%lpara) THEN
     CALL h_psi(lda, n, m, psi, hpsi)      ! original Fortran path
     RETURN
   END IF
   CALL start_clock('h_psi')
+  IF (noncolin .AND. (domag .OR. lspinorb)) THEN
+    ! magnetic / spin-orbit spinors: 2x2 potential and spin-dependent deeq_nc (h_psi.f90:184-190,225-229)
+    CALL qeb200_sync_state_nc()
+    CALL qeb200_check(qeb_h_psi_nc(ctx, lda, n, m, C_LOC(psi), C_LOC(hpsi)), 'h_psi')
+    IF (nkb > 0) CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%nc), npol*m), 'h_psi')
+    CALL stop_clock('h_psi')
+    RETURN
+  END IF
   CALL qeb200_sync_state()
   IF (noncolin) THEN
     ! Non-magnetic spinors without spin-orbit: both components see the same g2kin, the same scalar V(r)

@@ -98,6 +98,15 @@ int qeb_vloc_psi_gamma(qeb_ctx* ctx, int lda, int n, int m, const void* psi, con
  * v(:,1) on both components) is qeb_vloc_psi_k on 2m columns of leading dimension lda. */
 int qeb_set_vloc_nc(qeb_ctx* ctx, const double* v4);
 int qeb_vloc_psi_nc(qeb_ctx* ctx, int lda, int n, int m, const void* psi, const double* v4, void* hpsi);
+/* h_psi for noncollinear spinors with magnetisation / spin-orbit: PW/src/h_psi.f90:138-148 (kinetic term on both
+ * components), :184-190 (vloc_psi_nc), :225-229 -> calbec_nc (Modules/becmod.f90:575-616: one ZGEMM over m*npol
+ * columns) and add_vuspsi_nc (PW/src/add_vuspsi.f90:174-234).   
+ * qeb_set_nonlocal_nc: deeq_nc(nhm,nhm,nat,4) COMPLEX(DP) (host or device); nat, nhm, nh, ofsbeta are those of a
+ * preceding qeb_set_nonlocal (whose real deeq is not used by this path).
+ * qeb_h_psi_nc: psi(lda*2,m) -> hpsi(lda*2,m); rows n+1..lda of both components zeroed; leaves becp%nc(nkb,2,m) in
+ * the context (qeb_get_becp with 2*m columns). Needs qeb_set_vloc_nc. Serial k-point descriptor only. */
+int qeb_set_nonlocal_nc(qeb_ctx* ctx, const void* deeq_nc);
+int qeb_h_psi_nc(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* hpsi);
 
 /* invfft / fwfft (kind, f, dfft, howmany)  FFTXlib/src/fft_interfaces.f90:19-80,
  * fft_fwinv.f90:10-216: in-place 3-D transform of howmany boxes f(nnr*howmany).

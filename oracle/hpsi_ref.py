@@ -131,6 +131,53 @@ def vloc_psi_nc(d: Descriptor, lda: int, n: int, m: int, psi: np.ndarray, v: np.
     return hpsi
 
 
+def apply_deeq_nc(becp_nc: np.ndarray, deeq_nc: np.ndarray, nh_at: np.ndarray, ofsbeta: np.ndarray) -> np.ndarray:
+    """ps of add_vuspsi_nc, PW/src/add_vuspsi.f90:192-223. becp_nc (m, 2, nkb) = Fortran becp%nc(nkb,npol,m) memory;
+    deeq_nc (4, nat, nhm, nhm) complex = Fortran deeq_nc(nhm,nhm,nat,4) memory, i.e. deeq_nc[is, na, jh, ih]."""
+    ps = np.zeros_like(becp_nc)
+    for na, (nh, o) in enumerate(zip(nh_at, ofsbeta)):
+        D = [deeq_nc[k, na, :nh, :nh].T for k in range(4)]  # D[k][ih, jh]
+        b1, b2 = becp_nc[:, 0, o:o + nh], becp_nc[:, 1, o:o + nh]
+        ps[:, 0, o:o + nh] += b1 @ D[0].T + b2 @ D[1].T
+        ps[:, 1, o:o + nh] += b1 @ D[2].T + b2 @ D[3].T
+    return ps
+
+
+def h_psi_nc(d: Descriptor, lda, n, m, psi, v4, vkb, deeq_nc, nh_at, ofsbeta):
+    """Noncollinear h_psi_ with magnetisation (PW/src/h_psi.f90:138-148 kinetic on both components, :184-190
+    vloc_psi_nc, :225-229 calbec + add_vuspsi -> calbec_nc becmod.f90:575-616, add_vuspsi_nc add_vuspsi.f90:174-234).
+    psi (m, 2*lda); returns (hpsi (m, 2*lda), becp_nc (m, 2, nkb))."""
+    hpsi = np.zeros((m, 2 * lda), dtype=np.complex128)
+    for ipol in range(2):
+        hpsi[:, ipol * lda:ipol * lda + n] = d.g2kin[None, :n] * psi[:, ipol * lda:ipol * lda + n]
+    vloc_psi_nc(d, lda, n, m, psi, v4, hpsi)
+    nkb = 0 if vkb is None else vkb.shape[0]
+    becp = np.zeros((m, 2, nkb), dtype=np.complex128)
+    if nkb:
+        for ipol in range(2):
+            becp[:, ipol, :] = psi[:, ipol * lda:ipol * lda + n] @ np.conj(vkb[:, :n]).T
+        ps = apply_deeq_nc(becp, deeq_nc, nh_at, ofsbeta)
+        for ipol in range(2):
+            hpsi[:, ipol * lda:ipol * lda + n] += ps[:, ipol, :] @ vkb[:, :n]
+    return hpsi, becp
+
+
+def synthetic_deeq_nc(nh_at, seed: int = 0):
+    """Hermitian 2x2-spin D matrices in the deeq_nc(nhm,nhm,nat,4) layout (as newd_nc / spin-orbit produce them:
+    D^{ss'}_{ij} = conj(D^{s's}_{ji})); returned as (4, nat, nhm, nhm) complex."""
+    rng = np.random.default_rng(4411 + seed)
+    nat, nhm = len(nh_at), int(max(nh_at))
+    out = np.zeros((4, nat, nhm, nhm), dtype=np.complex128)
+    for na, nh in enumerate(nh_at):
+        big = rng.standard_normal((2 * nh, 2 * nh)) + 1j * rng.standard_normal((2 * nh, 2 * nh))
+        big = 0.5 * (big + big.conj().T)  # big[(s,ih),(s',jh)]
+        for s in range(2):
+            for sp in range(2):
+                blk = big[s * nh:(s + 1) * nh, sp * nh:(sp + 1) * nh]  # [ih, jh]
+                out[2 * s + sp, na, :nh, :nh] = blk.T  # memory [jh, ih]
+    return out
+
+
 def sum_band_rho(d: Descriptor, lda: int, n: int, m: int, evc: np.ndarray, w: np.ndarray, rho: np.ndarray):
     """Density part of sum_band: rho (nnr, INOUT) += sum_b w[b] |psi_b(r)|^2, w[b] = wg(b,ik)/omega.
     k: wave_g2r + get_rho_k per band (PW/src/sum_band.f90:578-593, :650-671); Gamma: two bands per transform,

@@ -114,6 +114,8 @@ struct qeb_ctx {
     DevBuf v_d, vp_d, vpl_d;
     DevBuf vnc_d;  // noncollinear 2x2 potential, four arrays in the vp layout
     bool have_vnc = false;
+    DevBuf dnc_d;  // deeq_nc(nhm,nhm,nat,4) complex
+    bool have_dnc = false;
     DevBuf revx_d;
     // full-box FFT plans
     DevBuf full_plan_d;
@@ -1524,6 +1526,29 @@ static int vloc_entry(qeb_ctx* c, int lda, int n, int m, const void* psi, const 
     return finish(c);
 }
 
+// m spinors = 2m component columns of leading dimension lda through the 2x2 potential; kinetic: hpsi = g2kin*psi + ...
+static int run_vloc_nc(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool kinetic)
+{
+    if (!c->have_vnc) QEB_FAIL(c, 50, "vloc_psi_nc: no 2x2 potential set (qeb_set_vloc_nc)");
+    if (2 * c->cfg.smem_x > c->max_smem) QEB_FAIL(c, 64, "vloc_psi_nc: x tile of this grid does not fit twice in shared memory");
+    if (kinetic && !c->have_g2kin) QEB_FAIL(c, 55, "h_psi_nc: no g2kin in the context (qeb_set_kpoint or qeb_g2_kin)");
+    VlocIO io;
+    io.psi = psi_d;
+    io.hpsi = hpsi_d;
+    io.g2kin = kinetic ? (const double*)c->g2kin_d.p : nullptr;
+    io.lda = lda;
+    io.n = n;
+    io.nbands = 2 * m;
+    io.gamma = 0;
+    const int bands_per_batch = std::max(1, c->batch / 2);
+    for (int b0 = 0; b0 < m; b0 += bands_per_batch) {
+        const int nb = std::min(bands_per_batch, m - b0);
+        io.band0 = 2 * b0;
+        QEB_CUDA(c, vloc_launch_batch_nc(c->T, io, c->cfg, nb, c->stream));
+    }
+    return 0;
+}
+
 // vloc_psi_nc with domag (PW/src/vloc_psi_acc.f90:269-369): psi(lda*2, m), hpsi(lda, 2, m) INOUT. The two components of a
 // band are columns 2b, 2b+1 of leading dimension lda, i.e. boxes 2b, 2b+1 of the batch.
 int qeb_vloc_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v4, void* hpsi)
@@ -1535,30 +1560,75 @@ int qeb_vloc_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, const do
     if (c->dist || c->gamma) QEB_FAIL(c, 63, "qeb_vloc_psi_nc: serial k-point descriptor only");
     if (m == 0) return 0;
     if (v4 && (rc = prepare_v_nc(c, v4))) return rc;
-    if (!c->have_vnc) QEB_FAIL(c, 50, "qeb_vloc_psi_nc: no 2x2 potential set (qeb_set_vloc_nc)");
-    if (2 * c->cfg.smem_x > c->max_smem) QEB_FAIL(c, 64, "qeb_vloc_psi_nc: x tile of this grid does not fit twice in shared memory");
     const size_t bytes = (size_t)lda * 2 * m * 16;
     const void* psi_d;
     if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
     const bool out_dev = is_device_ptr(hpsi);
     const void* hin;
     if ((rc = stage_in(c, hpsi, bytes, c->hpsi_stage, &hin))) return rc;  // INOUT
-    VlocIO io;
-    io.psi = (const cplx*)psi_d;
-    io.hpsi = (cplx*)hin;
-    io.g2kin = nullptr;
-    io.lda = lda;
-    io.n = n;
-    io.nbands = 2 * m;
-    io.gamma = 0;
-    const int bands_per_batch = std::max(1, c->batch / 2);
-    for (int b0 = 0; b0 < m; b0 += bands_per_batch) {
-        const int nb = std::min(bands_per_batch, m - b0);
-        io.band0 = 2 * b0;
-        QEB_CUDA(c, vloc_launch_batch_nc(c->T, io, c->cfg, nb, c->stream));
-    }
+    if ((rc = run_vloc_nc(c, lda, n, m, (const cplx*)psi_d, (cplx*)hin, false))) return rc;
     if (!out_dev) {
         QEB_CUDA(c, cudaMemcpyAsync(hpsi, hin, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+// deeq_nc(nhm,nhm,nat,4) complex of add_vuspsi_nc (PW/src/add_vuspsi.f90:174-234); nat/nhm as in qeb_set_nonlocal
+int qeb_set_nonlocal_nc(qeb_ctx* c, const void* deeq_nc)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_nl) QEB_FAIL(c, 51, "qeb_set_nonlocal_nc: qeb_set_nonlocal has not been called (nat, nhm, nh, ofsbeta)");
+    if (!deeq_nc) QEB_FAIL(c, 40, "qeb_set_nonlocal_nc: null deeq_nc");
+    const size_t nd = (size_t)c->nhm * c->nhm * c->nat * 4;
+    QEB_CUDA(c, c->dnc_d.ensure(nd * 16 + 16));
+    if (nd)
+        QEB_CUDA(c, cudaMemcpyAsync(c->dnc_d.p, deeq_nc, nd * 16,
+                                    is_device_ptr(deeq_nc) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_dnc = true;
+    return 0;
+}
+
+// h_psi_ for noncollinear spinors with magnetisation / spin-orbit (PW/src/h_psi.f90:138-148,184-190,225-229):
+// kinetic term on both components, vloc_psi_nc, calbec_nc (= calbec on 2m columns, becmod.f90:575-616), add_vuspsi_nc.
+// psi(lda*2,m) -> hpsi(lda*2,m); leaves becp%nc(nkb,2,m) in the context (qeb_get_becp with 2m columns).
+int qeb_h_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_h_psi_nc");
+    if (rc) return rc;
+    if (c->dist || c->gamma) QEB_FAIL(c, 63, "qeb_h_psi_nc: serial k-point descriptor only");
+    if (m == 0) return 0;
+    const int nkb = c->nkb;
+    if (nkb > 0 && !c->vkb_d) QEB_FAIL(c, 56, "qeb_h_psi_nc: no vkb in the context (qeb_set_kpoint or qeb_init_us_2)");
+    if (nkb > 0 && !c->have_dnc) QEB_FAIL(c, 51, "qeb_h_psi_nc: no deeq_nc in the context (qeb_set_nonlocal_nc)");
+    if (nkb > c->nl_rows) QEB_FAIL(c, 52, "qeb_h_psi_nc: vkb has projectors not covered by ofsbeta/nh of qeb_set_nonlocal");
+    const size_t bytes = (size_t)lda * 2 * m * 16;
+    const bool out_dev = is_device_ptr(hpsi);
+    const void* psi_d;
+    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
+    cplx* hpsi_d = (cplx*)hpsi;
+    if (!out_dev) {
+        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
+        hpsi_d = (cplx*)c->hpsi_stage.p;
+    }
+    if (lda > n) QEB_CUDA(c, cudaMemset2DAsync(hpsi_d + n, (size_t)lda * 16, 0, (size_t)(lda - n) * 16, 2 * m, c->stream));
+    if ((rc = run_vloc_nc(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true))) return rc;
+    if (nkb > 0) {
+        if ((rc = ensure_becp(c, nkb, 2 * m))) return rc;
+        if ((rc = run_calbec(c, c->vkb_d, c->npwx, nkb, (const cplx*)psi_d, lda, n, 2 * m, c->becp_d.p))) return rc;
+        c->becp_m = 2 * m;
+        const int ldps = (nkb + 1) & ~1;
+        QEB_CUDA(c, launch_apply_deeq_nc(c->becp_d.p, nkb, m, c->row_atom_d, c->ofs_d, c->nh_d, c->dnc_d.p, c->nhm, c->nat,
+                                         c->ps_d.p, ldps, c->stream));
+        QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, c->ps_d.p, ldps, n, nkb, 2 * m, true, hpsi_d, lda, c->stream));
+    }
+    if (!out_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hpsi_d, bytes, cudaMemcpyDeviceToHost, c->stream));
         QEB_CUDA(c, cudaStreamSynchronize(c->stream));
         return 0;
     }

@@ -390,6 +390,38 @@ __global__ void k_apply_deeq(const void* __restrict__ becp, int nkb, int m, cons
     }
 }
 
+// noncollinear: ps(ofs+ih, ipol, b) = sum_jh deeq_nc(ih,jh,na,1+2 ipol) becp(ofs+jh,1,b) + deeq_nc(ih,jh,na,2+2 ipol) becp(ofs+jh,2,b)
+// (add_vuspsi.f90:192-223). becp / ps columns: 2b = up, 2b+1 = down. deeq_nc complex, Fortran (nhm,nhm,nat,4).
+__global__ void k_apply_deeq_nc(const cplx* __restrict__ becp, int nkb, int m, const int* __restrict__ row_atom,
+                                const int* __restrict__ ofs, const int* __restrict__ nh, const cplx* __restrict__ dnc,
+                                int nhm, int nat, cplx* __restrict__ ps, int ldps)
+{
+    const size_t tot = (size_t)nkb * 2 * m;
+    const size_t dspin = (size_t)nhm * nhm * nat;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < tot; e += (size_t)gridDim.x * blockDim.x) {
+        const int col = (int)(e / nkb), i = (int)(e - (size_t)col * nkb);
+        const int b = col >> 1, ipol = col & 1;
+        const int na = row_atom[i];
+        if (na < 0) {
+            ps[(size_t)col * ldps + i] = mk(0.0, 0.0);
+            continue;
+        }
+        const int o = ofs[na], ih = i - o, nn = nh[na];
+        const cplx* D1 = dnc + (size_t)(2 * ipol) * dspin + (size_t)na * nhm * nhm + ih;
+        const cplx* D2 = D1 + dspin;
+        const cplx* B1 = becp + (size_t)(2 * b) * nkb + o;
+        const cplx* B2 = B1 + nkb;
+        double sx = 0.0, sy = 0.0;
+        for (int jh = 0; jh < nn; ++jh) {
+            const cplx d1 = D1[(size_t)jh * nhm], d2 = D2[(size_t)jh * nhm];
+            const cplx b1 = B1[jh], b2 = B2[jh];
+            sx += d1.x * b1.x - d1.y * b1.y + d2.x * b2.x - d2.y * b2.y;
+            sy += d1.x * b1.y + d1.y * b1.x + d2.x * b2.y + d2.y * b2.x;
+        }
+        ps[(size_t)col * ldps + i] = mk(sx, sy);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // add_vuspsi: hpsi(g,j) += sum_i vkb(g,i) ps(i,j)
 // ---------------------------------------------------------------------------
@@ -753,6 +785,18 @@ cudaError_t launch_apply_deeq(const void* becp, int nkb, int m, bool cplx_mode, 
         k_apply_deeq<true><<<blocks, 256, 0, st>>>(becp, nkb, m, row_atom, ofs, nh, deeq, nhm, ps, ldps);
     else
         k_apply_deeq<false><<<blocks, 256, 0, st>>>(becp, nkb, m, row_atom, ofs, nh, deeq, nhm, ps, ldps);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_apply_deeq_nc(const void* becp, int nkb, int m, const int* row_atom, const int* ofs, const int* nh,
+                                 const void* deeq_nc, int nhm, int nat, void* ps, int ldps, cudaStream_t st)
+{
+    const size_t tot = (size_t)nkb * 2 * m;
+    if (tot == 0) return cudaSuccess;
+    int blocks = (int)((tot + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_apply_deeq_nc<<<blocks, 256, 0, st>>>((const cplx*)becp, nkb, m, row_atom, ofs, nh, (const cplx*)deeq_nc, nhm, nat,
+                                            (cplx*)ps, ldps);
     return cudaGetLastError();
 }
 

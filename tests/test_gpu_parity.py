@@ -147,6 +147,48 @@ def test_vloc_psi_nc(mods, name, m):
     h2.close()
 
 
+@pytest.mark.parametrize("name", ["si2_small", "ortho_small", "si2", "al4"])
+@pytest.mark.parametrize("m", [1, 3, 6])
+def test_h_psi_nc(mods, name, m):
+    """noncollinear h_psi with magnetisation (kinetic on both components, vloc_psi_nc, calbec_nc, add_vuspsi_nc with a
+    Hermitian spin-dependent deeq_nc) against the oracle restatement; becp%nc left in the context"""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    c = d.extra["config"]
+    nh = c.get("nh_list") or [c["nh"]] * c["nat"]
+    inp = R.synthetic_inputs(d, 2 * m, nh, seed=6)
+    lda, n = inp["lda"], inp["n"]
+    rng = np.random.default_rng(29)
+    v4 = np.ascontiguousarray(rng.uniform(-1.0, 1.0, (4, d.nnr)))
+    dnc = R.synthetic_deeq_nc(inp["nh_at"], seed=m)
+    psi = np.ascontiguousarray(inp["psi"]).reshape(m, 2 * lda)
+    ref, becp_ref = R.h_psi_nc(d, lda, n, m, np.nan_to_num(psi), v4, np.nan_to_num(inp["vkb"]), dnc, inp["nh_at"],
+                               inp["ofsbeta"])
+    h = qe.HPsi(batch=4)
+    h.setup_from(d, inp)
+    h.set_vloc_nc(v4)
+    h.set_nonlocal_nc(dnc)
+    out = np.full((m, 2 * lda), np.nan + 1j * np.nan)
+    h.h_psi_nc(lda, n, m, psi, out)
+    assert relerr(out, ref) < TOL  # includes the zeroed rows n+1..lda of both components
+    becp = h.get_becp(2 * m).reshape(m, 2, -1)
+    assert relerr(becp, becp_ref) < TOL
+    # device pointers
+    psi_t = torch.from_numpy(np.nan_to_num(psi)).cuda()
+    out_t = torch.full((m, 2 * lda, 2), float("nan"), dtype=torch.float64, device="cuda")
+    h.h_psi_nc(lda, n, m, psi_t, out_t)
+    torch.cuda.synchronize()
+    assert relerr(torch.view_as_complex(out_t).cpu().numpy(), ref) < TOL
+    # Hermitian spinor operator: <a|H b> = conj(<b|H a>)
+    if m >= 2:
+        live = np.zeros(2 * lda, bool)
+        live[:n] = live[lda:lda + n] = True
+        P = np.nan_to_num(psi)[:, live]
+        A = P.conj() @ out[:, live].T
+        assert np.abs(A - A.conj().T).max() / np.abs(A).max() < 1e-11
+    h.close()
+
+
 @pytest.mark.parametrize("generic", [0, 1])
 def test_vloc_psi_nc_full_grid_ausurf(mods, generic, monkeypatch):
     """the spinor x pass at the AUSURF112 grid (125 = 25*5: the in-register mix between the last DIF and the first DIT

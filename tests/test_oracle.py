@@ -274,3 +274,25 @@ def test_vloc_psi_nc_reduces_to_scalar_and_is_hermitian():
     x01 = np.vdot(psi[0, live], hv[1, live])
     x10 = np.vdot(psi[1, live], hv[0, live])
     assert abs(x01 - np.conj(x10)) < 1e-12 * max(1.0, abs(x01))
+
+
+def test_h_psi_nc_block_diagonal_limit():
+    """h_psi_nc with v2=v3=v4=0 and deeq_nc(:,:,:,1)=deeq_nc(:,:,:,4)=deeq, (:,:,:,2:3)=0 (what newd sets without
+    magnetisation) is the scalar h_psi on 2m columns (h_psi.f90:138-148; add_vuspsi.f90:192-223 vs :151-155)."""
+    d = D.config_descriptor("ortho_small")
+    c = d.extra["config"]
+    nh = [c["nh"]] * c["nat"]
+    m = 2
+    inp = R.synthetic_inputs(d, 2 * m, nh, seed=8, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    psi = np.ascontiguousarray(inp["psi"]).reshape(m, 2 * lda)
+    v4 = np.zeros((4, d.nnr))
+    v4[0] = inp["vrs"]
+    nat, nhm = len(nh), max(nh)
+    dnc = np.zeros((4, nat, nhm, nhm), complex)
+    dnc[0] = dnc[3] = inp["deeq"]
+    a, ba = R.h_psi_nc(d, lda, n, m, psi, v4, inp["vkb"], dnc, inp["nh_at"], inp["ofsbeta"])
+    b, bb = R.h_psi(d, lda, n, 2 * m, psi.reshape(2 * m, lda), inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"],
+                    inp["ofsbeta"])
+    assert np.abs(a.reshape(2 * m, lda) - b).max() / np.abs(b).max() < 1e-13
+    assert np.abs(ba.reshape(2 * m, -1) - bb).max() < 1e-13
