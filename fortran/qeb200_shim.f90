@@ -78,6 +78,12 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_h_psi_nc(ctx, lda, n, m, psi, hpsi) BIND(C, name='qeb_h_psi_nc')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, hpsi; INTEGER(C_INT), VALUE :: lda, n, m
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_qq_nc(ctx, qq_nc) BIND(C, name='qeb_set_qq_nc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, qq_nc
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_s_psi_nc(ctx, lda, n, m, psi, spsi) BIND(C, name='qeb_s_psi_nc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, spsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
     INTEGER(C_INT) FUNCTION qeb_set_qq(ctx, nat, nhm, qq_at) BIND(C, name='qeb_set_qq')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, qq_at; INTEGER(C_INT), VALUE :: nat, nhm
     END FUNCTION
@@ -144,6 +150,7 @@ MODULE qeb200_state
   LOGICAL :: qq_loaded = .FALSE.   ! qq_at is filled once per run (upflib/init_us_1.f90)
   INTEGER :: vnc_loaded = -2       ! vloc_version the context's 2x2 potential belongs to
   INTEGER :: dnc_loaded = -2       ! deeq_version the context's deeq_nc belongs to
+  LOGICAL :: qnc_loaded = .FALSE.  ! qq_so / qq_at are filled once per run
 CONTAINS
   SUBROUTINE qeb200_check(rc, routine)
     INTEGER(C_INT), INTENT(IN) :: rc
@@ -240,6 +247,33 @@ CONTAINS
       CALL qeb200_check(qeb_set_nonlocal_nc(ctx, C_LOC(deeq_nc)), 'qeb_set_nonlocal_nc')
       dnc_loaded = deeq_version
     END IF
+  END SUBROUTINE
+  SUBROUTINE qeb200_sync_qq_nc()
+    !! per-atom 2x2-spin overlap of s_psi_nc (PW/src/s_psi.f90:326-360): qq_so(:,:,1:4,nt) with spin-orbit, else qq_at
+    !! on the spin diagonal; only ultrasoft types contribute (:328)
+    USE kinds,            ONLY: DP
+    USE uspp,             ONLY: qq_at, qq_so, okvan
+    USE uspp_param,       ONLY: nhm, upf
+    USE ions_base,        ONLY: nat, ityp
+    USE noncollin_module, ONLY: lspinorb
+    COMPLEX(DP), ALLOCATABLE, TARGET :: qq_nc(:, :, :, :)
+    INTEGER :: na, nt
+    IF (qnc_loaded .OR. .NOT. okvan) RETURN
+    ALLOCATE (qq_nc(nhm, nhm, nat, 4))
+    qq_nc = (0.0_DP, 0.0_DP)
+    DO na = 1, nat
+      nt = ityp(na)
+      IF (.NOT. upf(nt)%tvanp) CYCLE
+      IF (lspinorb) THEN
+        qq_nc(:, :, na, 1:4) = qq_so(:, :, 1:4, nt)
+      ELSE
+        qq_nc(:, :, na, 1) = qq_at(:, :, na)
+        qq_nc(:, :, na, 4) = qq_at(:, :, na)
+      END IF
+    END DO
+    CALL qeb200_check(qeb_set_qq_nc(ctx, C_LOC(qq_nc)), 'qeb_set_qq_nc')
+    DEALLOCATE (qq_nc)
+    qnc_loaded = .TRUE.
   END SUBROUTINE
   SUBROUTINE qeb200_sync_uspp(structure_changed)
     !! Pushes the run-constant inputs of init_us_2 / g2_kin (G-vector list, beta interpolation tables: once) and the
@@ -456,23 +490,30 @@ SUBROUTINE s_psi_qeb(lda, n, m, psi, spsi)
   !! s_psi(lda,n,m,psi,spsi) (PW/src/s_psi.f90:10-76): same EXTERNAL signature cegterg/regterg receive as
   !! s_psi_ptr (KS_Solvers/Davidson/cegterg.f90:110-118,196,467). Uses the projections of these m bands that the
   !! h_psi_qeb call just before left in the context (s_psi.f90:15), so becmod::becp is not re-uploaded.
-  !! Branches outside the library (real_space, noncolin) go to the reference routine.
+  !! Spinors (s_psi_nc, :308-370): magnetic / spin-orbit runs use the becp%nc of qeb_h_psi_nc and the 2x2 overlap;
+  !! non-magnetic spinors are 2*m scalar columns, as in h_psi_qeb. real_space goes to the reference routine.
   USE, INTRINSIC :: ISO_C_BINDING
   USE kinds,            ONLY: DP
-  USE noncollin_module, ONLY: noncolin
+  USE noncollin_module, ONLY: noncolin, npol, domag, lspinorb
   USE realus,           ONLY: real_space
   USE qeb200_c
   USE qeb200_state
   IMPLICIT NONE
   INTEGER, INTENT(IN) :: lda, n, m
-  COMPLEX(DP), INTENT(IN),  TARGET :: psi(lda, m)
-  COMPLEX(DP), INTENT(OUT), TARGET :: spsi(lda, m)
-  IF (noncolin .OR. real_space) THEN
+  COMPLEX(DP), INTENT(IN),  TARGET :: psi(lda*npol, m)
+  COMPLEX(DP), INTENT(OUT), TARGET :: spsi(lda*npol, m)
+  IF (real_space) THEN
     CALL s_psi(lda, n, m, psi, spsi)
     RETURN
   END IF
+  IF (noncolin .AND. (domag .OR. lspinorb)) THEN
+    CALL qeb200_sync_state_nc()
+    CALL qeb200_sync_qq_nc()
+    CALL qeb200_check(qeb_s_psi_nc(ctx, lda, n, m, C_LOC(psi), C_LOC(spsi)), 's_psi')
+    RETURN
+  END IF
   CALL qeb200_sync_state()
-  CALL qeb200_check(qeb_s_psi(ctx, lda, n, m, C_LOC(psi), C_LOC(spsi)), 's_psi')
+  CALL qeb200_check(qeb_s_psi(ctx, lda, n, npol*m, C_LOC(psi), C_LOC(spsi)), 's_psi')
 END SUBROUTINE s_psi_qeb
 
 !----------------------------------------------------------------------------

@@ -107,6 +107,11 @@ int qeb_vloc_psi_nc(qeb_ctx* ctx, int lda, int n, int m, const void* psi, const 
  * the context (qeb_get_becp with 2*m columns). Needs qeb_set_vloc_nc. Serial k-point descriptor only. */
 int qeb_set_nonlocal_nc(qeb_ctx* ctx, const void* deeq_nc);
 int qeb_h_psi_nc(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* hpsi);
+/* s_psi_nc   PW/src/s_psi.f90:308-370: spsi(lda*2,m) = psi + vkb (qq becp%nc), becp%nc from the preceding qeb_h_psi_nc.
+ * qeb_set_qq_nc: qq_nc(nhm,nhm,nat,4) COMPLEX(DP) per atom = qq_so(:,:,1:4,ityp(na)) with spin-orbit (:344-350), else
+ * qq_at(:,:,na) in blocks 1 and 4 (:336-342). Without it qeb_s_psi_nc is the norm-conserving copy. */
+int qeb_set_qq_nc(qeb_ctx* ctx, const void* qq_nc);
+int qeb_s_psi_nc(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* spsi);
 
 /* invfft / fwfft (kind, f, dfft, howmany)  FFTXlib/src/fft_interfaces.f90:19-80,
  * fft_fwinv.f90:10-216: in-place 3-D transform of howmany boxes f(nnr*howmany).

@@ -162,6 +162,17 @@ def h_psi_nc(d: Descriptor, lda, n, m, psi, v4, vkb, deeq_nc, nh_at, ofsbeta):
     return hpsi, becp
 
 
+def s_psi_nc(lda, n, m, psi, becp_nc, vkb, qq_nc, nh_at, ofsbeta):
+    """s_psi_nc, PW/src/s_psi.f90:308-370 (with the copy of all lda*npol rows, :118). qq_nc: (4, nat, nhm, nhm) per atom
+    (qq_so of the atom's type, or qq_at in blocks 1 and 4)."""
+    spsi = psi.copy()
+    if vkb is not None and vkb.shape[0] and qq_nc is not None:
+        ps = apply_deeq_nc(becp_nc, qq_nc, nh_at, ofsbeta)
+        for ipol in range(2):
+            spsi[:, ipol * lda:ipol * lda + n] += ps[:, ipol, :] @ vkb[:, :n]
+    return spsi
+
+
 def synthetic_deeq_nc(nh_at, seed: int = 0):
     """Hermitian 2x2-spin D matrices in the deeq_nc(nhm,nhm,nat,4) layout (as newd_nc / spin-orbit produce them:
     D^{ss'}_{ij} = conj(D^{s's}_{ji})); returned as (4, nat, nhm, nhm) complex."""

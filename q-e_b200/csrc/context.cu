@@ -116,6 +116,8 @@ struct qeb_ctx {
     bool have_vnc = false;
     DevBuf dnc_d;  // deeq_nc(nhm,nhm,nat,4) complex
     bool have_dnc = false;
+    DevBuf qnc_d;  // per-atom 2x2-spin overlap (nhm,nhm,nat,4) complex: qq_so of the atom's type, or qq_at on the diagonal
+    bool have_qnc = false;
     DevBuf revx_d;
     // full-box FFT plans
     DevBuf full_plan_d;
@@ -1752,6 +1754,60 @@ int qeb_s_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* spsi)
         const int ldps = (c->nkb + 1) & ~1;
         QEB_CUDA(c, cudaMemsetAsync(c->ps_d.p, 0, (size_t)ldps * m * (c->gamma ? 8 : 16), c->stream));
         if ((rc = run_addvus(c, lda, n, m, sd, 0, (const double*)c->qq_d.p))) return rc;
+    }
+    if (!out_dev) {
+        QEB_CUDA(c, cudaMemcpyAsync(spsi, sd, bytes, cudaMemcpyDeviceToHost, c->stream));
+        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return 0;
+    }
+    return finish(c);
+}
+
+// s_psi_nc (PW/src/s_psi.f90:308-370): qq_nc(nhm,nhm,nat,4) complex, per atom: qq_so(:,:,1:4,ityp(na)) with spin-orbit,
+// else qq_at(:,:,na) in blocks 1 and 4 and zero in 2 and 3 (:336-351)
+int qeb_set_qq_nc(qeb_ctx* c, const void* qq_nc)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!c->have_nl) QEB_FAIL(c, 51, "qeb_set_qq_nc: qeb_set_nonlocal has not been called (nat, nhm, nh, ofsbeta)");
+    if (!qq_nc) QEB_FAIL(c, 40, "qeb_set_qq_nc: null qq_nc");
+    const size_t nd = (size_t)c->nhm * c->nhm * c->nat * 4;
+    QEB_CUDA(c, c->qnc_d.ensure(nd * 16 + 16));
+    if (nd)
+        QEB_CUDA(c, cudaMemcpyAsync(c->qnc_d.p, qq_nc, nd * 16,
+                                    is_device_ptr(qq_nc) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_qnc = true;
+    return 0;
+}
+
+// spsi(lda*2,m) = psi + vkb (qq_nc becp%nc) with the becp%nc the preceding qeb_h_psi_nc left in the context
+int qeb_s_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, void* spsi)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    int rc = check_call(c, lda, n, m, psi, spsi, "qeb_s_psi_nc");
+    if (rc) return rc;
+    if (c->dist || c->gamma) QEB_FAIL(c, 63, "qeb_s_psi_nc: serial k-point descriptor only");
+    if (m == 0) return 0;
+    const size_t bytes = (size_t)lda * 2 * m * 16;
+    const bool okvan = c->nkb > 0 && c->have_qnc;
+    if (okvan && c->becp_m < 2 * m)
+        QEB_FAIL(c, 76, "qeb_s_psi_nc: no projections in the context for these spinors (qeb_h_psi_nc first)");
+    const bool out_dev = is_device_ptr(spsi);
+    cplx* sd = (cplx*)spsi;
+    if (!out_dev) {
+        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
+        sd = (cplx*)c->hpsi_stage.p;
+    }
+    QEB_CUDA(c, cudaMemcpyAsync(sd, psi, bytes, is_device_ptr(psi) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                                c->stream));
+    if (okvan) {
+        const int nkb = c->nkb, ldps = (nkb + 1) & ~1;
+        QEB_CUDA(c, cudaMemsetAsync(c->ps_d.p, 0, (size_t)ldps * 2 * m * 16, c->stream));
+        QEB_CUDA(c, launch_apply_deeq_nc(c->becp_d.p, nkb, m, c->row_atom_d, c->ofs_d, c->nh_d, c->qnc_d.p, c->nhm, c->nat,
+                                         c->ps_d.p, ldps, c->stream));
+        QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, c->ps_d.p, ldps, n, nkb, 2 * m, true, sd, lda, c->stream));
     }
     if (!out_dev) {
         QEB_CUDA(c, cudaMemcpyAsync(spsi, sd, bytes, cudaMemcpyDeviceToHost, c->stream));

@@ -59,6 +59,8 @@ def load_library():
     L.qeb_vloc_psi_nc.argtypes = [P, I, I, I, P, P, P]
     L.qeb_set_nonlocal_nc.argtypes = [P, P]
     L.qeb_h_psi_nc.argtypes = [P, I, I, I, P, P]
+    L.qeb_set_qq_nc.argtypes = [P, P]
+    L.qeb_s_psi_nc.argtypes = [P, I, I, I, P, P]
     L.qeb_fft.argtypes = [P, I, I, P, I]
     L.qeb_calbec.argtypes = [P, I, P, I, P, I, I, P]
     L.qeb_add_vuspsi.argtypes = [P, I, I, I, P, P]
@@ -91,7 +93,7 @@ def load_library():
     L.qeb_nonlocal_only.argtypes = [P, I, I, I, P, P]
     L.qeb_vloc_kernels_per_batch.argtypes = [P]
     for name in ("qeb_create", "qeb_destroy", "qeb_set_pipeline", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
-                 "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_set_vloc_nc", "qeb_vloc_psi_nc", "qeb_set_nonlocal_nc", "qeb_h_psi_nc", "qeb_fft",
+                 "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_set_vloc_nc", "qeb_vloc_psi_nc", "qeb_set_nonlocal_nc", "qeb_h_psi_nc", "qeb_set_qq_nc", "qeb_s_psi_nc", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
                  "qeb_set_grid_dist", "qeb_set_qq", "qeb_s_psi", "qeb_set_gvectors", "qeb_g2_kin", "qeb_set_beta_tables",
@@ -377,6 +379,15 @@ class HPsi:
         """h_psi for noncollinear spinors with magnetisation: psi(lda*2, m) -> hpsi(lda*2, m)"""
         self._ck(self._L.qeb_h_psi_nc(self._h, lda, n, m, _ptr(psi), _ptr(hpsi)), "qeb_h_psi_nc")
         return hpsi
+
+    def set_qq_nc(self, qq_nc):
+        """per-atom 2x2-spin overlap (nhm,nhm,nat,4) complex (memory (4, nat, nhm, nhm)) of s_psi_nc"""
+        self._ck(self._L.qeb_set_qq_nc(self._h, _ptr(qq_nc)), "qeb_set_qq_nc")
+
+    def s_psi_nc(self, lda, n, m, psi, spsi):
+        """s_psi for spinors: psi(lda*2, m) -> spsi(lda*2, m), becp%nc from the preceding h_psi_nc"""
+        self._ck(self._L.qeb_s_psi_nc(self._h, lda, n, m, _ptr(psi), _ptr(spsi)), "qeb_s_psi_nc")
+        return spsi
 
     def invfft(self, kind, f, howmany=1):
         """invfft(kind, f, dfft, howmany): G->R, in place."""

@@ -179,6 +179,14 @@ def test_h_psi_nc(mods, name, m):
     h.h_psi_nc(lda, n, m, psi_t, out_t)
     torch.cuda.synchronize()
     assert relerr(torch.view_as_complex(out_t).cpu().numpy(), ref) < TOL
+    # s_psi_nc with a spin-orbit-like 2x2 overlap, from the becp%nc in the context
+    qnc = R.synthetic_deeq_nc(inp["nh_at"], seed=100 + m)
+    sref = R.s_psi_nc(lda, n, m, np.nan_to_num(psi), becp_ref, np.nan_to_num(inp["vkb"]), qnc, inp["nh_at"], inp["ofsbeta"])
+    h.h_psi_nc(lda, n, m, psi, out)
+    h.set_qq_nc(qnc)
+    sp = np.zeros((m, 2 * lda), complex)
+    h.s_psi_nc(lda, n, m, np.nan_to_num(psi), sp)
+    assert relerr(sp, sref) < TOL
     # Hermitian spinor operator: <a|H b> = conj(<b|H a>)
     if m >= 2:
         live = np.zeros(2 * lda, bool)
