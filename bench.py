@@ -143,6 +143,13 @@ def cpu_reference_run(d, c, nh, m_sample: int, nthreads: int, reps: int = 1):
     ofs = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
     use_ref = R.ref_lib() is not None
     best = None
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: give OpenBLAS the host cores back for the reference's GEMMs
+    # (the FFT engine gets its thread count explicitly)
+    try:
+        from threadpoolctl import threadpool_limits
+        limiter = threadpool_limits(limits=nthreads)
+    except Exception:  # noqa: BLE001
+        limiter = None
     for _ in range(reps):
         t0 = time.perf_counter()
         hpsi = np.zeros((m_sample, lda), dtype=np.complex128)
@@ -161,6 +168,8 @@ def cpu_reference_run(d, c, nh, m_sample: int, nthreads: int, reps: int = 1):
             R.add_vuspsi_k(n, m_sample, vkb, ps, hpsi)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
+    if limiter is not None:
+        limiter.restore_original_limits()
     return best, ("reference" if use_ref else "port")
 
 
