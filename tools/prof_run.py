@@ -17,7 +17,7 @@ ap.add_argument("--workload", default="ausurf112")
 ap.add_argument("--bands", type=int, default=64)
 ap.add_argument("--calls", type=int, default=2)
 ap.add_argument("--batch", type=int, default=0)
-ap.add_argument("--mode", default="serial", choices=["serial", "rg"])
+ap.add_argument("--mode", default="serial", choices=["serial", "rg", "nc"])
 a = ap.parse_args()
 d, c, nh = workload(a.workload)
 n = lda = d.npw
@@ -43,7 +43,12 @@ else:
     h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
 h.set_vloc(rng.uniform(-1, 0, d.nnr))
 h.set_nonlocal(nh, ofs, deeq)
+if a.mode == "nc":  # noncollinear V_loc: the bands as bands/2 spinors through the 2x2 potential
+    h.set_vloc_nc(rng.uniform(-1, 1, (4, d.nnr)))
 for _ in range(a.calls):
-    h.h_psi(lda, n, a.bands, psi, hpsi)
+    if a.mode == "nc":
+        h.vloc_psi_nc(lda, n, a.bands // 2, psi, None, hpsi)
+    else:
+        h.h_psi(lda, n, a.bands, psi, hpsi)
 torch.cuda.synchronize()
 print("ok", h.stats())
