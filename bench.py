@@ -369,9 +369,9 @@ def run_ours(args):
         roofline_gemm["traffic_source"] = ("profiles/r1q_gemm_m800_ncu_full.csv: k_calbec3m 9.34+0.17 GB, k_addvus3m 5.36+1.21 GB "
                                            "per launch at m=800 (algorithmic operands: vkb 3.08 GB + psi/hpsi 1.22 GB each, per kernel)")
     if args.workload == "ausurf112" and kpb == 3:
-        roofline_vloc["traffic"] = (23.70e6 + 19.23e6 + 84.56e6 + 21.48e6 + 95.52e6 + 8.47e6) / 15 * mm
-        roofline_vloc["traffic_source"] = ("profiles/r1q_vloc_b15_ncu_full.csv: zinv 42.9 MB, plane 106.0 MB, zfwd 104.0 MB per "
-                                           "batch of 15 boxes (per-box figures scaled to the bands of the section)")
+        roofline_vloc["traffic"] = (33.77e6 + 51.11e6 + 108.42e6 + 45.59e6 + 129.37e6 + 18.71e6) / 20 * mm
+        roofline_vloc["traffic_source"] = ("profiles/r1zu_vloc_b20_ncu_full.csv: zinv 84.9 MB, plane 154.0 MB, zfwd 148.1 MB per "
+                                           "batch of 20 boxes (per-box figures scaled to the bands of the section)")
     # `roofline` = the kernel family with the largest share of the step
     roofline = roofline_gemm if (roofline_gemm and ms_nl >= ms_vloc) else roofline_vloc
     launches_step = nbatches * kpb + (4 if nkb else 0) + 1
