@@ -137,6 +137,10 @@ QEB_HD void spass_spin(int warp, int nwarps, int lane, int nl, double sgn, SrcU&
     for (int j = warp; j < NJ; j += nwarps) {
         const int base = j * R;
         cplx u[R], d[R];
+        double pv[R][4];  // the 2x2 potential of these R points: issued first, so that the global latency hides behind
+                          // the shared-memory loads and the two DIF butterflies
+#pragma unroll
+        for (int k = 0; k < R; ++k) mix.fetch(lane, base + k, pv[k]);
 #pragma unroll
         for (int b = 0; b < R; ++b) {
             u[b] = su.load(lane, base + b);
@@ -145,7 +149,7 @@ QEB_HD void spass_spin(int warp, int nwarps, int lane, int nl, double sgn, SrcU&
         Bfly<R>::run(u, sgn);
         Bfly<R>::run(d, sgn);
 #pragma unroll
-        for (int k = 0; k < R; ++k) mix.apply(lane, base + k, u[k], d[k]);
+        for (int k = 0; k < R; ++k) mix.apply(pv[k], u[k], d[k]);
         Bfly<R>::run(u, -sgn);
         Bfly<R>::run(d, -sgn);
 #pragma unroll
@@ -155,6 +159,43 @@ QEB_HD void spass_spin(int warp, int nwarps, int lane, int nl, double sgn, SrcU&
         }
     }
 }
+
+#if defined(__CUDACC__)
+// Spinor middle pass, half-warp layout: lanes 0-15 carry the up component of 16 lines, lanes 16-31 the down component
+// of the same lines, so one ordinary tile holds the spinor and the 2x2 mix is a register exchange with lane^16 between
+// the last DIF and the first DIT butterfly. Every lane of the warp takes part (idle lines compute on zeros).
+// Device only: the lane exchange has no serial emulation (tests: GPU parity at the AUSURF112 grid).
+template <class PL, class Src, class Mix>
+__device__ __forceinline__ void spass_spinx(int warp, int nwarps, int lane, double sgn, Src& src, Mix& mix)
+{
+    constexpr int R = PL::r(PL::NP - 1);
+    constexpr int NJ = PL::N / R;
+    const double s = lane < 16 ? 1.0 : -1.0;
+    for (int j = warp; j < NJ; j += nwarps) {
+        const int base = j * R;
+        cplx v[R];
+        double pv[R][4];
+#pragma unroll
+        for (int k = 0; k < R; ++k) mix.fetch(lane, base + k, pv[k]);
+#pragma unroll
+        for (int b = 0; b < R; ++b) v[b] = src.load(lane, base + b);
+        Bfly<R>::run(v, sgn);
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            cplx o;
+            o.x = __shfl_xor_sync(0xffffffffu, v[k].x, 16);
+            o.y = __shfl_xor_sync(0xffffffffu, v[k].y, 16);
+            // up:   psi_up (v1+v4) + psi_dn (v2 - i v3);  down: psi_dn (v1-v4) + psi_up (v2 + i v3)
+            const double a = pv[k][0] + s * pv[k][3];
+            const double sv3 = s * pv[k][2];
+            v[k] = mk(v[k].x * a + (o.x * pv[k][1] + o.y * sv3), v[k].y * a + (o.y * pv[k][1] - o.x * sv3));
+        }
+        Bfly<R>::run(v, -sgn);
+#pragma unroll
+        for (int k = 0; k < R; ++k) src.store(lane, base + k, v[k]);
+    }
+}
+#endif
 
 // run pass number `p` (runtime, warp-uniform) of plan PL: expands to a switch over the NP passes
 template <class PL, bool DIT, bool FUSE2, int P = 0, bool PF = false>

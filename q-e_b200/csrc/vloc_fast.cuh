@@ -195,15 +195,18 @@ struct SpinMix {
     const double* vnc;  // four arrays in the vp layout
     size_t vs;          // nr1*npos
     int npos, p0;
-    QEB_HD void apply(int line, int xpos, cplx& u, cplx& d) const
+    QEB_HD void fetch(int line, int xpos, double v[4]) const
     {
         const size_t iv = (size_t)xpos * npos + p0 + line;
 #if defined(__CUDA_ARCH__)
-        const double v1 = __ldg(vnc + iv), v2 = __ldg(vnc + vs + iv), v3 = __ldg(vnc + 2 * vs + iv), v4 = __ldg(vnc + 3 * vs + iv);
+        v[0] = __ldg(vnc + iv), v[1] = __ldg(vnc + vs + iv), v[2] = __ldg(vnc + 2 * vs + iv), v[3] = __ldg(vnc + 3 * vs + iv);
 #else
-        const double v1 = vnc[iv], v2 = vnc[vs + iv], v3 = vnc[2 * vs + iv], v4 = vnc[3 * vs + iv];
+        v[0] = vnc[iv], v[1] = vnc[vs + iv], v[2] = vnc[2 * vs + iv], v[3] = vnc[3 * vs + iv];
 #endif
-        const double a = v1 + v4, b = v1 - v4;
+    }
+    QEB_HD void apply(const double v[4], cplx& u, cplx& d) const
+    {
+        const double a = v[0] + v[3], b = v[0] - v[3], v2 = v[1], v3 = v[2];
         const cplx nu = mk(u.x * a + (d.x * v2 + d.y * v3), u.y * a + (d.y * v2 - d.x * v3));
         const cplx nd = mk(d.x * b + (u.x * v2 - u.y * v3), d.y * b + (u.y * v2 + u.x * v3));
         u = nu;

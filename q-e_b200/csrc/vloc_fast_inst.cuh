@@ -110,7 +110,77 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xspin_f(const __gr
     const FastTabs ft{twS, tabS, nullptr, nullptr};
     __syncthreads();
     for (int ph = 0; ph < 2 * PL::NP - 1; ++ph) {
-        xspin_fast_phase<PL>(ph, threadIdx.x, blockDim.x, t, blockIdx.x, blockIdx.y, smem, ft);
+        // band = fast grid index: the CTAs that share a line tile (the same slice of the four potentials) run together
+        xspin_fast_phase<PL>(ph, threadIdx.x, blockDim.x, t, blockIdx.y, blockIdx.x, smem, ft);
+        __syncthreads();
+    }
+}
+
+// spinor x pass, half-warp layout (fft_static.cuh::spass_spinx): block = (band, tile of 16 lines); ONE tile of 32 lanes
+// = 16 lines x 2 components, so the shared-memory footprint and the occupancy are those of the scalar x pass
+struct G2SpinX {  // lane -> (component = lane / 16, line = lane % 16); natural x, pruned; idle lines read zero
+    cplx* g2u;    // box of the up component; the down component is the next box
+    size_t g2_box;
+    const int* xmap;
+    int npos, p0, nl;
+    __device__ __forceinline__ cplx load(int lane, int x) const
+    {
+        const int line = lane & 15, xa = xmap[x];
+        if (xa < 0 || line >= nl) return mk(0.0, 0.0);
+        return g2u[(size_t)(lane >> 4) * g2_box + (size_t)xa * npos + p0 + line];
+    }
+    __device__ __forceinline__ void store(int lane, int x, cplx v) const
+    {
+        const int line = lane & 15, xa = xmap[x];
+        if (xa >= 0 && line < nl) g2u[(size_t)(lane >> 4) * g2_box + (size_t)xa * npos + p0 + line] = v;
+    }
+};
+struct SpinMixX {
+    const double* vnc;
+    size_t vs;
+    int npos, p0, nl;
+    __device__ __forceinline__ void fetch(int lane, int xpos, double v[4]) const
+    {
+        const int line = (lane & 15) < nl ? (lane & 15) : 0;
+        const size_t iv = (size_t)xpos * npos + p0 + line;
+        v[0] = __ldg(vnc + iv), v[1] = __ldg(vnc + vs + iv), v[2] = __ldg(vnc + 2 * vs + iv), v[3] = __ldg(vnc + 3 * vs + iv);
+    }
+};
+template <class PL>
+__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xspinx_f(const __grid_constant__ VlocTables t)
+{
+    QEB_SMEM;
+    constexpr int np = PL::NP;
+    cplx* twS = smem + ((size_t)t.nr1 * QEB_TL);
+    int* tabS = reinterpret_cast<int*>(twS + PL::N);
+    for (int i = threadIdx.x; i < PL::N; i += blockDim.x) twS[i] = t.px.tw[i];
+    for (int i = threadIdx.x; i < PL::N; i += blockDim.x) tabS[i] = t.xmap[i];
+    __syncthreads();
+    const int pair = blockIdx.x, p0 = blockIdx.y * 16;
+    const int nl = (t.npos - p0) < 16 ? (t.npos - p0) : 16;
+    const int warp = threadIdx.x / QEB_TL, lane = threadIdx.x % QEB_TL, nwarps = blockDim.x / QEB_TL;
+    LaneTile w{smem, QEB_TL};
+    G2SpinX g{t.g2 + (size_t)(2 * pair) * t.g2_box, t.g2_box, tabS, t.npos, p0, nl};
+    SpinMixX mix{t.vnc, (size_t)t.nr1 * t.npos, t.npos, p0, nl};
+    NoMid nm;
+    for (int ph = 0; ph < 2 * np - 1; ++ph) {
+        if (ph < np - 1) {
+            if (ph == 0)
+                SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, QEB_TL, twS, +1.0, g, w, nm);
+            else
+                SPassSel<PL, false, false>::run(ph, warp, nwarps, lane, QEB_TL, twS, +1.0, w, w, nm);
+        } else if (ph == np - 1) {
+            if (np == 1)
+                spass_spinx<PL>(warp, nwarps, lane, +1.0, g, mix);
+            else
+                spass_spinx<PL>(warp, nwarps, lane, +1.0, w, mix);
+        } else {
+            const int p = 2 * np - 2 - ph;
+            if (p == 0)
+                SPassSel<PL, true, false>::run(p, warp, nwarps, lane, QEB_TL, twS, -1.0, w, g, nm);
+            else
+                SPassSel<PL, true, false>::run(p, warp, nwarps, lane, QEB_TL, twS, -1.0, w, w, nm);
+        }
         __syncthreads();
     }
 }
@@ -196,6 +266,7 @@ void FastLaunch<PL>::attrs(int s)
     cudaFuncSetAttribute(k_vloc_xfus_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_xacc_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_xspin_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_xspinx_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
 }
 template <class PL>
 void FastLaunch<PL>::z(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
@@ -227,7 +298,13 @@ void FastLaunch<PL>::x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes
 template <class PL>
 void FastLaunch<PL>::xspin(const VlocTables& t, const VlocLaunchCfg& cfg, int nbands, cudaStream_t st)
 {
-    const dim3 grid(t.ntx, nbands);
+    if (env_int("QEB_XSPINX", 1)) {  // half-warp layout: one tile per spinor, 16 lines
+        const int nw = env_int("QEB_NWS", pick_warps<PL>(4, 10));
+        const dim3 gridx(nbands, (t.npos + 15) / 16);
+        k_vloc_xspinx_f<PL><<<gridx, nw * 32, (size_t)t.nr1 * QEB_TL * 16 + PL::N * 20 + 16, st>>>(t);
+        return;
+    }
+    const dim3 grid(nbands, t.ntx);
     // two tiles: one CTA per SM at the large grids, so the CTA carries all the warps the register file allows
     // (AUSURF112, 400 spinors: 10 warps 33.5 ms, 16 warps 31.0 ms)
     const size_t smem = 2 * cfg.smem_x + PL::N * 20 + 16;
