@@ -137,6 +137,7 @@ struct qeb_ctx {
     // caller's arrays page-locked once (the Davidson work arrays are re-used call after call)
     cudaStream_t s_in = nullptr, s_out = nullptr;
     std::vector<cudaEvent_t> ev;
+    std::vector<cudaEvent_t> ev_sub;  // sub-chunks of the first pipeline chunk
     struct HostReg { const char* p; size_t bytes; };
     std::vector<HostReg> hostreg;
     int pipeline_chunk = 0;  // 0 = automatic
@@ -264,6 +265,7 @@ int qeb_destroy(qeb_ctx* c)
         if (c->nccl_rg && c->nccl_rg_owned) nccl_api().CommDestroy(c->nccl_rg);
     }
     for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_sub) cudaEventDestroy(e);
     for (int i = 0; i < 5; ++i)
         if (c->vev[i]) cudaEventDestroy(c->vev[i]);
     for (int i = 1; i < 4; ++i)
@@ -1456,8 +1458,35 @@ static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* ps
     char* pd = (char*)c->psi_stage.p;
     char* hd = (char*)c->hpsi_stage.p;
     int c0 = 0;
+    // The copy-in of the first chunk is the one transfer no compute can hide. Its V_loc part only needs the columns
+    // that have landed, so the first chunk is copied in sub-chunks of `sub` columns and the V_loc passes follow them
+    // one sub-chunk behind; the projector GEMMs then run on the whole chunk (serial descriptor only: the distributed
+    // path keeps one collective schedule per chunk).
+    int sub = 40;
+    if (const char* e = getenv("QEB_PIPE_SUB")) sub = atoi(e);
+    if (sub & 1) ++sub;
     for (int i = 0; i < nch; c0 += sizes[i], ++i) {
         const int mm = sizes[i];
+        if (i == 0 && sub > 0 && mm > sub && !c->dist) {
+            while ((int)c->ev_sub.size() < (mm + sub - 1) / sub) {
+                cudaEvent_t e;
+                QEB_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                c->ev_sub.push_back(e);
+            }
+            for (int s0 = 0, k = 0; s0 < mm; s0 += sub, ++k) {
+                const int ms = std::min(sub, mm - s0);
+                QEB_CUDA(c, cudaMemcpyAsync(pd + col * s0, ph + col * s0, col * ms, cudaMemcpyHostToDevice, c->s_in));
+                QEB_CUDA(c, cudaEventRecord(c->ev_sub[k], c->s_in));
+                QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_sub[k], 0));
+                if ((rc = h_psi_cols(c, lda, n, ms, (const cplx*)(pd + col * s0), (cplx*)(hd + col * s0), true, false, true)))
+                    return rc;
+            }
+            if ((rc = h_psi_cols(c, lda, n, mm, (const cplx*)pd, (cplx*)hd, false, true, true, 0, m))) return rc;
+            QEB_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
+            QEB_CUDA(c, cudaStreamWaitEvent(c->s_out, c->ev[1], 0));
+            QEB_CUDA(c, cudaMemcpyAsync(hh, hd, col * mm, cudaMemcpyDeviceToHost, c->s_out));
+            continue;
+        }
         QEB_CUDA(c, cudaMemcpyAsync(pd + col * c0, ph + col * c0, col * mm, cudaMemcpyHostToDevice, c->s_in));
         QEB_CUDA(c, cudaEventRecord(c->ev[2 * i], c->s_in));
         QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev[2 * i], 0));

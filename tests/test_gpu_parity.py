@@ -379,11 +379,14 @@ def test_hermiticity_full_size_ausurf(mods):
 
 
 @pytest.mark.parametrize("name", ["ortho_small", "ortho_small_gamma"])
-@pytest.mark.parametrize("m,chunk", [(11, 4), (12, 6), (7, 2)])
-def test_h_psi_host_pipeline(mods, name, m, chunk):
+@pytest.mark.parametrize("m,chunk,sub", [(11, 4, 0), (12, 6, 0), (7, 2, 0), (12, 6, 2), (11, 8, 4), (9, 9, 2)])
+def test_h_psi_host_pipeline(mods, name, m, chunk, sub, monkeypatch):
     """Host psi/hpsi through the chunked three-stream pipeline (qeb_set_pipeline): same result as the oracle,
-    pad rows zeroed, becp of all columns kept; pageable numpy arrays get page-locked by the library."""
+    pad rows zeroed, becp of all columns kept; pageable numpy arrays get page-locked by the library.
+    sub > 0: the first chunk is copied in sub-chunks with the V_loc passes following them (QEB_PIPE_SUB)."""
     qe, D, R, torch = mods
+    if sub:
+        monkeypatch.setenv("QEB_PIPE_SUB", str(sub))
     d = D.config_descriptor(name)
     inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=11)
     lda, n = inp["lda"], inp["n"]
