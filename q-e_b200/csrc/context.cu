@@ -138,6 +138,7 @@ struct qeb_ctx {
     cudaStream_t s_in = nullptr, s_out = nullptr;
     std::vector<cudaEvent_t> ev;
     std::vector<cudaEvent_t> ev_sub;  // sub-chunks of the first pipeline chunk
+    std::vector<cudaEvent_t> ev_tail;  // add_vuspsi sub-chunks of the last pipeline chunks
     struct HostReg { const char* p; size_t bytes; };
     std::vector<HostReg> hostreg;
     int pipeline_chunk = 0;  // 0 = automatic
@@ -266,6 +267,7 @@ int qeb_destroy(qeb_ctx* c)
     }
     for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
     for (cudaEvent_t e : c->ev_sub) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_tail) cudaEventDestroy(e);
     for (int i = 0; i < 5; ++i)
         if (c->vev[i]) cudaEventDestroy(c->vev[i]);
     for (int i = 1; i < 4; ++i)
@@ -1465,6 +1467,9 @@ static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* ps
     int sub = 40;
     if (const char* e = getenv("QEB_PIPE_SUB")) sub = atoi(e);
     if (sub & 1) ++sub;
+    int tsub = 64;  // one band tile of the add_vuspsi kernels
+    if (const char* e = getenv("QEB_PIPE_TAIL")) tsub = atoi(e);
+    if (tsub & 1) ++tsub;
     for (int i = 0; i < nch; c0 += sizes[i], ++i) {
         const int mm = sizes[i];
         if (i == 0 && sub > 0 && mm > sub && !c->dist) {
@@ -1490,6 +1495,31 @@ static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* ps
         QEB_CUDA(c, cudaMemcpyAsync(pd + col * c0, ph + col * c0, col * mm, cudaMemcpyHostToDevice, c->s_in));
         QEB_CUDA(c, cudaEventRecord(c->ev[2 * i], c->s_in));
         QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev[2 * i], 0));
+        if (i > 0 && i >= nch - 2 && tsub > 0 && mm > tsub && !c->dist && c->nkb > 0 && c->vkb_d && c->have_nl) {
+            // The copy-out of the last chunks is the other transfer little compute is left to hide: add_vuspsi, the last
+            // kernel of a chunk, runs in sub-chunks of one band tile and each sub-chunk is copied out behind it.
+            const cplx* pc = (const cplx*)(pd + col * c0);
+            cplx* hc = (cplx*)(hd + col * c0);
+            if ((rc = h_psi_cols(c, lda, n, mm, pc, hc, true, false, true))) return rc;
+            char* becp = (char*)c->becp_d.p + (size_t)c0 * c->nkb * (c->gamma ? 8 : 16);
+            if ((rc = run_calbec(c, c->vkb_d, c->npwx, c->nkb, pc, lda, n, mm, becp))) return rc;
+            c->becp_m = c0 + mm;
+            while ((int)c->ev_tail.size() < (mm + tsub - 1) / tsub) {
+                cudaEvent_t e;
+                QEB_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                c->ev_tail.push_back(e);
+            }
+            for (int s0 = 0, k = 0; s0 < mm; s0 += tsub, ++k) {
+                const int ms = std::min(tsub, mm - s0);
+                cplx* hs = hc + (size_t)s0 * lda;
+                if ((rc = run_addvus(c, lda, n, ms, hs, c0 + s0))) return rc;
+                if (c->gamma && c->gstart == 2) QEB_CUDA(c, launch_zero_im_g0(hs, lda, ms, c->stream));
+                QEB_CUDA(c, cudaEventRecord(c->ev_tail[k], c->stream));
+                QEB_CUDA(c, cudaStreamWaitEvent(c->s_out, c->ev_tail[k], 0));
+                QEB_CUDA(c, cudaMemcpyAsync(hh + col * (c0 + s0), hs, col * ms, cudaMemcpyDeviceToHost, c->s_out));
+            }
+            continue;
+        }
         if ((rc = h_psi_cols(c, lda, n, mm, (const cplx*)(pd + col * c0), (cplx*)(hd + col * c0), true, true, true, c0, m)))
             return rc;
         QEB_CUDA(c, cudaEventRecord(c->ev[2 * i + 1], c->stream));

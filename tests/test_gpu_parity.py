@@ -379,7 +379,7 @@ def test_hermiticity_full_size_ausurf(mods):
 
 
 @pytest.mark.parametrize("name", ["ortho_small", "ortho_small_gamma"])
-@pytest.mark.parametrize("m,chunk,sub", [(11, 4, 0), (12, 6, 0), (7, 2, 0), (12, 6, 2), (11, 8, 4), (9, 9, 2)])
+@pytest.mark.parametrize("m,chunk,sub", [(11, 4, 0), (12, 6, 0), (7, 2, 0), (12, 6, 2), (11, 8, 4), (9, 9, 2), (13, 4, 2)])
 def test_h_psi_host_pipeline(mods, name, m, chunk, sub, monkeypatch):
     """Host psi/hpsi through the chunked three-stream pipeline (qeb_set_pipeline): same result as the oracle,
     pad rows zeroed, becp of all columns kept; pageable numpy arrays get page-locked by the library.
@@ -387,6 +387,7 @@ def test_h_psi_host_pipeline(mods, name, m, chunk, sub, monkeypatch):
     qe, D, R, torch = mods
     if sub:
         monkeypatch.setenv("QEB_PIPE_SUB", str(sub))
+        monkeypatch.setenv("QEB_PIPE_TAIL", str(sub))  # add_vuspsi + copy-out of the last chunks in sub-chunks
     d = D.config_descriptor(name)
     inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=11)
     lda, n = inp["lda"], inp["n"]
