@@ -107,4 +107,13 @@ ms = timed(lambda: h.vloc_psi_nc(lda, n, m // 2, psi, None, hpsi))
 ms_k = timed(lambda: h.vloc_psi_k(lda, n, m, psi, None, hpsi))
 out(item="vloc_psi_nc (400 spinors = 800 component FFT pairs, spinor x pass)", ms=ms, us_per_component=1e3 * ms / m,
     scalar_vloc_psi_k_same_columns_ms=ms_k)
+# whole noncollinear h_psi (kinetic + vloc_psi_nc + calbec_nc + add_vuspsi_nc) and s_psi_nc on the same 400 spinors
+dnc = torch.randn((4, nat, 18, 18, 2), generator=g, device=dev, dtype=torch.float64)
+h.set_nonlocal_nc(dnc)
+ms = timed(lambda: h.h_psi_nc(lda, n, m // 2, psi, hpsi))
+out(item="h_psi_nc (400 spinors: 2x2 potential, deeq_nc)", ms=ms, spinor_apps_per_s=(m // 2) / (ms * 1e-3),
+    scalar_h_psi_800_columns_ms=ms_h)
+h.set_qq_nc(dnc)
+ms = timed(lambda: h.s_psi_nc(lda, n, m // 2, psi, spsi))
+out(item="s_psi_nc (400 spinors, re-uses becp%nc)", ms=ms)
 h.close()
