@@ -1414,7 +1414,8 @@ static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* ps
     int mc = c->pipeline_chunk;
     if (mc <= 0) {
         // whole band tiles of BOTH projector kernels (calbec: 48 bands, add_vuspsi: 64): multiples of 192; measured at
-        // AUSURF112 m=800 (tools/e2e_sweep.py): 96 -> 101.0, 128 -> 95.7, 192 -> 93.1, 256 -> 100.0, 400 -> 112.9 ms
+        // AUSURF112 m=800 (tools/e2e_sweep.py): 96 -> 101.0, 128 -> 95.7, 192 -> 93.1, 256 -> 100.0, 400 -> 112.9 ms;
+        // with the sub-chunked first copy-in / last copy-outs below: 192 -> 87.9, 256 -> 91.5, 272 -> 93.0, 400 -> 91.2 ms
         mc = m >= 384 ? 192 : ((m + 7) / 8 + 63) / 64 * 64;
         if (mc < 64) mc = 64;
     }
