@@ -23,6 +23,15 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_destroy(ctx) BIND(C, name='qeb_destroy')
       IMPORT; TYPE(C_PTR), VALUE :: ctx
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_pin_host(ctx, p, bytes) BIND(C, name='qeb_pin_host')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, p; INTEGER(C_SIZE_T), VALUE :: bytes
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_unpin_host(ctx, p) BIND(C, name='qeb_unpin_host')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, p
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_device_count() BIND(C, name='qeb_device_count')
+      IMPORT
+    END FUNCTION
     TYPE(C_PTR) FUNCTION qeb_last_error(ctx) BIND(C, name='qeb_last_error')
       IMPORT; TYPE(C_PTR), VALUE :: ctx
     END FUNCTION
@@ -167,6 +176,18 @@ CONTAINS
     END DO
     CALL errore(routine, TRIM(msg), INT(rc))   ! UtilXlib/error_handler.f90:10 -> mp_abort
   END SUBROUTINE
+  FUNCTION qeb200_local_device() RESULT(dev)
+    !! The device mp_world_start binds this rank to: mod(node-local rank, device count)
+    !! (Modules/mp_world.f90:84-94: mp_count_nodes gives `key`, cudaSetDevice(mod(key, ndev))).
+    USE mp_world, ONLY: world_comm
+    USE mp,       ONLY: mp_count_nodes
+    INTEGER(C_INT) :: dev
+    INTEGER :: nnode_, color, key, ndev
+    CALL mp_count_nodes(nnode_, color, key, world_comm)
+    ndev = qeb_device_count()
+    IF (ndev < 1) CALL errore('qeb200', 'no CUDA device (the library has no CPU fallback)', 1)
+    dev = INT(MOD(key, ndev), C_INT)
+  END FUNCTION
   SUBROUTINE qeb200_touch_vloc();  vloc_version = vloc_version + 1; END SUBROUTINE
   SUBROUTINE qeb200_touch_deeq();  deeq_version = deeq_version + 1; END SUBROUTINE
   SUBROUTINE qeb200_touch_kpoint(); k_set = -1; END SUBROUTINE   ! after init_us_2 when atoms move
@@ -184,11 +205,10 @@ CONTAINS
     USE uspp_param,    ONLY: nh, nhm
     USE ions_base,     ONLY: nat, ityp
     USE control_flags, ONLY: gamma_only
-    USE mp_world,      ONLY: mpime
     INTEGER(C_INT), ALLOCATABLE, TARGET :: nh_at(:), ofs0(:)
     INTEGER :: na, ig
     TYPE(C_PTR) :: pnlm, pigk
-    IF (.NOT. C_ASSOCIATED(ctx)) CALL qeb200_check(qeb_create(ctx, INT(mpime, C_INT), C_NULL_PTR), 'qeb_create')
+    IF (.NOT. C_ASSOCIATED(ctx)) CALL qeb200_check(qeb_create(ctx, qeb200_local_device(), C_NULL_PTR), 'qeb_create')
     IF (.NOT. grid_set) THEN
       pnlm = C_NULL_PTR
       IF (gamma_only) pnlm = C_LOC(dffts%nlm)
@@ -324,7 +344,7 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
   INTEGER, INTENT(IN) :: lda, n, m
   COMPLEX(DP), INTENT(IN), TARGET :: psi(lda*npol, m)
   COMPLEX(DP), INTENT(OUT), TARGET :: hpsi(lda*npol, m)
-  INTEGER :: m_start, m_end, column_type
+  INTEGER :: m_start, m_end, column_type, m_becp
   INTEGER, ALLOCATABLE :: recv_counts(:), displs(:)
   !
   IF (real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. exx_is_active() .OR. &
@@ -342,6 +362,7 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
     RETURN
   END IF
   CALL qeb200_sync_state()
+  m_becp = m
   IF (noncolin) THEN
     ! Non-magnetic spinors without spin-orbit: both components see the same g2kin, the same scalar V(r)
     ! (vloc_psi_nc with domag = .FALSE., vloc_psi_acc.f90:269-369) and deeq_nc(:,:,na,1) = deeq_nc(:,:,na,4) = deeq,
@@ -357,6 +378,9 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
     ALLOCATE(recv_counts(mp_size(inter_bgrp_comm)), displs(mp_size(inter_bgrp_comm)))
     CALL divide_all(inter_bgrp_comm, m, m_start, m_end, recv_counts, displs)
     CALL qeb200_check(qeb_h_psi_bgrp(ctx, lda, n, m, C_LOC(psi), C_LOC(hpsi), nbgrp, my_bgrp_id), 'h_psi')
+    ! like the reference (h_psi.f90:57-62: h_psi_ on psi(1,m_start) with m_end-m_start+1 columns), becp then holds the
+    ! projections of THIS group's column block in its first columns, not those of all m bands
+    m_becp = MAX(m_end - m_start + 1, 0)
     CALL mp_type_create_column_section(hpsi(1, 1), 0, lda*npol, lda*npol, column_type)
     CALL mp_allgather(hpsi, column_type, recv_counts, displs, inter_bgrp_comm)
     CALL mp_type_free(column_type)
@@ -365,11 +389,11 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
     CALL qeb200_check(qeb_h_psi(ctx, lda, n, m, C_LOC(psi), C_LOC(hpsi)), 'h_psi')
   END IF
   ! side effect callers rely on (s_psi.f90:15,132,157): becmod::becp = <beta|psi> of these m columns
-  IF (nkb > 0) THEN
+  IF (nkb > 0 .AND. m_becp > 0) THEN
     IF (gamma_only) THEN
-      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%r), m), 'h_psi')
+      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%r), m_becp), 'h_psi')
     ELSE
-      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%k), m), 'h_psi')
+      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%k), m_becp), 'h_psi')
     END IF
   END IF
   CALL stop_clock('h_psi')

@@ -23,6 +23,8 @@
 #ifndef QEB200_H
 #define QEB200_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -36,6 +38,9 @@ typedef struct qeb_ctx qeb_ctx;
  * synchronises it before every entry point returns, which reproduces the
  * reference's blocking OpenACC regions). */
 int qeb_create(qeb_ctx** ctx, int device, void* stream);
+/* number of CUDA devices visible to the process (0 without a driver): the shim binds rank -> device with
+ * mod(node-local rank, qeb_device_count()), as Modules/mp_world.f90:87-94 does */
+int qeb_device_count(void);
 int qeb_destroy(qeb_ctx* ctx);
 const char* qeb_last_error(const qeb_ctx* ctx);
 /* version / build info string */
@@ -49,9 +54,14 @@ int qeb_set_async(qeb_ctx* ctx, int async);
 
 /* Host-buffer pipeline of qeb_h_psi: when psi and hpsi are HOST arrays with at least min_cols columns, the call is
  * split into chunks of chunk_cols columns (0 = automatic, about m/8 rounded to 64) whose H2D copy, kernels and D2H
- * copy overlap on three streams; the caller's arrays are page-locked once (cudaHostRegister) unless the
- * environment variable QEB_NO_HOSTREG is set. Columns are independent (h_psi.f90:53-67), results are unchanged. */
+ * copy overlap on three streams. Columns are independent (h_psi.f90:53-67), results are unchanged.
+ * The copies only overlap the kernels when the caller's arrays are page-locked. The library never page-locks caller
+ * memory on its own (it cannot see the caller free and re-allocate an array): the host brackets the lifetime of its
+ * work arrays with qeb_pin_host / qeb_unpin_host (cudaHostRegister), e.g. right after cegterg's ALLOCATE(psi, hpsi)
+ * and before the DEALLOCATE (KS_Solvers/Davidson/cegterg.f90:150-175, :680-700). Pageable arrays work, slower. */
 int qeb_set_pipeline(qeb_ctx* ctx, int chunk_cols, int min_cols);
+int qeb_pin_host(qeb_ctx* ctx, void* p, size_t bytes);
+int qeb_unpin_host(qeb_ctx* ctx, void* p); /* synchronises the context's streams first; call before freeing p */
 
 /* ---- state setters ----------------------------------------------------- */
 /* FFT grid + G-vector maps of dffts (serial descriptor):

@@ -309,15 +309,16 @@ def s_psi(d: Descriptor, lda, n, m, psi, becp, vkb=None, qq_at=None, nh_at=None,
     return spsi
 
 
-def synthetic_qq(nh_at, seed: int = 0):
-    """qq_at(nhm,nhm,nat) as numpy (nat,nhm,nhm): symmetric, like the integrals of Q_ij (upflib/init_us_1.f90)."""
+def synthetic_qq(nh_at, seed: int = 0, symmetric: bool = True):
+    """qq_at(nhm,nhm,nat) as numpy (nat,nhm,nhm): symmetric, like the integrals of Q_ij (upflib/init_us_1.f90);
+    symmetric=False pins the (ih,jh) orientation in a parity test."""
     nh_at = np.asarray(nh_at, dtype=np.int32)
     nhm = int(nh_at.max()) if len(nh_at) else 0
     rng = np.random.default_rng(5234 + seed)
     qq = np.zeros((len(nh_at), nhm, nhm))
     for a, nh in enumerate(nh_at):
         Q = rng.uniform(-0.5, 0.5, (nh, nh))
-        qq[a, :nh, :nh] = 0.5 * (Q + Q.T)
+        qq[a, :nh, :nh] = 0.5 * (Q + Q.T) if symmetric else Q
     return qq
 
 
@@ -332,7 +333,8 @@ def divide_all(m: int, nproc: int):
 # ----------------------------------------------------------------------------
 # Synthetic inputs
 # ----------------------------------------------------------------------------
-def synthetic_inputs(d: Descriptor, m: int, nh_at, seed: int = 0, lda: int | None = None, poison: bool = True):
+def synthetic_inputs(d: Descriptor, m: int, nh_at, seed: int = 0, lda: int | None = None, poison: bool = True,
+                     symmetric: bool = True):
     """Returns dict(psi (m,lda), vrs (nnr), vkb (nkb,lda), deeq (nat,nhm,nhm), nh_at, ofsbeta)."""
     n = d.npw
     if lda is None:
@@ -360,7 +362,8 @@ def synthetic_inputs(d: Descriptor, m: int, nh_at, seed: int = 0, lda: int | Non
     deeq = np.zeros((len(nh_at), nhm, nhm))
     for a, nh in enumerate(nh_at):
         D = rng.uniform(-1.0, 1.0, (nh, nh))
-        deeq[a, :nh, :nh] = 0.5 * (D + D.T)
+        # symmetric=False: a general matrix, so that the (ih,jh) orientation of deeq(ih,jh,na) is pinned by the test
+        deeq[a, :nh, :nh] = 0.5 * (D + D.T) if symmetric else D
     return dict(psi=psi, vrs=vrs, vkb=vkb, deeq=deeq, nh_at=nh_at, ofsbeta=ofsbeta, lda=lda, n=n, m=m, nkb=nkb)
 
 

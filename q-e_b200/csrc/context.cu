@@ -202,6 +202,16 @@ extern "C" {
 
 const char* qeb_version(void) { return "qeb200 0.1 (sm_100a; FP64 DMMA projectors; radix-2/3/5 pencil FFT)"; }
 
+int qeb_device_count(void)
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return ndev;
+}
+
 int qeb_create(qeb_ctx** out, int device, void* stream)
 {
     if (!out) return 1;
@@ -255,7 +265,8 @@ int qeb_destroy(qeb_ctx* c)
                       &c->revx_d, &c->full_plan_d, &c->nlint_d, &c->deeq_d, &c->becp_d, &c->ps_d, &c->part_d,
                       &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage, &c->tabp_d, &c->planp_d,
                       &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d, &c->qq_d, &c->us_int_d, &c->tab_beta_d, &c->us_scratch_d,
-                      &c->us_in_d, &c->gv_g_d, &c->gv_mill_d, &c->igk_dev_d, &c->st_eig_d, &c->st_int_d, &c->gpsi_d, &c->dav_small_d, &c->rho_d, &c->wts_d};
+                      &c->us_in_d, &c->gv_g_d, &c->gv_mill_d, &c->igk_dev_d, &c->st_eig_d, &c->st_int_d, &c->gpsi_d, &c->dav_small_d, &c->rho_d, &c->wts_d, &c->vnc_d, &c->dnc_d,
+                      &c->qnc_d};
     for (void* m : c->p2p_opened) cudaIpcCloseMemHandle(m);
     c->p2p_opened.clear();
     for (DevBuf* b : bufs) b->release();
@@ -303,6 +314,35 @@ int qeb_set_async(qeb_ctx* c, int async)
     if (!c) return 1;
     c->async = async != 0;
     return 0;
+}
+
+int qeb_pin_host(qeb_ctx* c, void* p, size_t bytes)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    if (!p || bytes == 0) QEB_FAIL(c, 110, "qeb_pin_host: bad arguments");
+    for (auto& r : c->hostreg)
+        if (r.p == (const char*)p) QEB_FAIL(c, 111, "qeb_pin_host: this address is already pinned (qeb_unpin_host first)");
+    QEB_CUDA(c, cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+    c->hostreg.push_back({(const char*)p, bytes});
+    return 0;
+}
+
+int qeb_unpin_host(qeb_ctx* c, void* p)
+{
+    if (!c) return 1;
+    QEB_CUDA(c, cudaSetDevice(c->device));
+    for (size_t i = 0; i < c->hostreg.size(); ++i)
+        if (c->hostreg[i].p == (const char*)p) {
+            // copies queued on the pipeline streams may still read the range
+            QEB_CUDA(c, cudaStreamSynchronize(c->stream));
+            if (c->s_in) QEB_CUDA(c, cudaStreamSynchronize(c->s_in));
+            if (c->s_out) QEB_CUDA(c, cudaStreamSynchronize(c->s_out));
+            c->hostreg.erase(c->hostreg.begin() + i);
+            QEB_CUDA(c, cudaHostUnregister(p));
+            return 0;
+        }
+    QEB_FAIL(c, 112, "qeb_unpin_host: this address was not pinned with qeb_pin_host");
 }
 
 // plans for the x direction permutation of V and for the full-box FFT
@@ -1171,6 +1211,8 @@ int qeb_p2p_import(qeb_ctx* c, const void* blobs, int nranks)
     if (!blobs || nranks != D.nproc) QEB_FAIL(c, 99, "qeb_p2p_import: one blob per rank of the R&G group expected");
     P2PState& P = c->P2P;
     P = P2PState();
+    for (void* m : c->p2p_opened) cudaIpcCloseMemHandle(m);  // mappings of a previous import
+    c->p2p_opened.clear();
     P.nslots = c->vloc_nstreams;
     P.batch = c->batch;
     P.peer_S.assign(nranks, nullptr);
@@ -1373,36 +1415,10 @@ static int h_psi_cols(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx
     return 0;
 }
 
-// Page-locks the caller's host array once so that its chunks can be copied asynchronously (pageable memory would
-// serialise the copies with the kernels). Ranges are remembered; already pinned memory is left alone.
-static void pin_host_range(qeb_ctx* c, const void* p, size_t bytes)
-{
-    if (bytes < ((size_t)1 << 20) || getenv("QEB_NO_HOSTREG")) return;  // small copies do not need the overlap
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost) return;  // pinned already
-    cudaGetLastError();
-    const char* b = (const char*)p;
-    for (auto& r : c->hostreg)
-        if (b >= r.p && b + bytes <= r.p + r.bytes) return;
-    // drop registrations this range overlaps (the caller re-allocated)
-    for (size_t i = 0; i < c->hostreg.size();) {
-        auto& r = c->hostreg[i];
-        if (b < r.p + r.bytes && r.p < b + bytes) {
-            cudaHostUnregister((void*)r.p);
-            c->hostreg.erase(c->hostreg.begin() + i);
-        } else {
-            ++i;
-        }
-    }
-    if (c->hostreg.size() >= 8) {
-        cudaHostUnregister((void*)c->hostreg.front().p);
-        c->hostreg.erase(c->hostreg.begin());
-    }
-    if (cudaHostRegister((void*)p, bytes, cudaHostRegisterDefault) == cudaSuccess)
-        c->hostreg.push_back({b, bytes});
-    else
-        cudaGetLastError();  // not fatal: the copies just do not overlap
-}
+// Page-locking of caller memory is EXPLICIT (qeb_pin_host / qeb_unpin_host, bracketing the lifetime of the caller's
+// work arrays): the library never registers memory on its own, because it cannot see the caller free and re-allocate
+// an array at the same address. Unpinned (pageable) arrays go through the same pipeline; cudaMemcpyAsync then stages
+// them through the driver's bounce buffers and the copies overlap less.
 
 // h_psi with HOST psi and hpsi: column chunks flow through three streams, so the H2D copy of chunk i+1 and the D2H
 // copy of chunk i-1 overlap the kernels of chunk i. Every column is independent in h_psi (h_psi.f90:53-67 splits
@@ -1450,8 +1466,6 @@ static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* ps
     }
     QEB_CUDA(c, c->psi_stage.ensure(col * m));
     QEB_CUDA(c, c->hpsi_stage.ensure(col * m));
-    pin_host_range(c, psi, col * m);
-    pin_host_range(c, hpsi, col * m);
     if (c->nkb > 0 && (rc = ensure_becp(c, c->nkb, m))) return rc;
     // the staging buffers may still be read by work queued earlier on the compute stream (async callers)
     QEB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));

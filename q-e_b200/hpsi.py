@@ -48,6 +48,9 @@ def load_library():
     L.qeb_set_batch.argtypes = [P, I]
     L.qeb_set_async.argtypes = [P, I]
     L.qeb_set_pipeline.argtypes = [P, I, I]
+    L.qeb_pin_host.argtypes = [P, P, ctypes.c_size_t]
+    L.qeb_unpin_host.argtypes = [P, P]
+    L.qeb_device_count.argtypes = []
     L.qeb_set_grid.argtypes = [P, I, I, I, I, I, I, I, P, P, I]
     L.qeb_set_kpoint.argtypes = [P, I, I, P, P, P, I, I]
     L.qeb_set_vloc.argtypes = [P, P]
@@ -92,7 +95,7 @@ def load_library():
                                 ctypes.POINTER(I), ctypes.POINTER(I), ctypes.POINTER(I)]
     L.qeb_nonlocal_only.argtypes = [P, I, I, I, P, P]
     L.qeb_vloc_kernels_per_batch.argtypes = [P]
-    for name in ("qeb_create", "qeb_destroy", "qeb_set_pipeline", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
+    for name in ("qeb_create", "qeb_destroy", "qeb_device_count", "qeb_pin_host", "qeb_unpin_host", "qeb_set_pipeline", "qeb_set_batch", "qeb_set_async", "qeb_set_grid", "qeb_set_kpoint",
                  "qeb_set_vloc", "qeb_set_nonlocal", "qeb_h_psi", "qeb_vloc_psi_k", "qeb_vloc_psi_gamma", "qeb_set_vloc_nc", "qeb_vloc_psi_nc", "qeb_set_nonlocal_nc", "qeb_h_psi_nc", "qeb_set_qq_nc", "qeb_s_psi_nc", "qeb_fft",
                  "qeb_calbec", "qeb_add_vuspsi", "qeb_get_becp", "qeb_divide_all", "qeb_h_psi_bgrp", "qeb_set_nccl",
                  "qeb_get_stats", "qeb_nonlocal_only", "qeb_set_nccl_comm", "qeb_nccl_unique_id", "qeb_nccl_init",
@@ -186,6 +189,13 @@ class HPsi:
 
     def set_pipeline(self, chunk_cols: int = 0, min_cols: int = 128):
         self._ck(self._L.qeb_set_pipeline(self._h, chunk_cols, min_cols), "qeb_set_pipeline")
+
+    def pin_host(self, arr):
+        """Page-locks a host array for the host pipeline (cudaHostRegister); the caller unpins it before freeing."""
+        self._ck(self._L.qeb_pin_host(self._h, _ptr(arr), arr.nbytes), "qeb_pin_host")
+
+    def unpin_host(self, arr):
+        self._ck(self._L.qeb_unpin_host(self._h, _ptr(arr)), "qeb_unpin_host")
 
     def set_async(self, flag: bool):
         self._ck(self._L.qeb_set_async(self._h, int(flag)), "qeb_set_async")

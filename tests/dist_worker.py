@@ -21,6 +21,13 @@ from oracle import hpsi_ref as R  # noqa: E402
 TOL = 1e-11
 
 
+def colerr(a, b):
+    """per-column (band) error relative to that column's own max"""
+    num = np.abs(a - b).max(axis=1)
+    den = np.abs(b).max(axis=1)
+    return float((num / den).max())
+
+
 def setup_rank(h, d, dd, me, inp, pad):
     rk = dd.ranks[me]
     h.set_grid_dist(d.nr1, d.nr2, d.nr3, dd.nproc, me, dd.nr3p, dd.nsw, dd.iss, dd.ismap, rk.nl,
@@ -36,12 +43,13 @@ def setup_rank(h, d, dd, me, inp, pad):
 
 def main():
     name, m = sys.argv[1], int(sys.argv[2])
+    big = name in ("si512", "h2o64", "ausurf112")  # BASELINE grids: fewer projectors keep the CPU oracle in seconds
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     d = D.config_descriptor(name)
-    nh = [8, 8, 8]
+    nh = [4] * 6 if big else [8, 8, 8]
     inp = R.synthetic_inputs(d, m, nh, seed=21, poison=False)
     n = inp["n"]
     ref, becp_ref = R.h_psi(d, inp["lda"], n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
@@ -58,8 +66,9 @@ def main():
         psi_l = X.split_rows(dd, inp["psi"][:, :n], pad=3, fill=np.nan)[rank]
         out = np.full((m, lda), np.nan + 1j * np.nan)
         h.h_psi(lda, rk.npw, m, psi_l, out)
-        e1 = np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max() / np.abs(ref).max()
-        e2 = np.abs(h.get_becp(m) - becp_ref).max() / np.abs(becp_ref).max()
+        # per band, relative to the band's own norm over ALL plane waves (this rank holds a subset of the rows)
+        e1 = float((np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max(axis=1) / np.abs(ref).max(axis=1)).max())
+        e2 = colerr(h.get_becp(m), becp_ref)
         ok = ok and e1 < TOL and e2 < TOL and np.all(out[:, rk.npw:] == 0)
         print(f"rank {rank} R&G batch={batch}: hpsi err {e1:.2e} becp err {e2:.2e}", flush=True)
     h.close()
@@ -72,7 +81,7 @@ def main():
     for rep in range(3):  # repeated calls: epochs keep counting
         out = np.full((m, lda), np.nan + 1j * np.nan)
         hp.h_psi(lda, rk.npw, m, psi_l, out)
-        e1 = np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max() / np.abs(ref).max()
+        e1 = float((np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max(axis=1) / np.abs(ref).max(axis=1)).max())
         ok = ok and e1 < TOL and np.all(out[:, rk.npw:] == 0)
     print(f"rank {rank} R&G p2p exchange: hpsi err {e1:.2e}", flush=True)
     dist.barrier()
@@ -85,7 +94,7 @@ def main():
     out_t = torch.zeros_like(psi_t)
     hb.h_psi_bgrp(inp["lda"], n, m, psi_t, out_t, world, rank)
     torch.cuda.synchronize()
-    e3 = np.abs(out_t.cpu().numpy()[:, :n] - ref[:, :n]).max() / np.abs(ref).max()
+    e3 = colerr(out_t.cpu().numpy()[:, :n], ref[:, :n])
     ok = ok and e3 < TOL
     print(f"rank {rank} band groups: hpsi err {e3:.2e}", flush=True)
     hb.close()

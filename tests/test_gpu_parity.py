@@ -26,7 +26,19 @@ def mods():
 
 
 def relerr(a, b):
-    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+    """Per-column error: max over the columns of the Fortran array (leading numpy index: one band, one projector
+    row of becp, one FFT box) of max|a - b| / max|b| of THAT column, so that a column which is wrong relative to its
+    own scale cannot hide behind a larger one (1-D arrays: one column)."""
+    a = np.asarray(a)
+    b = np.asarray(b)
+    if a.ndim < 2:
+        a, b = a.reshape(1, -1), b.reshape(1, -1)
+    a2, b2 = a.reshape(a.shape[0], -1), b.reshape(b.shape[0], -1)
+    num = np.abs(a2 - b2).max(axis=1)
+    den = np.abs(b2).max(axis=1)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        r = np.where(den > 0, num / den, np.where(num > 0, np.inf, 0.0))
+    return float(r.max()) if r.size else 0.0
 
 
 @pytest.mark.parametrize("shape", [(15, 15, 15), (25, 25, 25), (24, 20, 18), (27, 27, 27), (64, 45, 50), (75, 120, 180)])
@@ -251,7 +263,8 @@ def test_calbec_add_vuspsi(mods, name):
     qe, D, R, torch = mods
     d = D.config_descriptor(name)
     m = 6
-    inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=11, poison=False)
+    # a NON-symmetric deeq: pins the (ih,jh) orientation of deeq(ih,jh,na) against add_vuspsi.f90:151-155
+    inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=11, poison=False, symmetric=False)
     lda, n = inp["lda"], inp["n"]
     h = qe.HPsi()
     h.setup_from(d, inp)
@@ -317,10 +330,10 @@ def test_band_groups_match_full_call(mods):
     h.close()
 
 
-@pytest.mark.parametrize("name,m,nat_used", [("h2o64", 3, 6), ("ausurf112", 2, 4)])
+@pytest.mark.parametrize("name,m,nat_used", [("h2o64", 3, 6), ("h2o64", 8, 3), ("ausurf112", 2, 4), ("si512", 5, 6), ("si512", 16, 2)])
 def test_h_psi_full_grid_reduced_projectors(mods, name, m, nat_used):
-    """BASELINE grids at full size (135^3 Gamma, 125x64x200 k) against the oracle, with a reduced
-    projector count so that the CPU oracle finishes in seconds."""
+    """BASELINE grids at full size (135^3 Gamma, 125x64x200 k, 144^3 Gamma) against the oracle, with a reduced
+    projector count so that the CPU oracle finishes in seconds; m = 5 at Gamma: two band pairs + the odd remainder."""
     qe, D, R, torch = mods
     d = D.config_descriptor(name)
     c = d.extra["config"]
@@ -382,7 +395,7 @@ def test_hermiticity_full_size_ausurf(mods):
 @pytest.mark.parametrize("m,chunk,sub", [(11, 4, 0), (12, 6, 0), (7, 2, 0), (12, 6, 2), (11, 8, 4), (9, 9, 2), (13, 4, 2)])
 def test_h_psi_host_pipeline(mods, name, m, chunk, sub, monkeypatch):
     """Host psi/hpsi through the chunked three-stream pipeline (qeb_set_pipeline): same result as the oracle,
-    pad rows zeroed, becp of all columns kept; pageable numpy arrays get page-locked by the library.
+    pad rows zeroed, becp of all columns kept; pageable numpy arrays (page-locking is explicit, see test_pin_host_explicit).
     sub > 0: the first chunk is copied in sub-chunks with the V_loc passes following them (QEB_PIPE_SUB)."""
     qe, D, R, torch = mods
     if sub:
@@ -395,7 +408,7 @@ def test_h_psi_host_pipeline(mods, name, m, chunk, sub, monkeypatch):
     h = qe.HPsi()
     h.setup_from(d, inp)
     h.set_pipeline(chunk, 2)
-    for _ in range(2):  # second call re-uses the registration of the same arrays
+    for _ in range(2):
         out = np.full((m, lda), np.nan + 1j * np.nan)
         h.h_psi(lda, n, m, inp["psi"], out)
         assert relerr(out, ref) < TOL
@@ -415,7 +428,7 @@ def test_s_psi_after_h_psi(mods, name, m):
     nh = c.get("nh_list") or [c["nh"]] * c["nat"]
     inp = R.synthetic_inputs(d, m, nh, seed=5, poison=False)
     lda, n = inp["lda"], inp["n"]
-    qq = R.synthetic_qq(nh, seed=5)
+    qq = R.synthetic_qq(nh, seed=5, symmetric=(m != 4))  # m = 4: general qq, pins the (ih,jh) orientation
     _, becp_ref = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
     ref = R.s_psi(d, lda, n, m, inp["psi"], becp_ref, inp["vkb"], qq, inp["nh_at"], inp["ofsbeta"])
     h = qe.HPsi()
@@ -684,4 +697,101 @@ def test_edge_cases_empty_and_tight(mods, name):
     one = np.zeros((1, lda), dtype=complex)
     h.h_psi(lda, n, 1, inp["psi"][:1].copy(), one)
     assert relerr(one, ref[:1]) < TOL
+    h.close()
+
+
+@pytest.mark.parametrize("name", ["ortho_small", "si2"])
+def test_projectors_3m_adversarial_scales(mods, name):
+    """The complex projector GEMMs run in the 3-multiplication form (gemm.cu k_calbec3m / k_addvus3m), whose error bound
+    is normwise. Adversarial operands: band columns scaled over 12 decades (1e-6 .. 1e+6) and projectors with
+    |Re vkb| = 1e6 |Im vkb|; every band column and every becp column must still meet 1e-11 relative to ITS OWN scale
+    (per-column relerr), for calbec, add_vuspsi and the whole h_psi."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    c = d.extra["config"]
+    nh = c.get("nh_list") or [c["nh"]] * c["nat"]
+    m = 13
+    inp = R.synthetic_inputs(d, m, nh, seed=31, poison=False, symmetric=False)
+    lda, n = inp["lda"], inp["n"]
+    scale = 10.0 ** np.linspace(-6.0, 6.0, m)
+    psi = inp["psi"] * scale[:, None]
+    vkb = inp["vkb"].copy()
+    vkb = vkb.real * 1.0e3 + 1j * vkb.imag * 1.0e-3  # |Re| = 1e6 |Im|
+    inp["vkb"] = vkb
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    becp_ref = R.calbec_k(n, vkb, psi, m)
+    becp = np.zeros_like(becp_ref)
+    h.calbec(n, None, psi, becp, m, lda=lda)
+    assert relerr(becp, becp_ref) < TOL
+    ps = R.apply_deeq(becp_ref, inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    href = np.zeros((m, lda), complex)
+    R.add_vuspsi_k(n, m, vkb, ps, href)
+    hout = np.zeros((m, lda), complex)
+    h.add_vuspsi(lda, n, m, hout, becp_ref.copy())
+    assert relerr(hout, href) < TOL
+    ref, _ = R.h_psi(d, lda, n, m, psi, inp["vrs"], vkb, inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    out = np.full((m, lda), np.nan + 0j)
+    h.h_psi(lda, n, m, psi, out)
+    assert relerr(out, ref) < TOL
+    # the imaginary parts of the projections, which the 3M form obtains by cancellation (P3 + P1 - P2), on their own scale:
+    # documented bound eps * |Re| / |Im| ~ 1e-16 * 1e6
+    im_err = np.abs(becp.imag - becp_ref.imag).max(axis=1) / np.abs(becp_ref.imag).max(axis=1)
+    assert im_err.max() < 1e-8
+    h.close()
+
+
+def test_band_groups_leave_local_becp(mods):
+    """The shim's band-group sequence (fortran/qeb200_shim.f90 h_psi_qeb): qeb_h_psi_bgrp on this group's column block,
+    then qeb_get_becp for the LOCAL block only - the reference's h_psi_ leaves becp for m_end-m_start+1 columns
+    (PW/src/h_psi.f90:57-62); asking for all m columns is an error."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor("ortho_small")
+    m, nb = 7, 3
+    inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=4, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    _, becp_ref = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    out = np.zeros((m, lda), dtype=complex)
+    for g in range(nb):
+        s, e = qe.divide_all(m, nb, g)
+        h.h_psi_bgrp(lda, n, m, inp["psi"], out, nb, g)
+        assert relerr(h.get_becp(e - s), becp_ref[s:e]) < TOL
+        with pytest.raises(qe.QebError):
+            h.get_becp(m)
+    h.close()
+
+
+def test_pin_host_explicit(mods):
+    """Page-locking of caller arrays is explicit (qeb_pin_host / qeb_unpin_host): pinned and pageable arrays give the
+    same result through the host pipeline; a freed-and-reallocated array is never assumed to be pinned."""
+    qe, D, R, torch = mods
+    d = D.config_descriptor("ortho_small")
+    m = 12
+    inp = R.synthetic_inputs(d, m, [8, 8, 8], seed=12)
+    lda, n = inp["lda"], inp["n"]
+    ref, _ = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    h.set_pipeline(4, 2)
+    psi = inp["psi"].copy()
+    out = np.full((m, lda), np.nan + 0j)
+    h.pin_host(psi)
+    h.pin_host(out)
+    with pytest.raises(qe.QebError):
+        h.pin_host(out)  # already pinned
+    h.h_psi(lda, n, m, psi, out)
+    assert relerr(out, ref) < TOL
+    h.unpin_host(psi)
+    h.unpin_host(out)
+    with pytest.raises(qe.QebError):
+        h.unpin_host(out)
+    del psi, out
+    for _ in range(3):  # fresh pageable arrays (possibly at the old addresses): no stale registration is used
+        p2 = inp["psi"].copy()
+        o2 = np.full((m, lda), np.nan + 0j)
+        h.h_psi(lda, n, m, p2, o2)
+        assert relerr(o2, ref) < TOL
+        del p2, o2
     h.close()
