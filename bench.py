@@ -41,6 +41,9 @@ def parse():
     ap.add_argument("--cpu-sample-bands", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the output check of the timed step")
+    ap.add_argument("--parity-cols", type=int, default=8)
+    ap.add_argument("--no-library-bar", action="store_true", help="skip the cuFFT + cuBLAS bar")
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="--mode rg: stick<->plane exchange as peer-to-peer copy-engine writes (default) or NCCL send/recv")
@@ -103,8 +106,16 @@ class ClockSampler:
 # ---------------------------------------------------------------------------
 # workload
 # ---------------------------------------------------------------------------
-def workload(name: str, seed: int = 0):
-    """descriptor + sizes from the library's own descriptor builder (qeb_desc_*, host setup, not timed)."""
+def workload(name: str, seed: int = 0, impl: str = "ours"):
+    """descriptor + sizes (host setup, not timed). Our arm uses the library's own descriptor builder (qeb_desc_*); the
+    reference arm uses the oracle's (oracle/descriptor.py), so that process never maps libqeb200.so."""
+    if impl == "reference":
+        from oracle import descriptor as OD
+
+        c = dict(OD.CONFIGS[name])
+        c["nh"] = c.get("nh_list") or [c["nh"]] * c["nat"]
+        d = OD.build_descriptor(c["at"], c["alat"], c["ecutwfc"], xk=c["xk"], gamma_only=c["gamma"], ecutrho=c["ecutrho"])
+        return d, c, np.asarray(c["nh"], dtype=np.int32)
     import qe_b200
 
     c = dict(qe_b200.descriptor.WORKLOADS[name])
@@ -113,6 +124,14 @@ def workload(name: str, seed: int = 0):
         xk = xk + 0.01 * seed  # a different k-point per pool
     d = qe_b200.descriptor.Descriptor(c["at"], c["alat"], c["ecutwfc"], c["ecutrho"], xk, c["gamma"])
     return d, c, np.asarray(c["nh"], dtype=np.int32)
+
+
+def config_dict(workload_name, d, npw, nkb, m, n_gpus, mode="pools", exchange="p2p"):
+    """the `config` object: identical keys and values in both arms for the same command line"""
+    par = {"pools": "k-pools", "bgrp": "band-groups", "rg": "R&G slab FFT (" + exchange + " exchange)"}[mode]
+    return {"workload": workload_name, "grid": [int(d.nr1), int(d.nr2), int(d.nr3)], "npw": int(npw), "nkb": int(nkb),
+            "bands_per_step": int(m), "gamma_only": bool(d.gamma_only), "parallelism": f"{par} x{n_gpus}",
+            "l2": "inputs larger than L2 (psi+hpsi+vkb = %.1f GB)" % ((2 * m * npw * 16 + nkb * npw * 16) / 1e9)}
 
 
 def peaks():
@@ -173,13 +192,52 @@ def cpu_reference_run(d, c, nh, m_sample: int, nthreads: int, reps: int = 1):
     return best, ("reference" if use_ref else "port")
 
 
+def parity_check(torch, d, lda, n, m, psi, hpsi, vkb, vrs, deeq, nh, ofs, k=8):
+    """k evenly spaced columns of the step's own output against the checker: the code the reference arm times
+    (oracle: reference C FFT engine for V_loc when built, numpy/OpenBLAS zgemm restating becmod.f90:431-486 and
+    add_vuspsi.f90:140-170). Per-column max|d| / max|ref column|."""
+    from oracle import hpsi_ref as R  # checker only
+
+    cols = np.unique(np.linspace(0, m - 1, min(k, m)).astype(np.int64))
+    if d.gamma_only:  # whole band pairs, as the Gamma path transforms them
+        cols = np.unique(np.concatenate([cols - cols % 2, np.minimum(cols - cols % 2 + 1, m - 1)]))
+    ct = torch.from_numpy(cols).to(psi.device)
+    ps = np.ascontiguousarray(torch.view_as_complex(psi[ct].contiguous()).cpu().numpy())
+    got = torch.view_as_complex(hpsi[ct].contiguous()).cpu().numpy()
+    kk = len(cols)
+    ref = np.zeros((kk, lda), dtype=np.complex128)
+    ref[:, :n] = d.g2kin[None, :n] * ps[:, :n]
+    use_ref = R.ref_lib() is not None
+    if use_ref:
+        R.ref_vloc_psi(d, lda, n, kk, ps, vrs, ref, os.cpu_count() or 1)
+    else:
+        (R.vloc_psi_gamma if d.gamma_only else R.vloc_psi_k)(d, lda, n, kk, ps, vrs, ref)
+    nkb = int(np.sum(nh))
+    if nkb:
+        vk = torch.view_as_complex(vkb).cpu().numpy()
+        if d.gamma_only:
+            becp = R.calbec_gamma(n, vk, ps, kk, d.gstart)
+            R.add_vuspsi_gamma(n, kk, vk, R.apply_deeq(becp, deeq, nh, ofs), ref)
+        else:
+            becp = R.calbec_k(n, vk, ps, kk)
+            R.add_vuspsi_k(n, kk, vk, R.apply_deeq(becp, deeq, nh, ofs), ref)
+        del vk
+    if d.gamma_only and d.gstart == 2:
+        ref[:, 0] = ref[:, 0].real
+    num = np.abs(got[:, :n] - ref[:, :n]).max(axis=1)
+    den = np.abs(ref[:, :n]).max(axis=1)
+    return {"cols": int(kk), "max_rel": float((num / den).max()), "tolerance": 1e-11,
+            "checker": ("reference C FFT engine (oracle/_ref)" if use_ref else "numpy restatement") + " + numpy zgemm",
+            "pad_rows_zero": bool(np.all(got[:, n:] == 0))}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    d, c, nh = workload(args.workload)
+    d, c, nh = workload(args.workload, impl="reference")
     cores = os.cpu_count() or 1
-    m_s = args.cpu_sample_bands or min(int(c.get("nbnd", 128)), 800)
+    m_s = args.cpu_sample_bands or args.bands or int(c.get("nbnd", 128))
     times = []
     kind = "port"
     for i in range(args.warmup + args.steps):
@@ -192,14 +250,18 @@ def run_reference(args):
         "impl": "reference", "metric": "h_psi band-applications/s", "value": val, "unit": "band-applications/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "grid": [d.nr1, d.nr2, d.nr3], "npw": d.npw, "nkb": int(nh.sum()),
-                   "bands_per_step": m_s, "note": "bounded sample of the m-band workload"},
+        "config": config_dict(args.workload, d, d.npw, int(nh.sum()), m_s, args.gpus, args.mode, args.exchange),
         "cpu_baseline": {"value": val, "unit": "band-applications/s", "cores": cores, "kind": kind,
                          "sample": f"{m_s} bands of the {args.workload} h_psi: V_loc via the reference C FFT engine "
                                    f"(OpenMP over bands), projectors via OpenBLAS zgemm"},
         "e2e": {"value": val, "unit": "band-applications/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    # this arm must not map the product library (only oracle/_ref + numpy/OpenBLAS)
+    try:
+        line["maps_libqeb200"] = "libqeb200" in open("/proc/self/maps").read()
+    except OSError:
+        line["maps_libqeb200"] = None
     emit(line)
 
 
@@ -265,13 +327,15 @@ def run_ours(args):
         if world > 1:
             h.nccl_init(qe_b200.COMM_RG)
         h.set_kpoint(n, lda, None if d.gamma_only else rk.igk, rk.g2kin, vkb, nkb, rk.gstart)
-        h.set_vloc(rng.uniform(-1.0, 0.0, d.nr1 * d.nr2 * int(d.nr3p[rank])))
+        vrs = rng.uniform(-1.0, 0.0, d.nr1 * d.nr2 * int(d.nr3p[rank]))
+        h.set_vloc(vrs)
         if world > 1 and args.exchange == "p2p":
             h.p2p_setup()
     else:
         h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
         h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
-        h.set_vloc(rng.uniform(-1.0, 0.0, d.nnr))
+        vrs = rng.uniform(-1.0, 0.0, d.nnr)
+        h.set_vloc(vrs)
     h.set_nonlocal(nh, ofs, deeq)
     h.set_async(True)
     st = h.stats()
@@ -348,10 +412,14 @@ def run_ours(args):
     # FP64 tensor (DMMA) ceiling: 148 SMs x 64 FMA/clk x SM clock; cuBLAS DGEMM timed beside it as the empirical ceiling
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
     fp64_peak = torch.cuda.get_device_properties(dev).multi_processor_count * 64 * 2 * sm_mhz * 1e6 / 1e12
-    a64 = torch.randn((4096, 4096), device=dev, dtype=torch.float64)
-    ms_dgemm = time_section(lambda: torch.matmul(a64, a64), reps=5)
-    dgemm_tf = 2 * 4096 ** 3 / (ms_dgemm * 1e-3) / 1e12
-    del a64
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import library_bar as LB  # bench infrastructure (cuFFT / cuBLAS through torch), not part of libqeb200
+
+    fp64 = LB.fp64_ceiling(torch, dev) if rank == 0 else {"dgemm_8192_tflops": float("nan"), "zgemm_8192_tflops": float("nan")}
+    fp64["dmma_peak_tflops"] = fp64_peak
+    fp64["how"] = ("cuBLAS DGEMM / ZGEMM 8192^3 (torch.matmul, 3 reps, CUDA events) in this run; dmma_peak = 148 SMs x 64 "
+                   "FP64 FMA/clk x the SM clock sampled during the timed region")
+    dgemm_tf = fp64["dgemm_8192_tflops"]
     roofline_gemm = None
     if ms_nl > 0:
         roofline_gemm = {"bound": "tensor", "achieved": gemm_tf, "peak": fp64_peak, "unit": "TFLOP/s",
@@ -361,17 +429,20 @@ def run_ours(args):
                          "complex_product": "3M (executed flops = 0.75 x algorithmic)" if three_m else "4M / real",
                          "ms_projector_section": ms_nl,
                          "peak_source": "148 SMs x 64 FP64 FMA/clk x %.0f MHz (FP64 tensor = FP64 vector rate on B200); "
-                                        "cuBLAS DGEMM 4096^3 in this run: %.1f TFLOP/s" % (sm_mhz, dgemm_tf)}
+                                        "cuBLAS DGEMM 8192^3 in this run: %.1f TFLOP/s, ZGEMM %.1f" % (sm_mhz, dgemm_tf, fp64["zgemm_8192_tflops"])}
     kpb = h.vloc_kernels_per_batch()  # 3 with the fused plane kernel (zinv, plane, zfwd), else 5
-    # DRAM traffic of the same launches from the committed `ncu --set full` capture (dram__bytes_read+write, per launch)
-    if roofline_gemm and args.workload == "ausurf112" and mm == 800 and three_m:
-        roofline_gemm["traffic"] = 9.337911e9 + 0.174068e9 + 5.360086e9 + 1.208370e9
-        roofline_gemm["traffic_source"] = ("profiles/r1q_gemm_m800_ncu_full.csv: k_calbec3m 9.34+0.17 GB, k_addvus3m 5.36+1.21 GB "
-                                           "per launch at m=800 (algorithmic operands: vkb 3.08 GB + psi/hpsi 1.22 GB each, per kernel)")
-    if args.workload == "ausurf112" and kpb == 3:
-        roofline_vloc["traffic"] = (33.77e6 + 51.11e6 + 108.42e6 + 45.59e6 + 129.37e6 + 18.71e6) / 20 * mm
-        roofline_vloc["traffic_source"] = ("profiles/r1zu_vloc_b20_ncu_full.csv: zinv 84.9 MB, plane 154.0 MB, zfwd 148.1 MB per "
-                                           "batch of 20 boxes (per-box figures scaled to the bands of the section)")
+    # DRAM traffic (dram__bytes_read + write per launch) of the same kernels from the committed `ncu --set full` summary
+    # profiles/traffic.json, written by tools/ncu_summary.py from the capture of the commit it names
+    tj = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tj):
+        tr = json.load(open(tj)).get(args.workload, {})
+        if roofline_gemm and three_m and tr.get("gemm_bytes_per_band"):
+            roofline_gemm["traffic"] = tr["gemm_bytes_per_band"] * mm
+            roofline_gemm["traffic_source"] = tr.get("gemm_source")
+        key = "vloc_bytes_per_box_plane" if kpb == 3 else "vloc_bytes_per_box_5k"
+        if tr.get(key):
+            roofline_vloc["traffic"] = tr[key] * boxes
+            roofline_vloc["traffic_source"] = tr.get("vloc_source")
     # `roofline` = the kernel family with the largest share of the step
     roofline = roofline_gemm if (roofline_gemm and ms_nl >= ms_vloc) else roofline_vloc
     launches_step = nbatches * kpb + (4 if nkb else 0) + 1
@@ -389,7 +460,7 @@ def run_ours(args):
         h.h_psi(lda, n, mm, pn, hn)
         barrier()
         t0 = time.perf_counter()
-        reps = max(2, min(args.steps, 3))
+        reps = max(5, args.steps)
         for _ in range(reps):
             h.h_psi(lda, n, mm, pn, hn)
         torch.cuda.synchronize()
@@ -403,18 +474,46 @@ def run_ours(args):
                "ms_per_step": dt * 1e3}
         h.set_async(True)
 
+    # ---- output check of the timed step: a sample of columns against the checker (the reference arm's code) ----
+    parity = None
+    lib_bar = None
+    if rank == 0 and not rg and not args.no_parity:
+        step()  # the timed step once more (hpsi was overwritten by the section timings)
+        torch.cuda.synchronize()
+        parity = parity_check(torch, d, lda, n, mm, psi, hpsi, vkb, vrs, deeq, nh, ofs, k=args.parity_cols)
+    # ---- the same-box GPU library bar: cuFFT full-box Z2Z + cuBLAS ZGEMM composed as the reference's GPU path ----
+    if rank == 0 and world == 1 and not rg and not args.no_library_bar:
+        try:
+            lib_bar = LB.measure(torch, d, psi[:mm], vkb, vrs, deeq, nh, ofs, reps=2)
+            Hl = lib_bar.pop("hpsi")
+            ours = torch.view_as_complex(hpsi[:mm])
+            if d.gamma_only and d.gstart == 2:
+                Hl[:, 0] = Hl[:, 0].real
+            num = (Hl[:, :n] - ours[:, :n]).abs().amax(dim=1)
+            den = Hl[:, :n].abs().amax(dim=1)
+            lib_bar["max_rel_vs_ours"] = float((num / den).max().item())  # per column, all bands of the step
+            lib_bar["ours_over_library"] = value / lib_bar["value"]
+            lib_bar["vloc_ours_over_library"] = lib_bar["vloc_us_per_band"] / (1e3 * ms_vloc / mm)
+            lib_bar["projectors_ours_over_library"] = (lib_bar["projectors_us_per_band"] / (1e3 * ms_nl / mm)) if ms_nl else None
+            del Hl
+        except Exception as exc:  # noqa: BLE001  (e.g. out of memory on a shared box): reported, never fatal
+            lib_bar = {"unavailable": repr(exc)[:200]}
+        torch.cuda.empty_cache()
+
     if rank == 0:
         line = {
             "metric": "h_psi band-applications/s", "value": value, "unit": "band-applications/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak" if pools else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload, "grid": [d.nr1, d.nr2, d.nr3], "npw": n, "bands_per_step": m_total,
-                       "nkb": nkb, "gamma_only": bool(d.gamma_only), "parallelism": {"pools": "k-pools", "bgrp": "band-groups", "rg": "R&G slab FFT (" + args.exchange + " exchange)"}[args.mode] + f" x{world}",
-                       "vloc_batch_boxes": st["batch"], "l2": "inputs larger than L2 (psi+hpsi+vkb = %.1f GB)" % ((2 * m_total * lda * 16 + nkb * lda * 16) / 1e9)},
+            "config": config_dict(args.workload, d, d.npw, nkb, m_total, world, args.mode, args.exchange),
+            "tuning": {"vloc_batch_boxes": st["batch"], "vloc_kernels_per_batch": kpb},
+            "fp64_ceiling": fp64,
             "roofline": roofline,
             "roofline_vloc": roofline_vloc,
             "roofline_projectors": roofline_gemm,
             "sections_ms": {"vloc": ms_vloc, "projectors": ms_nl},
+            "parity_check": parity,
+            "gpu_library_bar": lib_bar,
             "gpu_launches": launches_step * args.steps,
             "clocks": clocks,
         }

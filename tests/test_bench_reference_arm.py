@@ -30,6 +30,9 @@ def test_reference_arm_line():
     assert j["cpu_baseline"]["kind"] in ("reference", "port") and j["cpu_baseline"]["cores"] >= 1
     assert j["e2e"]["h2d_bytes_per_step"] == 0 and j["e2e"]["d2h_bytes_per_step"] == 0
     assert j["gpu_launches"] == 0
+    assert j["maps_libqeb200"] is False  # the reference arm never loads the product library
+    # both arms print the same `config` keys for the same command line (the driver compares the dicts)
+    assert sorted(j["config"]) == ["bands_per_step", "gamma_only", "grid", "l2", "nkb", "npw", "parallelism", "workload"]
 
 
 def test_reference_arm_other_ranks_are_silent():
