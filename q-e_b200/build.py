@@ -15,7 +15,8 @@ OUT = os.path.join(HERE, "libqeb200.so")
 BUILD = os.path.join(HERE, "build")
 SOURCES = ["context.cu", "vloc.cu", "gemm.cu", "fullfft.cu", "distfft.cu", "nccl_glue.cu", "descriptor.cu", "uspp.cu", "davidson.cu"] + [
     f"vloc_fast_{n}.cu" for n in (15, 25, 27, 64, 125, 135, 144, 200, "200b")] + [
-    f"vloc_plane_{a}_{b}.cu" for a, b in ((125, 64), (25, 25), (27, 27), (15, 15), (64, 64), ("125b", 64), ("125b", "64b"))]
+    f"vloc_plane_{a}_{b}.cu" for a, b in ((125, 64), (25, 25), (27, 27), (15, 15), (64, 64), ("125b", 64), ("125b", "64b"))] + [
+    f"vloc_planew_{a}_{b}.cu" for a, b in ((125, 64), (25, 25), (27, 27), (15, 15), (64, 64))]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--use_fast_math=false",
@@ -73,29 +74,52 @@ def build_variant(tag: str, defines: list[str], verbose: bool = True) -> str:
     return out
 
 
+def _deps(path, seen=None):
+    """the file plus every `#include "..."` it reaches (resolved against its own directory and csrc/)"""
+    import re
+
+    seen = set() if seen is None else seen
+    path = os.path.normpath(path)
+    if path in seen or not os.path.exists(path):
+        return seen
+    seen.add(path)
+    for inc in re.findall(r'^\s*#\s*include\s+"([^"]+)"', open(path).read(), flags=re.M):
+        for base in (os.path.dirname(path), CSRC):
+            cand = os.path.normpath(os.path.join(base, inc))
+            if os.path.exists(cand):
+                _deps(cand, seen)
+                break
+    return seen
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
+    """Incremental: an object is recompiled when its source or a header it includes (transitively) changed."""
     srcs = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
-    deps.append(os.path.join(os.path.dirname(HERE), "include", "qeb200.h"))
-    stamp = os.path.join(BUILD, "stamp")
-    dig = _digest(deps)
-    if not force and os.path.exists(OUT) and os.path.exists(stamp) and open(stamp).read() == dig:
-        return OUT
     nvcc = _nvcc()
     os.makedirs(BUILD, exist_ok=True)
-    objs = []
-    with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
-        futs = [ex.submit(_compile, nvcc, s, os.path.join(BUILD, s.replace(".cu", ".o"))) for s in srcs]
+    todo, objs, digs = [], [], {}
+    for s in srcs:
+        obj = os.path.join(BUILD, s.replace(".cu", ".o"))
+        dig = _digest(_deps(os.path.join(CSRC, s)))
+        stamp = obj + ".stamp"
+        objs.append(obj)
+        digs[obj] = dig
+        if force or not os.path.exists(obj) or not os.path.exists(stamp) or open(stamp).read() != dig:
+            todo.append((s, obj))
+    if not todo and os.path.exists(OUT) and os.path.getmtime(OUT) >= max(os.path.getmtime(o) for o in objs):
+        return OUT
+    with cf.ThreadPoolExecutor(max_workers=min(8, max(1, len(todo)))) as ex:
+        futs = [ex.submit(_compile, nvcc, s, obj) for s, obj in todo]
         for f in futs:
-            objs.append(f.result())
-    libs = []
-    cmd = [nvcc, "-shared", "-o", OUT, *objs, "-gencode", "arch=compute_100a,code=sm_100a", *libs]
+            f.result()
+    for _, obj in todo:
+        open(obj + ".stamp", "w").write(digs[obj])
+    cmd = [nvcc, "-shared", "-o", OUT, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    open(stamp, "w").write(dig)
     if verbose:
-        print("built", OUT)
+        print("built", OUT, f"({len(todo)} of {len(srcs)} objects recompiled)")
     return OUT
 
 

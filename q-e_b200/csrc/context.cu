@@ -1400,8 +1400,7 @@ static int h_psi_cols(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx
                       bool kinetic, int col0 = 0, int m_total = -1)
 {
     int rc;
-    if (kinetic && lda > n)
-        QEB_CUDA(c, cudaMemset2DAsync(hpsi_d + n, (size_t)lda * 16, 0, (size_t)(lda - n) * 16, m, c->stream));
+    if (kinetic && lda > n) QEB_CUDA(c, launch_zero_pad_rows(hpsi_d, lda, n, m, c->stream));
     if (do_vloc && (rc = run_vloc(c, lda, n, m, psi_d, hpsi_d, kinetic))) return rc;
     if (do_nl && c->nkb > 0 && !c->vkb_d) QEB_FAIL(c, 56, "h_psi: no vkb in the context (qeb_set_kpoint or qeb_init_us_2)");
     if (do_nl && c->nkb > 0) {
@@ -1692,7 +1691,7 @@ int qeb_h_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
         QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
         hpsi_d = (cplx*)c->hpsi_stage.p;
     }
-    if (lda > n) QEB_CUDA(c, cudaMemset2DAsync(hpsi_d + n, (size_t)lda * 16, 0, (size_t)(lda - n) * 16, 2 * m, c->stream));
+    if (lda > n) QEB_CUDA(c, launch_zero_pad_rows(hpsi_d, lda, n, 2 * m, c->stream));
     if ((rc = run_vloc_nc(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true))) return rc;
     if (nkb > 0) {
         if ((rc = ensure_becp(c, nkb, 2 * m))) return rc;

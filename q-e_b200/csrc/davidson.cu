@@ -57,4 +57,25 @@ cudaError_t launch_col_dot(int n, int m, const cplx* a, int lda, const cplx* b, 
     return cudaGetLastError();
 }
 
+// rows n..lda-1 of m columns = 0 (h_psi.f90:141). A kernel, not cudaMemset2D: the pitched region of a 2-D memset that
+// starts n elements into the first column ends n elements past the last one, i.e. outside an exactly sized array.
+__global__ void k_zero_pad_rows(cplx* __restrict__ a, int lda, int n, int m)
+{
+    const int w = lda - n;
+    const size_t tot = (size_t)w * m;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < tot; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t k = e / w;
+        a[k * lda + n + (e - k * w)] = mk(0.0, 0.0);
+    }
+}
+
+cudaError_t launch_zero_pad_rows(cplx* a, int lda, int n, int m, cudaStream_t st)
+{
+    if (m <= 0 || lda <= n) return cudaSuccess;
+    const size_t tot = (size_t)(lda - n) * m;
+    const int blocks = (int)((tot + 255) / 256 < 1184 ? (tot + 255) / 256 : 1184);
+    k_zero_pad_rows<<<blocks, 256, 0, st>>>(a, lda, n, m);
+    return cudaGetLastError();
+}
+
 }  // namespace qeb

@@ -11,4 +11,6 @@ cudaError_t launch_g_psi(int lda, int n, int m, cplx* psi, const double* e, cons
 // 2*sum - [gstart==2] Re a(1,k) Re b(1,k) (regterg.f90:340-345). Fixed reduction order: deterministic.
 cudaError_t launch_col_dot(int n, int m, const cplx* a, int lda, const cplx* b, int ldb, int gamma, int gstart,
                            double* out, cudaStream_t st);
+// a(n+1:lda, 1:m) = 0: the pad rows h_psi zeroes (PW/src/h_psi.f90:141)
+cudaError_t launch_zero_pad_rows(cplx* a, int lda, int n, int m, cudaStream_t st);
 }  // namespace qeb

@@ -4,6 +4,7 @@
 #include "vloc.h"
 #include "vloc_fast_inst.cuh"
 #include "vloc_plane_inst.cuh"
+#include "vloc_planew_inst.cuh"
 
 namespace qeb {
 
@@ -141,6 +142,22 @@ static bool launch_x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, 
 QEB_FOR_PLANES(X)
 #undef X
 
+// warp-local form of the plane kernel (vloc_planew.cuh): preferred when instantiated for the plans (QEB_PLANEW=0: off)
+#define QEB_FOR_PLANEWS(X) X(SP125, SP64, 512) X(SP25, SP25, 512) X(SP27, SP27, 512) X(SP15, SP15, 512) X(SP64, SP64, 512)
+#define X(PX, PY, MT) extern template struct PlaneWLaunch<PX, PY, MT>;
+QEB_FOR_PLANEWS(X)
+#undef X
+
+static bool launch_planew(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
+{
+    if (!env_int("QEB_PLANEW", 1)) return false;
+#define X(PX, PY, MT) \
+    if (PlaneWLaunch<PX, PY, MT>::run(t, nboxes, cfg.num_sms, cfg.max_smem, st)) return true;
+    QEB_FOR_PLANEWS(X)
+#undef X
+    return false;
+}
+
 bool vloc_plane_available(const VlocTables& t)
 {
 #define X(PX, PY, MT) \
@@ -155,6 +172,7 @@ static bool launch_plane(const VlocTables& t, const VlocLaunchCfg& cfg, int nbox
     if (!t.pl_v || cfg.smem_plane == 0 || cfg.smem_plane > cfg.max_smem || env_int("QEB_GENERIC", 0) ||
         !env_int("QEB_PLANE", 1))
         return false;
+    if (launch_planew(t, cfg, nboxes, st)) return true;
 #define X(PX, PY, MT) \
     if (PlaneLaunch<PX, PY, MT>::run(t, nboxes, cfg.num_sms, cfg.max_smem, st)) return true;
     QEB_FOR_PLANES(X)
@@ -211,6 +229,10 @@ cudaError_t vloc_init_attrs(size_t max_smem)
 #define X(PX, PY, MT) \
     if ((e = PlaneLaunch<PX, PY, MT>::attrs(s))) return e;
     QEB_FOR_PLANES(X)
+#undef X
+#define X(PX, PY, MT) \
+    if ((e = PlaneWLaunch<PX, PY, MT>::attrs(s))) return e;
+    QEB_FOR_PLANEWS(X)
 #undef X
     return cudaGetLastError();
 }

@@ -124,8 +124,8 @@ def test_vloc_fast_phases_full_baseline_grids(emul, name, m):
     emul.emul_set_fast(0)
 
 
-def _run_plane_emul(emul, name, m, nthr, batch):
-    emul.emul_set_fast(2)
+def _run_plane_emul(emul, name, m, nthr, batch, mode=2):
+    emul.emul_set_fast(mode)
     try:
         d = D.config_descriptor(name)
         inp = R.synthetic_inputs(d, m, [4, 4], seed=2)
@@ -150,6 +150,20 @@ def test_plane_phases_match_oracle(emul, name, nthr):
     """the fused plane pass (vloc_plane.cuh: y | x*V*x | y on one shared-memory plane) on the small grids with an
     instantiated (x,y) plan pair, with fewer, as many and more warps than line groups"""
     _run_plane_emul(emul, name, 3, nthr, 2)
+
+
+@pytest.mark.parametrize("name", ["si2_small", "si2_small_gamma", "si2", "al4"])
+@pytest.mark.parametrize("nthr", [32, 96, 512])
+def test_planew_steps_match_oracle(emul, name, nthr):
+    """the warp-local plane pass (vloc_planew.cuh: a line belongs to a team of lanes of one warp) on the small grids"""
+    _run_plane_emul(emul, name, 3, nthr, 2, mode=3)
+
+
+@pytest.mark.parametrize("nthr", [512, 352, 64])
+def test_planew_steps_ausurf_grid(emul, nthr):
+    """BASELINE AUSURF112 grid through the warp-local plane pass: 125 = 25*5 with teams of 5 (6 rows per warp),
+    64 = 8*8 with teams of 8 (4 columns per warp), shifted plane layout (ldp 133); 16, 11 and 2 warps"""
+    _run_plane_emul(emul, "ausurf112", 1, nthr, 1, mode=3)
 
 
 def test_plane_phases_ausurf_grid(emul):

@@ -7,6 +7,7 @@
 #   dist       multi-GPU parity tests (needs gpurun --gpus N)
 #   scale      bench.py under torchrun on all GPUs of the box (k-pools + strong-scaling modes)
 #   bench:<workload>  bench.py --workload <workload> (si2 al4 h2o64 si512)
+#   sweep      tools/vloc_sweep.py with SWEEP_ENV / SWEEP_BATCHES / SWEEP_BANDS
 # Every stage runs under its own timeout; a failed stage does not stop the round. ncu stages run only after the same
 # command has exited 0 without ncu.
 T=${1:-rX}; shift
@@ -57,6 +58,9 @@ for S in "$@"; do
           CMD="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N"; fi
         timeout 1200 $CMD --no-cpu-baseline > $O/${T}_n${N}.json 2> $O/${T}_n${N}.err; echo "scale N=$N rc=$?"; cut -c1-250 $O/${T}_n${N}.json
       done;;
+    sweep)  # V_loc parameter sweep: SWEEP_ENV='A=1;A=2,B=3' SWEEP_BATCHES=20,30 SWEEP_BANDS=400 [SWEEP_WORKLOAD=ausurf112]
+      timeout 900 python tools/vloc_sweep.py --workload ${SWEEP_WORKLOAD:-ausurf112} --bands ${SWEEP_BANDS:-400} \
+        --batches ${SWEEP_BATCHES:-20} --env "${SWEEP_ENV}" > $O/${T}_sweep.log 2>&1; echo "sweep rc=$?"; cat $O/${T}_sweep.log;;
     *) echo "unknown stage $S";;
   esac
 done
