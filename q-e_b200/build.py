@@ -16,7 +16,7 @@ BUILD = os.path.join(HERE, "build")
 SOURCES = ["context.cu", "vloc.cu", "gemm.cu", "fullfft.cu", "distfft.cu", "nccl_glue.cu", "descriptor.cu", "uspp.cu", "davidson.cu"] + [
     f"vloc_fast_{n}.cu" for n in (15, 25, 27, 64, 125, 135, 144, 200, "200b")] + [
     f"vloc_plane_{a}_{b}.cu" for a, b in ((125, 64), (25, 25), (27, 27), (15, 15), (64, 64), ("125b", 64), ("125b", "64b"))] + [
-    f"vloc_planew_{a}_{b}.cu" for a, b in ((125, 64), (25, 25), (27, 27), (15, 15), (64, 64))]
+    f"vloc_plane2_{a}_{b}.cu" for a, b in ((125, 64), ("125b", 64), (25, 25), (27, 27), (15, 15), (64, 64))]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--use_fast_math=false",

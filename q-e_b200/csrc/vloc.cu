@@ -4,7 +4,7 @@
 #include "vloc.h"
 #include "vloc_fast_inst.cuh"
 #include "vloc_plane_inst.cuh"
-#include "vloc_planew_inst.cuh"
+#include "vloc_plane2_inst.cuh"
 
 namespace qeb {
 
@@ -142,18 +142,20 @@ static bool launch_x(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, 
 QEB_FOR_PLANES(X)
 #undef X
 
-// warp-local form of the plane kernel (vloc_planew.cuh): preferred when instantiated for the plans (QEB_PLANEW=0: off)
-#define QEB_FOR_PLANEWS(X) X(SP125, SP64, 512) X(SP25, SP25, 512) X(SP27, SP27, 512) X(SP15, SP15, 512) X(SP64, SP64, 512)
-#define X(PX, PY, MT) extern template struct PlaneWLaunch<PX, PY, MT>;
-QEB_FOR_PLANEWS(X)
+// second form of the plane kernel (vloc_plane2.cuh: compile-time phases, persistent over the (box, z) list, bulk
+// asynchronous stick rows); preferred when instantiated for the plans (QEB_PLANE2=0: the first form)
+#define QEB_FOR_PLANE2S(X) \
+    X(SP125, SP64, 512) X(SP125b, SP64, 800) X(SP25, SP25, 512) X(SP27, SP27, 512) X(SP15, SP15, 512) X(SP64, SP64, 512)
+#define X(PX, PY, NT) extern template struct Plane2Launch<PX, PY, NT>;
+QEB_FOR_PLANE2S(X)
 #undef X
 
-static bool launch_planew(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
+static bool launch_plane2(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
 {
-    if (!env_int("QEB_PLANEW", 1)) return false;
-#define X(PX, PY, MT) \
-    if (PlaneWLaunch<PX, PY, MT>::run(t, nboxes, cfg.num_sms, cfg.max_smem, st)) return true;
-    QEB_FOR_PLANEWS(X)
+    if (!env_int("QEB_PLANE2", 1)) return false;
+#define X(PX, PY, NT) \
+    if (Plane2Launch<PX, PY, NT>::run(t, nboxes, cfg.num_sms, cfg.max_smem, st)) return true;
+    QEB_FOR_PLANE2S(X)
 #undef X
     return false;
 }
@@ -172,7 +174,7 @@ static bool launch_plane(const VlocTables& t, const VlocLaunchCfg& cfg, int nbox
     if (!t.pl_v || cfg.smem_plane == 0 || cfg.smem_plane > cfg.max_smem || env_int("QEB_GENERIC", 0) ||
         !env_int("QEB_PLANE", 1))
         return false;
-    if (launch_planew(t, cfg, nboxes, st)) return true;
+    if (launch_plane2(t, cfg, nboxes, st)) return true;
 #define X(PX, PY, MT) \
     if (PlaneLaunch<PX, PY, MT>::run(t, nboxes, cfg.num_sms, cfg.max_smem, st)) return true;
     QEB_FOR_PLANES(X)
@@ -230,9 +232,9 @@ cudaError_t vloc_init_attrs(size_t max_smem)
     if ((e = PlaneLaunch<PX, PY, MT>::attrs(s))) return e;
     QEB_FOR_PLANES(X)
 #undef X
-#define X(PX, PY, MT) \
-    if ((e = PlaneWLaunch<PX, PY, MT>::attrs(s))) return e;
-    QEB_FOR_PLANEWS(X)
+#define X(PX, PY, NT) \
+    if ((e = Plane2Launch<PX, PY, NT>::attrs(s))) return e;
+    QEB_FOR_PLANE2S(X)
 #undef X
     return cudaGetLastError();
 }

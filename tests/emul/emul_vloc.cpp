@@ -9,7 +9,7 @@
 #include "fullfft_kernels.cuh"
 #include "vloc_fast.cuh"
 #include "vloc_plane.cuh"
-#include "vloc_planew.cuh"
+#include "vloc_plane2.cuh"
 
 using namespace qeb;
 
@@ -94,14 +94,14 @@ static pfn pick_plane(const VlocTables& t, int* nph)
     return nullptr;
 }
 
-// warp-local form of the plane pass (vloc_planew.cuh): g_fast == 3. Steps are executed for every thread in turn, which
-// is a legal interleaving of both the __syncwarp()- and the __syncthreads()-separated steps of the kernel.
-typedef void (*pwfn)(int, int, int, const VlocTables&, int, cplx*, const cplx*, cplx*, const PlaneSm&, int);
-#define QEB_FOR_PLANEWS(X) X(SP125, SP64) X(SP25, SP25) X(SP27, SP27) X(SP15, SP15) X(SP64, SP64)
-static pwfn pick_planew(const VlocTables& t, int* ns, int* ldp, int* maxsh)
+// second form of the plane pass (vloc_plane2.cuh): g_fast == 3. Same stick rows in / out; tables as the kernel stages them.
+typedef void (*p2fn)(int, int, int, const VlocTables&, int, cplx*, const cplx*, cplx*, const Plane2Sm&);
+typedef void (*p2mask)(const int*, int*);
+#define QEB_FOR_PLANE2S(X) X(SP125, SP64) X(SP125b, SP64) X(SP25, SP25) X(SP27, SP27) X(SP15, SP15) X(SP64, SP64)
+static p2fn pick_plane2(const VlocTables& t, int* nph, int* ldp, int* nmask, p2mask* mk)
 {
-#define X(PX, PY) if (PX::matches(t.px) && PY::matches(t.py)) { *ns = planew_nsteps<PX, PY>(); *ldp = planew_ldp<PX, PY>(t.nr1, t.nr2); *maxsh = PlwShift<PY>::max_shift(t.nr2); return (pwfn)planew_step<PX, PY>; }
-    QEB_FOR_PLANEWS(X)
+#define X(PX, PY) if (PX::matches(t.px) && PY::matches(t.py)) { *nph = Plane2<PX, PY>::NPH; *ldp = Plane2<PX, PY>::LDP; *nmask = Plane2<PX, PY>::XMASK; *mk = (p2mask)plane2_xmask<PX>; return (p2fn)plane2_phase<PX, PY>; }
+    QEB_FOR_PLANE2S(X)
 #undef X
     return nullptr;
 }
@@ -142,9 +142,10 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
     int plane_nph = 0;
     pfn plane_fn = g_fast == 2 ? pick_plane(t, &plane_nph) : nullptr;
     if (g_fast == 2 && !plane_fn) return 2;  // no instantiated plane kernel for this grid
-    int pw_ns = 0, pw_ldp = 0, pw_maxsh = 0;
-    pwfn planew_fn = g_fast == 3 ? pick_planew(t, &pw_ns, &pw_ldp, &pw_maxsh) : nullptr;
-    if (g_fast == 3 && !planew_fn) return 2;
+    int p2_nph = 0, p2_ldp = 0, p2_nmask = 0;
+    p2mask p2_mk = nullptr;
+    p2fn plane2_fn = g_fast == 3 ? pick_plane2(t, &p2_nph, &p2_ldp, &p2_nmask, &p2_mk) : nullptr;
+    if (g_fast == 3 && !plane2_fn) return 2;
     // potential: permuted by rev_x and scaled
     std::vector<double> vp((size_t)nr1 * t.npos);
     const double sc = 1.0 / ((double)nr1 * nr2 * nr3);
@@ -178,17 +179,19 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
                 for (int ph = 0; ph < zinv_nphase(t); ++ph)
                     for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
             }
-            if (planew_fn) {
-                const PlaneSm psm{t.px.tw, t.py.tw, t.pl_ymapT, t.xmap, t.pl_xact};
-                std::vector<cplx> P((size_t)nr2 * pw_ldp + pw_maxsh), sin(H.nst), sout(H.nst);
+            if (plane2_fn) {
+                std::vector<int> xmask(p2_nmask);
+                p2_mk(t.xmap, xmask.data());
+                const Plane2Sm psm{t.px.tw, t.py.tw, t.pl_ymapT, t.pl_xact, xmask.data()};
+                std::vector<cplx> P((size_t)nr2 * p2_ldp), sin(H.nst), sout(H.nst);
                 const int pthr = ((nthr + 31) / 32) * 32;  // whole warps
                 for (int z = 0; z < nr3; ++z) {
                     for (auto& x : P) x = nanv;
                     for (auto& x : sout) x = nanv;
                     cplx* row = t.g1 + (size_t)box * t.g1_box + (size_t)z * t.g1_zs;
                     for (int i = 0; i < H.nst; ++i) sin[i] = row[i];
-                    for (int st = 0; st < pw_ns; ++st)
-                        for (int tid = 0; tid < pthr; ++tid) planew_fn(st, tid, pthr, t, z, P.data(), sin.data(), sout.data(), psm, pw_ldp);
+                    for (int ph = 0; ph < p2_nph; ++ph)
+                        for (int tid = 0; tid < pthr; ++tid) plane2_fn(ph, tid, pthr, t, z, P.data(), sin.data(), sout.data(), psm);
                     for (int i = 0; i < H.nst; ++i) row[i] = sout[i];
                 }
             } else if (plane_fn) {

@@ -154,15 +154,22 @@ def test_plane_phases_match_oracle(emul, name, nthr):
 
 @pytest.mark.parametrize("name", ["si2_small", "si2_small_gamma", "si2", "al4"])
 @pytest.mark.parametrize("nthr", [32, 96, 512])
-def test_planew_steps_match_oracle(emul, name, nthr):
-    """the warp-local plane pass (vloc_planew.cuh: a line belongs to a team of lanes of one warp) on the small grids"""
+def test_plane2_phases_match_oracle(emul, name, nthr):
+    """the second form of the plane pass (vloc_plane2.cuh: compile-time phases, flat task list dealt to the warps,
+    column masks) on the small grids"""
     _run_plane_emul(emul, name, 3, nthr, 2, mode=3)
 
 
 @pytest.mark.parametrize("nthr", [512, 352, 64])
-def test_planew_steps_ausurf_grid(emul, nthr):
-    """BASELINE AUSURF112 grid through the warp-local plane pass: 125 = 25*5 with teams of 5 (6 rows per warp),
-    64 = 8*8 with teams of 8 (4 columns per warp), shifted plane layout (ldp 133); 16, 11 and 2 warps"""
+def test_plane2_phases_ausurf_grid(emul, nthr):
+    """BASELINE AUSURF112 grid through the plane2 pass with the default plans (125 = 25*5, 64 = 8*8); 16, 11, 2 warps"""
+    _run_plane_emul(emul, "ausurf112", 1, nthr, 1, mode=3)
+
+
+@pytest.mark.parametrize("nthr", [800, 1024, 96])
+def test_plane2_phases_ausurf_grid_555(emul, monkeypatch, nthr):
+    """AUSURF112 grid through the plane2 pass with the low-register x plan 125 = 5*5*5 (the kernel's 25 warps; 32; 3)"""
+    monkeypatch.setenv("QEB_XPLAN", "5,5,5")
     _run_plane_emul(emul, "ausurf112", 1, nthr, 1, mode=3)
 
 

@@ -30,19 +30,20 @@ vrs = rng.uniform(-1, 0, d.nnr)
 s = torch.cuda.Stream()
 torch.cuda.set_stream(s)
 for batch in [int(x) for x in a.batches.split(",")]:
-    h = qe_b200.HPsi(stream=s.cuda_stream, batch=batch)
-    h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
-    h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, None, 0, d.gstart)
-    h.set_vloc(vrs)
-    h.set_async(True)
-    f = h.vloc_psi_gamma if d.gamma_only else h.vloc_psi_k
     for setting in (a.env.split(";") if a.env else [""]):
         keys = []
         for kv in setting.split(","):
             if "=" in kv:
-                k, v = kv.split("=")
-                os.environ[k] = v
+                k, v = kv.split("=", 1)
+                os.environ[k] = v.replace("+", ",")  # radix lists are written 5+5+5 inside a setting
                 keys.append(k)
+        # the context is created per setting: the plan overrides (QEB_[XYZ]PLAN) are read by qeb_set_grid
+        h = qe_b200.HPsi(stream=s.cuda_stream, batch=batch)
+        h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
+        h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, None, 0, d.gstart)
+        h.set_vloc(vrs)
+        h.set_async(True)
+        f = h.vloc_psi_gamma if d.gamma_only else h.vloc_psi_k
         for _ in range(2):
             f(lda, n, m, psi, None, hpsi)
         torch.cuda.synchronize()
@@ -55,7 +56,7 @@ for batch in [int(x) for x in a.batches.split(",")]:
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / reps / m
         st = h.stats()
-        print(f"batch={batch:3d} {setting:40s} {us:8.2f} us/band  {st['vloc_bytes_per_band'] / us / 1e3:8.1f} GB/s")
+        print(f"batch={batch:3d} {setting:40s} {us:8.2f} us/band  {st['vloc_bytes_per_band'] / us / 1e3:8.1f} GB/s", flush=True)
+        h.close()
         for k in keys:
             del os.environ[k]
-    h.close()
