@@ -51,37 +51,44 @@ QEB_HD cplx stw(const cplx* tw, int j, double sgn) { return mk(tw[j].x, sgn * tw
 // One radix pass P of plan PL over the tile; see fft_core.cuh::fft_pass_r for the math.
 // PF: software-pipelined input (the loads of the next butterfly are issued before the current one is computed) for
 // passes whose source is global memory, where each warp otherwise exposes one L2/DRAM round trip per butterfly
-template <class PL, int P, bool DIT, bool FUSE2, bool PF = false, class Src, class Dst, class Mid>
-QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double sgn, Src& src, Dst& dst, Mid& mid)
+// SUB: butterflies per warp. Tiles of at most 16 lines (the z passes at nr3 = 200: 51 KB per 16-stick tile) would leave half
+// of every warp idle with one line per lane; with SUB = 2 lanes 0-15 and 16-31 carry the same 16 lines of two consecutive
+// butterfly indices, so the FP64 instructions run with full warps and a warp keeps twice the loads in flight.
+template <class PL, int P, bool DIT, bool FUSE2, bool PF = false, int SUB = 1, class Src, class Dst, class Mid>
+QEB_HD void spass(int warp, int nwarps, int lane_, int nl, const cplx* tw, double sgn, Src& src, Dst& dst, Mid& mid)
 {
     constexpr int R = PL::r(P);
     constexpr int L = PL::L(P);
     constexpr int A = L / R;
     constexpr int NB = PL::N / L;
     constexpr int NJ = PL::N / R;
+    constexpr int TLN = QEB_TL / SUB;
+    const int sub = SUB > 1 ? lane_ / TLN : 0;
+    const int lane = SUB > 1 ? lane_ - sub * TLN : lane_;  // the line
+    const int j0 = warp * SUB + sub, jstep = nwarps * SUB;
     if (lane >= nl) return;
     double fnext[FUSE2 ? R : 1];
     cplx vnext[PF ? R : 1];
-    if (FUSE2 && QEB_VPF && warp < NJ) {  // pointwise factor of the first butterfly (software pipeline, see below)
-        const int blk = warp / A;
-        const int base = blk * L + (warp - blk * A);
+    if (FUSE2 && QEB_VPF && j0 < NJ) {  // pointwise factor of the first butterfly (software pipeline, see below)
+        const int blk = j0 / A;
+        const int base = blk * L + (j0 - blk * A);
 #pragma unroll
         for (int d = 0; d < R; ++d) fnext[d] = mid.fetch(lane, base + d);
     }
-    for (int j = warp; j < NJ; j += nwarps) {
+    for (int j = j0; j < NJ; j += jstep) {
         const int blk = j / A;
         const int a = j - blk * A;
         const int base = blk * L + a;
         cplx v[R];
         double f[FUSE2 ? R : 1];
         if (PF) {
-            if (j == warp) {
+            if (j == j0) {
 #pragma unroll
                 for (int b = 0; b < R; ++b) vnext[b] = src.load(lane, base + A * b);
             }
 #pragma unroll
             for (int b = 0; b < R; ++b) v[b] = vnext[b];
-            const int jn = j + nwarps;
+            const int jn = j + jstep;
             if (jn < NJ) {
                 const int blkn = jn / A;
                 const int basen = blkn * L + (jn - blkn * A);
@@ -93,7 +100,7 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
                       // its L2 latency hides behind this butterfly
 #pragma unroll
             for (int d = 0; d < R; ++d) f[d] = QEB_VPF ? fnext[d] : mid.fetch(lane, base + d);
-            const int jn = j + nwarps;
+            const int jn = j + jstep;
             if (QEB_VPF && jn < NJ) {
                 const int blkn = jn / A;
                 const int basen = blkn * L + (jn - blkn * A);
@@ -125,108 +132,6 @@ QEB_HD void spass(int warp, int nwarps, int lane, int nl, const cplx* tw, double
         for (int d = 0; d < R; ++d) dst.store(lane, base + A * d, v[d]);
     }
 }
-
-// The same radix pass for ONE line handled by a team of threads of one warp (vloc_planew.cuh): this thread computes the
-// butterflies j = j0, j0 + jstep, ... (cnt of them) of its line; the team covers j = 0 .. N/R - 1 between two
-// __syncwarp()s. Src / Dst address the thread's own line (their `lane` argument is passed as 0).
-template <class PL, int P, bool DIT, bool FUSE2, class Src, class Dst, class Mid>
-QEB_HD void spass_t(int j0, int jstep, int cnt, const cplx* tw, double sgn, Src& src, Dst& dst, Mid& mid)
-{
-    constexpr int R = PL::r(P);
-    constexpr int L = PL::L(P);
-    constexpr int A = L / R;
-    constexpr int NB = PL::N / L;
-    double fnext[FUSE2 ? R : 1];
-    if (FUSE2 && QEB_VPF && cnt > 0) {
-        const int blk = j0 / A;
-        const int base = blk * L + (j0 - blk * A);
-#pragma unroll
-        for (int d = 0; d < R; ++d) fnext[d] = mid.fetch(0, base + d);
-    }
-    for (int jj = 0; jj < cnt; ++jj) {
-        const int j = j0 + jj * jstep;
-        const int blk = j / A;
-        const int a = j - blk * A;
-        const int base = blk * L + a;
-        cplx v[R];
-        double f[FUSE2 ? R : 1];
-        if (FUSE2) {
-#pragma unroll
-            for (int d = 0; d < R; ++d) f[d] = QEB_VPF ? fnext[d] : mid.fetch(0, base + d);
-            if (QEB_VPF && jj + 1 < cnt) {
-                const int jn = j + jstep;
-                const int blkn = jn / A;
-                const int basen = blkn * L + (jn - blkn * A);
-#pragma unroll
-                for (int d = 0; d < R; ++d) fnext[d] = mid.fetch(0, basen + d);
-            }
-        }
-#pragma unroll
-        for (int b = 0; b < R; ++b) v[b] = src.load(0, base + A * b);
-        if (DIT && A > 1) {
-            const int st = a * NB;
-#pragma unroll
-            for (int b = 1; b < R; ++b) v[b] = cmul(v[b], stw(tw, st * b, sgn));
-        }
-        Bfly<R>::run(v, sgn);
-        if (FUSE2) {
-#pragma unroll
-            for (int d = 0; d < R; ++d) v[d] = scal(v[d], f[d]);
-            Bfly<R>::run(v, -sgn);
-        }
-        if (!DIT && !FUSE2 && A > 1) {
-            const int st = a * NB;
-#pragma unroll
-            for (int d = 1; d < R; ++d) v[d] = cmul(v[d], stw(tw, st * d, sgn));
-        }
-#pragma unroll
-        for (int d = 0; d < R; ++d) dst.store(0, base + A * d, v[d]);
-    }
-}
-
-// team size for a plan: the largest common divisor of the butterfly counts N/R_p of all passes that fits a warp
-template <class PL>
-struct STeam {
-    QEB_HD static constexpr int gcd(int a, int b) { return b == 0 ? a : gcd(b, a % b); }
-    QEB_HD static constexpr int common()
-    {
-        int g = 0;
-        for (int p = 0; p < PL::NP; ++p) g = gcd(g, PL::N / PL::r(p));
-        return g;
-    }
-    QEB_HD static constexpr int pick()
-    {
-        int best = 1;
-        for (int t = 1; t <= 32; ++t)
-            if (common() % t == 0) best = t;
-        return best;
-    }
-    static constexpr int T = pick();      // threads per line
-    static constexpr int LPW = 32 / T;    // lines per warp
-};
-
-// pass `p` (runtime, warp-uniform) of plan PL for team member `tm` of STeam<PL>::T: butterflies are dealt to the team
-// in contiguous runs in the pass with A == 1 (whole blocks: consecutive members touch consecutive 16-byte units) and
-// strided otherwise
-template <class PL, bool DIT, bool FUSE2, int P = 0>
-struct SPassSelT {
-    template <class Src, class Dst, class Mid>
-    QEB_HD static void run(int p, int tm, const cplx* tw, double sgn, Src& src, Dst& dst, Mid& mid)
-    {
-        if (p == P) {
-            constexpr int T = STeam<PL>::T;
-            constexpr int NJ = PL::N / PL::r(P);
-            constexpr int cnt = NJ / T;
-            constexpr bool contig = (PL::L(P) / PL::r(P)) == 1;
-            if (contig)
-                spass_t<PL, P, DIT, FUSE2>(tm * cnt, 1, cnt, tw, sgn, src, dst, mid);
-            else
-                spass_t<PL, P, DIT, FUSE2>(tm, T, cnt, tw, sgn, src, dst, mid);
-        } else if constexpr (P + 1 < PL::NP) {
-            SPassSelT<PL, DIT, FUSE2, P + 1>::run(p, tm, tw, sgn, src, dst, mid);
-        }
-    }
-};
 
 // Spinor form of the fused middle pass: last DIF pass (A = 1, no twiddles) of BOTH components of a spinor, the 2x2
 // pointwise mix (mix.apply(lane, pos, up, dn)), first DIT pass of both. 2*R complex values live per thread.
@@ -300,16 +205,16 @@ __device__ __forceinline__ void spass_spinx(int warp, int nwarps, int lane, doub
 #endif
 
 // run pass number `p` (runtime, warp-uniform) of plan PL: expands to a switch over the NP passes
-template <class PL, bool DIT, bool FUSE2, int P = 0, bool PF = false>
+template <class PL, bool DIT, bool FUSE2, int P = 0, bool PF = false, int SUB = 1>
 struct SPassSel {
     template <class Src, class Dst, class Mid>
     QEB_HD static void run(int p, int warp, int nwarps, int lane, int nl, const cplx* tw, double sgn, Src& src, Dst& dst,
                            Mid& mid)
     {
         if (p == P)
-            spass<PL, P, DIT, FUSE2, PF>(warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
+            spass<PL, P, DIT, FUSE2, PF, SUB>(warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
         else if constexpr (P + 1 < PL::NP)
-            SPassSel<PL, DIT, FUSE2, P + 1, PF>::run(p, warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
+            SPassSel<PL, DIT, FUSE2, P + 1, PF, SUB>::run(p, warp, nwarps, lane, nl, tw, sgn, src, dst, mid);
     }
 };
 

@@ -7,10 +7,18 @@
 // stage it in shared memory). Executed on the CPU by tests/emul like the
 // generic phases.
 #pragma once
+#include <stdlib.h>
 #include "fft_static.cuh"
 #include "vloc_kernels.cuh"
 
 namespace qeb {
+
+// butterflies per warp in the fast z passes for tiles of TZ sticks (fft_static.cuh::spass SUB); QEB_ZSUB=2 switches it on: measured slower at AUSURF112 (V_loc 21.1 -> 23.6 us/band, profiles/r2f_sweep.log: the per-lane butterfly index costs the warp-uniform addressing and spills)
+inline int vloc_zsub(int TZ)
+{
+    const char* e = getenv("QEB_ZSUB");
+    return (TZ <= QEB_TL / 2 && e && atoi(e) == 2) ? 2 : 1;
+}
 
 // software-pipelined loads in the global-source (first DIT) passes: measured SLOWER (zfwd 66 -> 81 us per 15 boxes at
 // AUSURF112, Si512 25.8 -> 28.8 us/band: the extra live butterfly spills at the 128-register budget); off by default
@@ -40,7 +48,7 @@ struct LaneTile {  // S[pos*ld + lane]
 // ---------------------------------------------------------------------------
 // P1 fast: scatter + z inverse
 // ---------------------------------------------------------------------------
-template <class PL>
+template <class PL, int SUB = 1>
 QEB_HD void zinv_fast_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem,
                                 const FastTabs& ft)
 {
@@ -55,16 +63,20 @@ QEB_HD void zinv_fast_phase(int ph, int tid, int nthr, const VlocTables& t, cons
     NoMid nm;
     if (p == PL::NP - 1) {
         G1Dst d{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.g1_zs};
-        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, d, nm);
+        SPassSel<PL, false, false, 0, false, SUB>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, d, nm);
     } else {
-        SPassSel<PL, false, false>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, s, nm);
+        SPassSel<PL, false, false, 0, false, SUB>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, s, nm);
     }
 }
 
 // ---------------------------------------------------------------------------
 // P5 fast: z forward + gather
 // ---------------------------------------------------------------------------
-template <class PL>
+// STAGE: the G1 slab of the group is already in the tile (zfwd_stage: S[irev[z]*TZ + line], all of it requested at once
+// with cp.async before phase 0), so the first DIT pass reads shared memory. Without it the first pass loads G1 itself:
+// every warp then exposes one DRAM round trip per butterfly it owns (ncu source page, profiles/r2e_*: 18 % of the
+// kernel's samples on the first use of those loads).
+template <class PL, int SUB = 1, bool STAGE = false>
 QEB_HD void zfwd_fast_phase(int ph, int tid, int nthr, const VlocTables& t, const VlocIO& io, int grp, int box, cplx* smem,
                                 const FastTabs& ft)
 {
@@ -78,11 +90,32 @@ QEB_HD void zfwd_fast_phase(int ph, int tid, int nthr, const VlocTables& t, cons
     const int nl = t.grp_nl[grp];
     LaneTile s{smem, t.TZ};
     NoMid nm;
-    if (ph == 0) {
+    if (ph == 0 && !STAGE) {
         G1Dst g{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.g1_zs};
-        SPassSel<PL, true, false, 0, QEB_GPF>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, g, s, nm);
+        SPassSel<PL, true, false, 0, QEB_GPF, SUB>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, g, s, nm);
     } else {
-        SPassSel<PL, true, false>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, s, s, nm);
+        SPassSel<PL, true, false, 0, false, SUB>::run(p, warp, nwarps, lane, nl, ft.tw, -1.0, s, s, nm);
+    }
+}
+
+// the slab copy of the STAGE form: element (z, line) of the group -> S[irev[z]*TZ + line] (irev: inverse of ft.rev).
+// On the device the copies are cp.async (the kernel waits for all of them once); the CPU emulation copies.
+QEB_HD void zfwd_stage(int tid, int nthr, const VlocTables& t, int grp, int box, cplx* smem, const int* irev, const int* sticks)
+{
+    const int TZ = t.TZ, nl = t.grp_nl[grp];
+    const cplx* g = t.g1 + (size_t)box * t.g1_box;
+    const int tot = t.nr3 * TZ;
+    for (int i = tid; i < tot; i += nthr) {
+        const int z = i / TZ, l = i - z * TZ;
+        if (l >= nl) continue;
+        cplx* dst = smem + irev[z] * TZ + l;
+        const cplx* src = g + (size_t)z * t.g1_zs + sticks[l];
+#if defined(__CUDA_ARCH__)
+        const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(src));
+#else
+        *dst = *src;
+#endif
     }
 }
 

@@ -14,7 +14,7 @@ namespace qeb {
 #define QEB_SMEM extern __shared__ __align__(16) unsigned char smem_raw[]; cplx* smem = reinterpret_cast<cplx*>(smem_raw)
 
 // ---- fast variants: compile-time plan of the pass direction, warp-mapped work ----
-template <class PL>
+template <class PL, int SUB>
 __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_zinv_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
 {
     QEB_SMEM;
@@ -26,23 +26,34 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_zinv_f(const __gri
     const FastTabs ft{twS, nullptr, tabS, tabS + PL::N};
     __syncthreads();
     for (int ph = 0; ph < 2 + PL::NP; ++ph) {
-        zinv_fast_phase<PL>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
+        zinv_fast_phase<PL, SUB>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
         __syncthreads();
     }
 }
-template <class PL>
-__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_zfwd_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
+template <class PL, int SUB, bool STAGE>
+__global__ void __launch_bounds__(STAGE ? 256 : QEB_FAST_MAXTHREADS, STAGE ? 2 : 1)
+    k_vloc_zfwd_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
 {
     QEB_SMEM;
     cplx* twS = smem + ((size_t)t.nr3 * t.TZ);
     int* tabS = reinterpret_cast<int*>(twS + PL::N);
+    int* irevS = tabS + PL::N + QEB_TL;
+    for (int i = threadIdx.x; i < PL::N; i += blockDim.x) {
+        const int r = t.pz.rev[i];
+        tabS[i] = r;
+        if (STAGE) irevS[r] = i;
+    }
     for (int i = threadIdx.x; i < PL::N; i += blockDim.x) twS[i] = t.pz.tw[i];
-    for (int i = threadIdx.x; i < PL::N; i += blockDim.x) tabS[i] = t.pz.rev[i];
     for (int i = threadIdx.x; i < t.TZ; i += blockDim.x) tabS[PL::N + i] = t.grp_stick[(size_t)blockIdx.x * t.TZ + i];
     const FastTabs ft{twS, nullptr, tabS, tabS + PL::N};
     __syncthreads();
+    if (STAGE) {
+        zfwd_stage(threadIdx.x, blockDim.x, t, blockIdx.x, blockIdx.y, smem, irevS, ft.sticks);
+        asm volatile("cp.async.wait_all;\n" ::: "memory");
+        __syncthreads();
+    }
     for (int ph = 0; ph < 1 + PL::NP; ++ph) {
-        zfwd_fast_phase<PL>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
+        zfwd_fast_phase<PL, SUB, STAGE>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
         __syncthreads();
     }
 }
@@ -218,7 +229,7 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xacc_f(const __gri
 
 // warps per CTA for a plan: the count in [lo,hi] that wastes the fewest warp-rounds over the passes
 template <class PL>
-static int pick_warps(int lo, int hi)
+static int pick_warps(int lo, int hi, int sub = 1)
 {
     int best = lo;
     double beff = -1.0;
@@ -227,7 +238,7 @@ static int pick_warps(int lo, int hi)
         for (int p = 0; p < PL::NP; ++p) {
             const int nj = PL::N / PL::r(p);
             used += nj;
-            tot += (long)((nj + nw - 1) / nw) * nw;
+            tot += (long)((nj + nw * sub - 1) / (nw * sub)) * (nw * sub);
         }
         const double eff = (double)used / (double)tot;
         if (eff > beff - 1e-9) {  // ties: more warps
@@ -259,8 +270,11 @@ struct FastLaunch {
 template <class PL>
 void FastLaunch<PL>::attrs(int s)
 {
-    cudaFuncSetAttribute(k_vloc_zinv_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
-    cudaFuncSetAttribute(k_vloc_zfwd_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zinv_f<PL, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zinv_f<PL, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_yinv_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_yfwd_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_xfus_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
@@ -272,11 +286,25 @@ template <class PL>
 void FastLaunch<PL>::z(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
 {
     const dim3 grid(t.ngrp, nboxes);
-    const int nw = env_int("QEB_NWZ", pick_warps<PL>(4, 10));
-    if (inv)
-        k_vloc_zinv_f<PL><<<grid, nw * 32, cfg.smem_z + PL::N * 20 + 4 * QEB_TL + 16, st>>>(t, io);
-    else
-        k_vloc_zfwd_f<PL><<<grid, nw * 32, cfg.smem_z + PL::N * 20 + 4 * QEB_TL + 16, st>>>(t, io);
+    // tiles of <= 16 sticks: two butterflies per warp (fft_static.cuh::spass SUB = 2) when QEB_ZSUB=2
+    const bool sub2 = vloc_zsub(t.TZ) == 2;
+    const bool stage = !inv && env_int("QEB_ZSTAGE", 1) != 0;
+    int nw = env_int("QEB_NWZ", pick_warps<PL>(4, stage ? 8 : 10, sub2 ? 2 : 1));
+    if (stage && nw > 8) nw = 8;
+    const size_t smem = cfg.smem_z + PL::N * 24 + 4 * QEB_TL + 16;
+    if (inv) {
+        if (sub2)
+            k_vloc_zinv_f<PL, 2><<<grid, nw * 32, smem, st>>>(t, io);
+        else
+            k_vloc_zinv_f<PL, 1><<<grid, nw * 32, smem, st>>>(t, io);
+    } else {
+        if (stage)
+            k_vloc_zfwd_f<PL, 1, true><<<grid, nw * 32, smem, st>>>(t, io);
+        else if (sub2)
+            k_vloc_zfwd_f<PL, 2, false><<<grid, nw * 32, smem, st>>>(t, io);
+        else
+            k_vloc_zfwd_f<PL, 1, false><<<grid, nw * 32, smem, st>>>(t, io);
+    }
 }
 template <class PL>
 void FastLaunch<PL>::y(bool inv, const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)

@@ -55,6 +55,8 @@ QEB_HD void plane2_xmask(const int* xmap, int* xmask)
 }
 
 // ---- one butterfly of a y pass for lane's column -------------------------------------------------------------------
+// ymapT holds, per (y, xa), the stick id or - for a column position without a stick - the index of a spare element
+// behind the row (stin: a zero; stout: a sink), so the pruned first / last pass needs no test per element.
 template <class PL, int P, bool DIT, int LDP>
 QEB_HD void p2_bfly_y(int j, bool active, int lane_col, int nxw, const cplx* tw, cplx* col, const cplx* stin, cplx* stout,
                       const int* ymapT)
@@ -65,16 +67,14 @@ QEB_HD void p2_bfly_y(int j, bool active, int lane_col, int nxw, const cplx* tw,
     const int blk = j / A, a = j - blk * A, base = blk * L + a;
     cplx v[R];
     if (!DIT && P == 0) {  // natural y in: the plane's sticks, zero elsewhere (pruned input)
-        const int* ym = ymapT + (size_t)base * nxw + lane_col;
+        const int* ym = ymapT + (base * nxw + lane_col);
+        const int ys = A * nxw;
 #pragma unroll
-        for (int b = 0; b < R; ++b) {
-            const int s = ym[(size_t)(A * b) * nxw];
-            v[b] = s >= 0 ? stin[s] : mk(0.0, 0.0);
-        }
+        for (int b = 0; b < R; ++b) v[b] = stin[ym[b * ys]];
     } else {
-        const cplx* c = col + (size_t)base * LDP;
+        const cplx* c = col + base * LDP;
 #pragma unroll
-        for (int b = 0; b < R; ++b) v[b] = c[(size_t)(A * b) * LDP];
+        for (int b = 0; b < R; ++b) v[b] = c[(A * b) * LDP];
     }
     if (DIT && A > 1) {
         const int st = a * NB;
@@ -88,16 +88,14 @@ QEB_HD void p2_bfly_y(int j, bool active, int lane_col, int nxw, const cplx* tw,
         for (int d = 1; d < R; ++d) v[d] = cmul(v[d], stw(tw, st * d, sgn));
     }
     if (DIT && P == 0) {  // natural y out: keep the stick rows
-        const int* ym = ymapT + (size_t)base * nxw + lane_col;
+        const int* ym = ymapT + (base * nxw + lane_col);
+        const int ys = A * nxw;
 #pragma unroll
-        for (int d = 0; d < R; ++d) {
-            const int s = ym[(size_t)(A * d) * nxw];
-            if (s >= 0) stout[s] = v[d];
-        }
+        for (int d = 0; d < R; ++d) stout[ym[d * ys]] = v[d];
     } else {
-        cplx* c = col + (size_t)base * LDP;
+        cplx* c = col + base * LDP;
 #pragma unroll
-        for (int d = 0; d < R; ++d) c[(size_t)(A * d) * LDP] = v[d];
+        for (int d = 0; d < R; ++d) c[(A * d) * LDP] = v[d];
     }
 }
 
@@ -117,9 +115,9 @@ QEB_HD void p2_bfly_x(int j, bool active, const cplx* tw, cplx* row, const int* 
 #pragma unroll
         for (int d = 0; d < R; ++d) {
 #if defined(__CUDA_ARCH__)
-            f[d] = __ldg(vrow + (size_t)(base + d) * NY);
+            f[d] = __ldg(vrow + (base + d) * NY);
 #else
-            f[d] = vrow[(size_t)(base + d) * NY];
+            f[d] = vrow[(base + d) * NY];
 #endif
         }
     }
@@ -176,7 +174,7 @@ struct Plane2 {
 struct Plane2Sm {  // shared-memory tables of the plane2 kernel (host arrays in the CPU emulation)
     const cplx* twx;
     const cplx* twy;
-    const int* ymapT;  // [nr2*nxw] stick id at (y, xa) or -1
+    const int* ymapT;  // [nr2*nxw] stick id at (y, xa), or the spare element nst (plane2_ymap) where there is none
     const int* xact;   // [nxw]     xa -> x
     const int* xmask;  // [Plane2::XMASK]
 };
@@ -221,7 +219,7 @@ QEB_HD void plane2_phase_c(int tid, int nthr, int nxw, const P2Roles& ro, cplx* 
         for (int t = tid >> 5; t < NJ * NG; t += nw) {
             const int y = g * 32 + lane;
             const bool active = y < G::NY;
-            cplx* row = P + (size_t)(active ? y : 0) * LDP;
+            cplx* row = P + (active ? y : 0) * LDP;
             p2_bfly_x<PLX, p, KIND, G::NY>(j, active, sm.twx, row, sm.xmask, vz + (active ? y : 0));
             g += k.dg;
             j += k.dj;
@@ -264,12 +262,16 @@ QEB_HD void plane2_phase(int ph, int tid, int nthr, const VlocTables& t, int z, 
     Plane2Sel<PLX, PLY>::run(ph, tid, nthr, t.nxw, ro, P, stin, stout, sm, t.pl_v + (size_t)z * t.nr1 * t.nr2);
 }
 
-// shared-memory bytes: plane, two stick rows, twiddles, ymapT, xact, xmask, two mbarriers
+// stick rows carry spare elements behind the nst sticks (index nst: the zero of stin / the sink of stout)
+QEB_HD int plane2_row_elems(int nst) { return (nst + 1 + 3) & ~3; }
+QEB_HD int plane2_ymap(int s, int nst) { return s >= 0 ? s : nst; }
+
+// shared-memory bytes: plane, two stick rows, twiddles, ymapT, xact, xmask, mbarrier
 template <class PLX, class PLY>
 QEB_HD size_t plane2_smem_bytes(int nst, int nxw)
 {
     using G = Plane2<PLX, PLY>;
-    const size_t nstp = ((size_t)nst + 3) & ~(size_t)3;
+    const size_t nstp = (size_t)plane2_row_elems(nst);
     const size_t c16 = (size_t)G::NY * G::LDP + 2 * nstp + G::NX + G::NY;
     const size_t i4 = (size_t)G::NY * nxw + nxw + G::XMASK;
     return c16 * 16 + ((i4 * 4 + 15) & ~(size_t)15) + 32;

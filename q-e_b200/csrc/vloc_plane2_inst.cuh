@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(NT, 1) k_vloc_plane2(const __grid_constant__ V
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cplx* P = reinterpret_cast<cplx*>(smem_raw);
     const int nst = t.nst, nxw = t.nxw;
-    const int nstp = (nst + 3) & ~3;
+    const int nstp = plane2_row_elems(nst);
     cplx* stin = P + (size_t)G::NY * G::LDP;
     cplx* stout = stin + nstp;
     cplx* twx = stout + nstp;
@@ -96,18 +96,17 @@ __global__ void __launch_bounds__(NT, 1) k_vloc_plane2(const __grid_constant__ V
         reinterpret_cast<unsigned long long*>((reinterpret_cast<uintptr_t>(xmaskS + G::XMASK) + 15) & ~(uintptr_t)15);
     const int tid = threadIdx.x, nthr = blockDim.x;
     const long long Q = (long long)t.nr3 * nboxes;
-    const long long q0 = Q * blockIdx.x / gridDim.x, q1 = Q * (blockIdx.x + 1) / gridDim.x;
+    const int q0 = (int)(Q * blockIdx.x / gridDim.x), q1 = (int)(Q * (blockIdx.x + 1) / gridDim.x);
     if (q0 >= q1) return;
+    int z = q0 % t.nr3, box = q0 / t.nr3;
     const unsigned row_bytes = (unsigned)nst * 16u;
     if (tid == 0) p2_mbar_init(bar, 1);
     __syncthreads();
-    if (tid == 0) {
-        const int z = (int)(q0 % t.nr3), box = (int)(q0 / t.nr3);
-        p2_bulk_load(stin, t.g1 + (size_t)box * t.g1_box + (size_t)z * t.g1_zs, row_bytes, bar);
-    }
+    if (tid == 0) p2_bulk_load(stin, t.g1 + (size_t)box * t.g1_box + (size_t)z * t.g1_zs, row_bytes, bar);
     for (int i = tid; i < G::NX; i += nthr) twx[i] = t.px.tw[i];
     for (int i = tid; i < G::NY; i += nthr) twy[i] = t.py.tw[i];
-    for (int i = tid; i < G::NY * nxw; i += nthr) ymapT[i] = t.pl_ymapT[i];
+    for (int i = tid; i < G::NY * nxw; i += nthr) ymapT[i] = plane2_ymap(t.pl_ymapT[i], nst);
+    if (tid == 0) stin[nst] = mk(0.0, 0.0);  // the zero every stick-less column position reads (bulk loads stop before it)
     for (int i = tid; i < nxw; i += nthr) xactS[i] = t.pl_xact[i];
     if (tid < G::XMASK) {
         constexpr int R = PLX::r(0), A = G::XMASK;
@@ -122,23 +121,25 @@ __global__ void __launch_bounds__(NT, 1) k_vloc_plane2(const __grid_constant__ V
     unsigned parity = 0;
     __syncthreads();
 #pragma unroll 1
-    for (long long q = q0; q < q1; ++q) {
-        const int z = (int)(q % t.nr3), box = (int)(q / t.nr3);
-        P2Ctx cx;
-        cx.next_row = nullptr;
-        if (q + 1 < q1) {
-            const int zn = (int)((q + 1) % t.nr3), bn = (int)((q + 1) / t.nr3);
-            cx.next_row = t.g1 + (size_t)bn * t.g1_box + (size_t)zn * t.g1_zs;
+    for (int q = q0; q < q1; ++q) {
+        int zn = z + 1, bn = box;
+        if (zn == t.nr3) {
+            zn = 0;
+            ++bn;
         }
+        P2Ctx cx;
+        cx.next_row = q + 1 < q1 ? t.g1 + (size_t)bn * t.g1_box + (size_t)zn * t.g1_zs : nullptr;
         cx.stin_w = stin;
         cx.bar = bar;
         cx.row_bytes = row_bytes;
         p2_mbar_wait(bar, parity);
         parity ^= 1u;
-        P2Run<PLX, PLY, 0>::go(tid, nthr, nxw, ro, P, stin, stout, sm, t.pl_v + (size_t)z * G::NX * G::NY, cx);
+        P2Run<PLX, PLY, 0>::go(tid, nthr, nxw, ro, P, stin, stout, sm, t.pl_v + (size_t)z * (G::NX * G::NY), cx);
         p2_fence_async();  // the generic-proxy writes of stout become visible to the bulk store
         __syncthreads();
         if (tid == 0) p2_bulk_store(t.g1 + (size_t)box * t.g1_box + (size_t)z * t.g1_zs, stout, row_bytes);
+        z = zn;
+        box = bn;
     }
     if (tid == 0) p2_bulk_wait_all();
 }

@@ -131,6 +131,9 @@ def allgather_columns(hpsi, m: int, group=None):
     return hpsi
 
 
+_CALLER_STREAMS = set()  # stream handles contexts were created on (HPsi(stream=...))
+
+
 def _ptr(a):
     """address of a numpy array / torch tensor / None / int"""
     if a is None:
@@ -144,6 +147,15 @@ def _ptr(a):
     if hasattr(a, "data_ptr"):
         if not a.is_contiguous():
             raise QebError("tensor must be contiguous")
+        if getattr(a, "is_cuda", False):
+            # The library's own streams are non-blocking: work the caller queued on torch's current stream (the fill or
+            # the upload of this very tensor) is ordered before the library call here, as a Fortran caller's
+            # synchronous host code is. A context created ON the caller's stream needs no such wait.
+            import torch
+
+            cs = torch.cuda.current_stream(a.device)
+            if cs.cuda_stream not in _CALLER_STREAMS:
+                cs.synchronize()
         return ctypes.c_void_p(a.data_ptr())
     raise QebError(f"unsupported array type {type(a)}")
 
@@ -163,6 +175,8 @@ class HPsi:
         if rc:
             self._h = None
             raise QebError(f"qeb_create failed (code {rc}): a CUDA device is required, there is no CPU fallback")
+        if stream:
+            _CALLER_STREAMS.add(int(stream))
         self.gamma_only = False
         self._keep = {}
         if batch:

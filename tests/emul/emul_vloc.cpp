@@ -61,12 +61,38 @@ static void zfwd_g(int ph, int tid, int nthr, const VlocTables& t, const VlocIO&
 static void yinv_g(int ph, int tid, int nthr, const VlocTables& t, int z, int x, int b, cplx* s, const FastTabs&) { yinv_phase(ph, tid, nthr, t, z, x, b, s); }
 static void yfwd_g(int ph, int tid, int nthr, const VlocTables& t, int z, int x, int b, cplx* s, const FastTabs&) { yfwd_phase(ph, tid, nthr, t, z, x, b, s); }
 static void xfus_g(int ph, int tid, int nthr, const VlocTables& t, int tile, int b, cplx* s, const FastTabs&) { xfus_phase(ph, tid, nthr, t, tile, b, s); }
-static zfn pick_z(const FftPlan& pl, bool inv)
+static zfn pick_z(const FftPlan& pl, bool inv, int TZ = 32)
 {
-#define X(PL) if (g_fast && PL::matches(pl)) return inv ? (zfn)zinv_fast_phase<PL> : (zfn)zfwd_fast_phase<PL>;
+    // the half-warp mapping of the kernels (two butterflies per warp for tiles of <= 16 sticks) when they would use it
+#define X(PL) if (g_fast && PL::matches(pl) && vloc_zsub(TZ) == 2) return inv ? (zfn)zinv_fast_phase<PL, 2> : (zfn)zfwd_fast_phase<PL, 2>; \
+              if (g_fast && PL::matches(pl)) return inv ? (zfn)zinv_fast_phase<PL, 1> : (zfn)zfwd_fast_phase<PL, 1>;
     QEB_FOR_PLANS(X)
 #undef X
     return inv ? zinv_g : zfwd_g;
+}
+// staged z-forward kernel form (vloc_fast.cuh::zfwd_stage + the STAGE phases): what the fast launcher runs unless QEB_ZSTAGE=0
+static zfn pick_zfwd_staged(const FftPlan& pl)
+{
+    const char* e = getenv("QEB_ZSTAGE");
+    if (!g_fast || (e && atoi(e) == 0)) return nullptr;
+#define X(PL) if (PL::matches(pl)) return (zfn)zfwd_fast_phase<PL, 1, true>;
+    QEB_FOR_PLANS(X)
+#undef X
+    return nullptr;
+}
+static void run_zfwd_group(const VlocTables& t, const VlocIO& io, int g, int box, cplx* smem, int nthr)
+{
+    const FastTabs ft{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ};
+    if (zfn f = pick_zfwd_staged(t.pz)) {
+        std::vector<int> irev(t.nr3);
+        for (int i = 0; i < t.nr3; ++i) irev[t.pz.rev[i]] = i;
+        for (int tid = 0; tid < nthr; ++tid) zfwd_stage(tid, nthr, t, g, box, smem, irev.data(), ft.sticks);
+        for (int ph = 0; ph < zfwd_nphase(t); ++ph)
+            for (int tid = 0; tid < nthr; ++tid) f(ph, tid, nthr, t, io, g, box, smem, ft);
+        return;
+    }
+    for (int ph = 0; ph < zfwd_nphase(t); ++ph)
+        for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, false, t.TZ)(ph, tid, nthr, t, io, g, box, smem, ft);
 }
 static yfn pick_y(const FftPlan& pl, bool inv)
 {
@@ -177,19 +203,22 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
                 for (int ph = 0; ph < zinv_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true, t.TZ)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
             }
             if (plane2_fn) {
                 std::vector<int> xmask(p2_nmask);
                 p2_mk(t.xmap, xmask.data());
-                const Plane2Sm psm{t.px.tw, t.py.tw, t.pl_ymapT, t.pl_xact, xmask.data()};
-                std::vector<cplx> P((size_t)nr2 * p2_ldp), sin(H.nst), sout(H.nst);
+                std::vector<int> ymap2((size_t)nr2 * H.nxw);
+                for (size_t i = 0; i < ymap2.size(); ++i) ymap2[i] = plane2_ymap(t.pl_ymapT[i], H.nst);
+                const Plane2Sm psm{t.px.tw, t.py.tw, ymap2.data(), t.pl_xact, xmask.data()};
+                std::vector<cplx> P((size_t)nr2 * p2_ldp), sin(plane2_row_elems(H.nst)), sout(plane2_row_elems(H.nst));
                 const int pthr = ((nthr + 31) / 32) * 32;  // whole warps
                 for (int z = 0; z < nr3; ++z) {
                     for (auto& x : P) x = nanv;
                     for (auto& x : sout) x = nanv;
                     cplx* row = t.g1 + (size_t)box * t.g1_box + (size_t)z * t.g1_zs;
                     for (int i = 0; i < H.nst; ++i) sin[i] = row[i];
+                    sin[H.nst] = mk(0.0, 0.0);
                     for (int ph = 0; ph < p2_nph; ++ph)
                         for (int tid = 0; tid < pthr; ++tid) plane2_fn(ph, tid, pthr, t, z, P.data(), sin.data(), sout.data(), psm);
                     for (int i = 0; i < H.nst; ++i) row[i] = sout[i];
@@ -228,8 +257,7 @@ extern "C" int emul_vloc(int nr1, int nr2, int nr3, int npw, const int* nl, cons
             }
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
-                for (int ph = 0; ph < zfwd_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, false)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+                run_zfwd_group(t, io, g, box, smem.data(), nthr);
             }
         }
     }
@@ -280,7 +308,7 @@ extern "C" int emul_sumband(int nr1, int nr2, int nr3, int npw, const int* nl, c
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
                 for (int ph = 0; ph < zinv_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true, t.TZ)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
             }
             for (int xa = 0; xa < H.nxw; ++xa)
                 for (int zt = 0; zt < H.nty; ++zt) {
@@ -360,7 +388,7 @@ extern "C" int emul_vloc_nc(int nr1, int nr2, int nr3, int npw, const int* nl, c
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
                 for (int ph = 0; ph < zinv_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, true, t.TZ)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
             }
             for (int xa = 0; xa < H.nxw; ++xa)
                 for (int zt = 0; zt < H.nty; ++zt) {
@@ -394,8 +422,7 @@ extern "C" int emul_vloc_nc(int nr1, int nr2, int nr3, int npw, const int* nl, c
                 }
             for (int g = 0; g < H.ngrp; ++g) {
                 for (auto& x : smem) x = nanv;
-                for (int ph = 0; ph < zfwd_nphase(t); ++ph)
-                    for (int tid = 0; tid < nthr; ++tid) pick_z(t.pz, false)(ph, tid, nthr, t, io, g, box, smem.data(), FastTabs{t.pz.tw, nullptr, t.pz.rev, t.grp_stick + (size_t)g * t.TZ});
+                run_zfwd_group(t, io, g, box, smem.data(), nthr);
             }
         }
     }
