@@ -250,6 +250,8 @@ QEB_HD void fft_pass(int tid, int nthr, int nl, const FastDiv& divNl, const Pass
     case 10: fft_pass_r<10, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     case 12: fft_pass_r<12, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     case 15: fft_pass_r<15, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
+    case 16: fft_pass_r<16, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
+    case 20: fft_pass_r<20, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     case 25: fft_pass_r<25, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     case 27: fft_pass_r<27, DIT, FUSE2>(tid, nthr, nl, divNl, pd, tw, sgn, src, dst, mid); break;
     default: break;

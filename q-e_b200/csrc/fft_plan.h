@@ -102,7 +102,7 @@ inline bool preferred_factors(int n, std::vector<int>& out)
     case 125: out = {25, 5}; return true;
     case 135: out = {15, 9}; return true;
     case 144: out = {12, 12}; return true;
-    case 200: out = {25, 8}; return true;
+    case 200: out = {8, 5, 5}; return true;  // measured at AUSURF112 (z passes): 20.3 vs 20.7 us/band for {25, 8} (profiles/r2k_sweep.log)
     default: return false;
     }
 }
@@ -130,7 +130,7 @@ inline bool make_host_plan(int n, HostPlan& hp, int maxr = 10, const char* overr
 {
     hp.n = n;
     if (parse_plan(override_txt, n, hp.r)) {
-        static const int ok[] = {2, 3, 4, 5, 8, 9, 12, 15, 25, 27};
+        static const int ok[] = {2, 3, 4, 5, 6, 8, 9, 10, 12, 15, 16, 20, 25, 27};
         for (int r : hp.r) {
             bool f = false;
             for (int o : ok) f = f || (o == r);

@@ -232,6 +232,8 @@ using SP200 = SPlan<200, 25, 8>;
 // low-register alternatives (radices <= 8: about half the registers per thread, twice the resident warps, one more
 // shared-memory exchange); selected with QEB_XPLAN / QEB_YPLAN / QEB_ZPLAN
 using SP200b = SPlan<200, 8, 5, 5>;
+using SP200c = SPlan<200, 20, 10>;
+using SP200d = SPlan<200, 10, 20>;
 using SP125b = SPlan<125, 5, 5, 5>;
 using SP64b = SPlan<64, 4, 4, 4>;
 

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(256) k_vloc_xacc(const __grid_constant__ VlocT
 }
 
 // ---- fast variants (vloc_fast_inst.cuh, instantiated in vloc_fast_<N>.cu) ----
-#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200) X(SP200b)
+#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200) X(SP200b) X(SP200c) X(SP200d)
 #define X(PL) extern template struct FastLaunch<PL>;
 QEB_FOR_PLANS(X)
 #undef X

@@ -8,6 +8,7 @@ struct VlocLaunchCfg {
     int threads_z, threads_y, threads_x;
     // fused plane pass (vloc_plane.cuh): used when t.pl_v is set and smem_plane <= max_smem
     size_t smem_plane = 0, max_smem = 0;
+    size_t max_smem_sm = 0;  // shared memory of one SM (occupancy planning of the z passes)
     int num_sms = 148;
 };
 cudaError_t vloc_init_attrs(size_t max_smem);

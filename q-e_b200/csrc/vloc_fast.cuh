@@ -13,13 +13,6 @@
 
 namespace qeb {
 
-// butterflies per warp in the fast z passes for tiles of TZ sticks (fft_static.cuh::spass SUB); QEB_ZSUB=2 switches it on: measured slower at AUSURF112 (V_loc 21.1 -> 23.6 us/band, profiles/r2f_sweep.log: the per-lane butterfly index costs the warp-uniform addressing and spills)
-inline int vloc_zsub(int TZ)
-{
-    const char* e = getenv("QEB_ZSUB");
-    return (TZ <= QEB_TL / 2 && e && atoi(e) == 2) ? 2 : 1;
-}
-
 // software-pipelined loads in the global-source (first DIT) passes: measured SLOWER (zfwd 66 -> 81 us per 15 boxes at
 // AUSURF112, Si512 25.8 -> 28.8 us/band: the extra live butterfly spills at the 128-register budget); off by default
 #ifdef QEB_USE_GPF

@@ -14,8 +14,10 @@ namespace qeb {
 #define QEB_SMEM extern __shared__ __align__(16) unsigned char smem_raw[]; cplx* smem = reinterpret_cast<cplx*>(smem_raw)
 
 // ---- fast variants: compile-time plan of the pass direction, warp-mapped work ----
-template <class PL, int SUB>
-__global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_zinv_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
+// OCC: resident CTAs per SM the register budget is compiled for (1: 128 registers with up to 512 threads; 4: 160 threads
+// and 102 registers, so that four 51 KB tiles fit an SM)
+template <class PL, int OCC>
+__global__ void __launch_bounds__(OCC > 1 ? 160 : QEB_FAST_MAXTHREADS, OCC) k_vloc_zinv_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
 {
     QEB_SMEM;
     cplx* twS = smem + ((size_t)t.nr3 * t.TZ);
@@ -26,12 +28,12 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_zinv_f(const __gri
     const FastTabs ft{twS, nullptr, tabS, tabS + PL::N};
     __syncthreads();
     for (int ph = 0; ph < 2 + PL::NP; ++ph) {
-        zinv_fast_phase<PL, SUB>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
+        zinv_fast_phase<PL, 1>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
         __syncthreads();
     }
 }
-template <class PL, int SUB, bool STAGE>
-__global__ void __launch_bounds__(STAGE ? 256 : QEB_FAST_MAXTHREADS, STAGE ? 2 : 1)
+template <class PL, bool STAGE, int OCC>
+__global__ void __launch_bounds__(OCC > 1 ? 160 : (STAGE ? 256 : QEB_FAST_MAXTHREADS), OCC > 1 ? OCC : (STAGE ? 2 : 1))
     k_vloc_zfwd_f(const __grid_constant__ VlocTables t, const __grid_constant__ VlocIO io)
 {
     QEB_SMEM;
@@ -53,7 +55,7 @@ __global__ void __launch_bounds__(STAGE ? 256 : QEB_FAST_MAXTHREADS, STAGE ? 2 :
         __syncthreads();
     }
     for (int ph = 0; ph < 1 + PL::NP; ++ph) {
-        zfwd_fast_phase<PL, SUB, STAGE>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
+        zfwd_fast_phase<PL, 1, STAGE>(ph, threadIdx.x, blockDim.x, t, io, blockIdx.x, blockIdx.y, smem, ft);
         __syncthreads();
     }
 }
@@ -229,7 +231,7 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xacc_f(const __gri
 
 // warps per CTA for a plan: the count in [lo,hi] that wastes the fewest warp-rounds over the passes
 template <class PL>
-static int pick_warps(int lo, int hi, int sub = 1)
+static int pick_warps(int lo, int hi)
 {
     int best = lo;
     double beff = -1.0;
@@ -238,7 +240,7 @@ static int pick_warps(int lo, int hi, int sub = 1)
         for (int p = 0; p < PL::NP; ++p) {
             const int nj = PL::N / PL::r(p);
             used += nj;
-            tot += (long)((nj + nw * sub - 1) / (nw * sub)) * (nw * sub);
+            tot += (long)((nj + nw - 1) / nw) * nw;
         }
         const double eff = (double)used / (double)tot;
         if (eff > beff - 1e-9) {  // ties: more warps
@@ -271,10 +273,10 @@ template <class PL>
 void FastLaunch<PL>::attrs(int s)
 {
     cudaFuncSetAttribute(k_vloc_zinv_f<PL, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
-    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
-    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
-    cudaFuncSetAttribute(k_vloc_zinv_f<PL, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
-    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zinv_f<PL, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
+    cudaFuncSetAttribute(k_vloc_zfwd_f<PL, true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_yinv_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_yfwd_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
     cudaFuncSetAttribute(k_vloc_xfus_f<PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, s);
@@ -286,24 +288,26 @@ template <class PL>
 void FastLaunch<PL>::z(bool inv, const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
 {
     const dim3 grid(t.ngrp, nboxes);
-    // tiles of <= 16 sticks: two butterflies per warp (fft_static.cuh::spass SUB = 2) when QEB_ZSUB=2
-    const bool sub2 = vloc_zsub(t.TZ) == 2;
     const bool stage = !inv && env_int("QEB_ZSTAGE", 1) != 0;
-    int nw = env_int("QEB_NWZ", pick_warps<PL>(4, stage ? 8 : 10, sub2 ? 2 : 1));
-    if (stage && nw > 8) nw = 8;
     const size_t smem = cfg.smem_z + PL::N * 24 + 4 * QEB_TL + 16;
+    // QEB_ZOCC=4: the 96-register build with four resident CTAs per SM; measured slower (spills: 22.9 vs 20.8 us/band at
+    // AUSURF112, profiles/r2j_sweep.log), off by default
+    const bool occ4 = env_int("QEB_ZOCC", 1) == 4 && 4 * (smem + 1024) <= cfg.max_smem_sm;
+    int nw = env_int("QEB_NWZ", pick_warps<PL>(4, occ4 ? 5 : (stage ? 8 : 10)));
+    if (occ4 && nw > 5) nw = 5;
+    if (stage && nw > 8) nw = 8;
     if (inv) {
-        if (sub2)
-            k_vloc_zinv_f<PL, 2><<<grid, nw * 32, smem, st>>>(t, io);
+        if (occ4)
+            k_vloc_zinv_f<PL, 4><<<grid, nw * 32, smem, st>>>(t, io);
         else
             k_vloc_zinv_f<PL, 1><<<grid, nw * 32, smem, st>>>(t, io);
     } else {
-        if (stage)
-            k_vloc_zfwd_f<PL, 1, true><<<grid, nw * 32, smem, st>>>(t, io);
-        else if (sub2)
-            k_vloc_zfwd_f<PL, 2, false><<<grid, nw * 32, smem, st>>>(t, io);
+        if (stage && occ4)
+            k_vloc_zfwd_f<PL, true, 4><<<grid, nw * 32, smem, st>>>(t, io);
+        else if (stage)
+            k_vloc_zfwd_f<PL, true, 1><<<grid, nw * 32, smem, st>>>(t, io);
         else
-            k_vloc_zfwd_f<PL, 1, false><<<grid, nw * 32, smem, st>>>(t, io);
+            k_vloc_zfwd_f<PL, false, 1><<<grid, nw * 32, smem, st>>>(t, io);
     }
 }
 template <class PL>

@@ -50,7 +50,7 @@ extern "C" int emul_fft1d(int n, int sign, int nlines, const double* in, double*
     return 0;
 }
 
-#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200) X(SP200b)
+#define QEB_FOR_PLANS(X) X(SP15) X(SP25) X(SP27) X(SP64) X(SP125) X(SP135) X(SP144) X(SP200) X(SP200b) X(SP200c) X(SP200d)
 typedef void (*zfn)(int, int, int, const VlocTables&, const VlocIO&, int, int, cplx*, const FastTabs&);
 typedef void (*yfn)(int, int, int, const VlocTables&, int, int, int, cplx*, const FastTabs&);
 typedef void (*xfn)(int, int, int, const VlocTables&, int, int, cplx*, const FastTabs&);
@@ -61,11 +61,9 @@ static void zfwd_g(int ph, int tid, int nthr, const VlocTables& t, const VlocIO&
 static void yinv_g(int ph, int tid, int nthr, const VlocTables& t, int z, int x, int b, cplx* s, const FastTabs&) { yinv_phase(ph, tid, nthr, t, z, x, b, s); }
 static void yfwd_g(int ph, int tid, int nthr, const VlocTables& t, int z, int x, int b, cplx* s, const FastTabs&) { yfwd_phase(ph, tid, nthr, t, z, x, b, s); }
 static void xfus_g(int ph, int tid, int nthr, const VlocTables& t, int tile, int b, cplx* s, const FastTabs&) { xfus_phase(ph, tid, nthr, t, tile, b, s); }
-static zfn pick_z(const FftPlan& pl, bool inv, int TZ = 32)
+static zfn pick_z(const FftPlan& pl, bool inv, int = 32)
 {
-    // the half-warp mapping of the kernels (two butterflies per warp for tiles of <= 16 sticks) when they would use it
-#define X(PL) if (g_fast && PL::matches(pl) && vloc_zsub(TZ) == 2) return inv ? (zfn)zinv_fast_phase<PL, 2> : (zfn)zfwd_fast_phase<PL, 2>; \
-              if (g_fast && PL::matches(pl)) return inv ? (zfn)zinv_fast_phase<PL, 1> : (zfn)zfwd_fast_phase<PL, 1>;
+#define X(PL) if (g_fast && PL::matches(pl)) return inv ? (zfn)zinv_fast_phase<PL, 1> : (zfn)zfwd_fast_phase<PL, 1>;
     QEB_FOR_PLANS(X)
 #undef X
     return inv ? zinv_g : zfwd_g;
