@@ -96,6 +96,16 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_set_qq(ctx, nat, nhm, qq_at) BIND(C, name='qeb_set_qq')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, qq_at; INTEGER(C_INT), VALUE :: nat, nhm
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_cegterg(ctx, npw, npwx, nvec, nvecx, npol, evc, ethr, uspp, e, btype, notcnv, lrot, &
+                                        dav_iter, nhpsi) BIND(C, name='qeb_cegterg')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, evc, e, btype, notcnv, dav_iter, nhpsi
+      INTEGER(C_INT), VALUE :: npw, npwx, nvec, nvecx, npol, uspp, lrot; REAL(C_DOUBLE), VALUE :: ethr
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_regterg(ctx, npw, npwx, nvec, nvecx, evc, ethr, uspp, e, btype, notcnv, lrot, &
+                                        dav_iter, nhpsi) BIND(C, name='qeb_regterg')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, evc, e, btype, notcnv, dav_iter, nhpsi
+      INTEGER(C_INT), VALUE :: npw, npwx, nvec, nvecx, uspp, lrot; REAL(C_DOUBLE), VALUE :: ethr
+    END FUNCTION
     INTEGER(C_INT) FUNCTION qeb_s_psi(ctx, lda, n, m, psi, spsi) BIND(C, name='qeb_s_psi')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, spsi; INTEGER(C_INT), VALUE :: lda, n, m
     END FUNCTION
@@ -319,6 +329,23 @@ CONTAINS
       k_set = -1
     END IF
   END SUBROUTINE
+  LOGICAL FUNCTION qeb200_hpsi_supported()
+    !! .FALSE. for the h_psi_ branches the library does not build (SURVEY 8a a18): they keep the reference routines
+    USE realus,   ONLY: real_space
+    USE fft_base, ONLY: dffts
+    USE ldaU,     ONLY: lda_plus_u
+    USE bp,       ONLY: lelfield
+    USE xc_lib,   ONLY: exx_is_active, xclib_dft_is
+    qeb200_hpsi_supported = .NOT. (real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. &
+                                   exx_is_active() .OR. xclib_dft_is('meta') .OR. dffts%lpara)
+  END FUNCTION
+  SUBROUTINE qeb200_push_g_psi_diag(n, hd, sd)
+    !! g_psi_mod::h_diag / s_diag of the current k-point -> context (PW/src/c_bands.f90 fills them before the solver)
+    USE kinds, ONLY: DP
+    INTEGER, INTENT(IN) :: n
+    REAL(DP), INTENT(IN), TARGET :: hd(*), sd(*)
+    CALL qeb200_check(qeb_set_g_psi_diag(ctx, n, C_LOC(hd), C_LOC(sd)), 'qeb_set_g_psi_diag')
+  END SUBROUTINE
 END MODULE qeb200_state
 
 !----------------------------------------------------------------------------
@@ -347,8 +374,7 @@ SUBROUTINE h_psi_qeb(lda, n, m, psi, hpsi)
   INTEGER :: m_start, m_end, column_type, m_becp
   INTEGER, ALLOCATABLE :: recv_counts(:), displs(:)
   !
-  IF (real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. exx_is_active() .OR. &
-      xclib_dft_is('meta') .OR. dffts%lpara) THEN
+  IF (.NOT. qeb200_hpsi_supported()) THEN
     CALL h_psi(lda, n, m, psi, hpsi)      ! original Fortran path
     RETURN
   END IF
@@ -559,6 +585,72 @@ SUBROUTINE g_psi_qeb(lda, n, m, npol, psi, e)
   END IF
   CALL qeb200_check(qeb_g_psi(ctx, lda, n, m, npol, C_LOC(psi), C_LOC(e)), 'g_psi')
 END SUBROUTINE g_psi_qeb
+
+!----------------------------------------------------------------------------
+SUBROUTINE cegterg_qeb(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, npol, evc, ethr, e, btype, &
+                       notcnv, lrot, dav_iter, nhpsi)
+  !! cegterg(...) (KS_Solvers/Davidson/cegterg.f90:18-21), same argument list, for the call in PW/src/c_bands.f90
+  !! (diag_bands_k). The whole solve runs on the device with psi, hpsi, spsi resident in HBM (qeb_cegterg); the
+  !! EXTERNAL operator arguments are accepted for signature compatibility and used only by the fallback: the library
+  !! applies ITS h_psi / s_psi / g_psi, which are what h_psi_qeb / s_psi_qeb / g_psi_qeb would compute. Spinors, more
+  !! than one band group, parallel diagonalisation and every h_psi_ branch the library does not build (see h_psi_qeb)
+  !! go to the reference cegterg with the pointers the caller passed. g_psi_mod::h_diag / s_diag are pushed here.
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds,            ONLY: DP
+  USE noncollin_module, ONLY: noncolin
+  USE mp_bands,         ONLY: nbgrp
+  USE g_psi_mod,        ONLY: h_diag, s_diag
+  USE qeb200_c
+  USE qeb200_state
+  IMPLICIT NONE
+  EXTERNAL :: h_psi_ptr, s_psi_ptr, g_psi_ptr
+  LOGICAL, INTENT(IN) :: uspp, lrot
+  INTEGER, INTENT(IN) :: npw, npwx, nvec, nvecx, npol
+  COMPLEX(DP), INTENT(INOUT), TARGET :: evc(npwx*npol, nvec)
+  REAL(DP), INTENT(IN) :: ethr
+  REAL(DP), INTENT(OUT), TARGET :: e(nvec)
+  INTEGER, INTENT(IN), TARGET :: btype(nvec)
+  INTEGER, INTENT(OUT), TARGET :: notcnv, dav_iter, nhpsi
+  IF (noncolin .OR. npol /= 1 .OR. nbgrp > 1 .OR. .NOT. qeb200_hpsi_supported()) THEN
+    CALL cegterg(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, npol, evc, ethr, e, btype, &
+                 notcnv, lrot, dav_iter, nhpsi)
+    RETURN
+  END IF
+  CALL qeb200_sync_state()
+  CALL qeb200_push_g_psi_diag(npw, h_diag, s_diag)
+  CALL qeb200_check(qeb_cegterg(ctx, npw, npwx, nvec, nvecx, npol, C_LOC(evc), ethr, MERGE(1, 0, uspp), C_LOC(e), &
+                                C_LOC(btype), C_LOC(notcnv), MERGE(1, 0, lrot), C_LOC(dav_iter), C_LOC(nhpsi)), 'cegterg')
+END SUBROUTINE cegterg_qeb
+
+!----------------------------------------------------------------------------
+SUBROUTINE regterg_qeb(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, evc, ethr, e, btype, &
+                       notcnv, lrot, dav_iter, nhpsi)
+  !! regterg(...) (KS_Solvers/Davidson/regterg.f90:18-21), the gamma_only twin of cegterg_qeb (diag_bands_gamma).
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds,     ONLY: DP
+  USE mp_bands,  ONLY: nbgrp
+  USE g_psi_mod, ONLY: h_diag, s_diag
+  USE qeb200_c
+  USE qeb200_state
+  IMPLICIT NONE
+  EXTERNAL :: h_psi_ptr, s_psi_ptr, g_psi_ptr
+  LOGICAL, INTENT(IN) :: uspp, lrot
+  INTEGER, INTENT(IN) :: npw, npwx, nvec, nvecx
+  COMPLEX(DP), INTENT(INOUT), TARGET :: evc(npwx, nvec)
+  REAL(DP), INTENT(IN) :: ethr
+  REAL(DP), INTENT(OUT), TARGET :: e(nvec)
+  INTEGER, INTENT(IN), TARGET :: btype(nvec)
+  INTEGER, INTENT(OUT), TARGET :: notcnv, dav_iter, nhpsi
+  IF (nbgrp > 1 .OR. .NOT. qeb200_hpsi_supported()) THEN
+    CALL regterg(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, evc, ethr, e, btype, &
+                 notcnv, lrot, dav_iter, nhpsi)
+    RETURN
+  END IF
+  CALL qeb200_sync_state()
+  CALL qeb200_push_g_psi_diag(npw, h_diag, s_diag)
+  CALL qeb200_check(qeb_regterg(ctx, npw, npwx, nvec, nvecx, C_LOC(evc), ethr, MERGE(1, 0, uspp), C_LOC(e), &
+                                C_LOC(btype), C_LOC(notcnv), MERGE(1, 0, lrot), C_LOC(dav_iter), C_LOC(nhpsi)), 'regterg')
+END SUBROUTINE regterg_qeb
 
 !----------------------------------------------------------------------------
 SUBROUTINE init_us_2_qeb(npw_, igk_, q_, vkb_)

@@ -218,6 +218,22 @@ int qeb_dav_gemm_cn(qeb_ctx* ctx, int n, const void* A, int lda, int ka, const v
 int qeb_dav_gemm_nn(qeb_ctx* ctx, int n, const void* A, int lda, int k, const void* B, int ldb, int m, void* C,
                     int ldc, int accumulate);
 
+/* ---- device-resident block-Davidson solver ----------------- */
+/* cegterg(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, npol, evc, ethr, e, btype, notcnv, lrot,
+ *         dav_iter, nhpsi)                                 KS_Solvers/Davidson/cegterg.f90:18-700
+ * regterg(... same list without npol ...)                  KS_Solvers/Davidson/regterg.f90:18-640 (gamma_only grids)
+ * The three EXTERNAL operators are the context's own (qeb_h_psi, qeb_s_psi when uspp != 0 - it needs qeb_set_qq for
+ * ultrasoft overlaps -, qeb_g_psi with the diagonals of qeb_set_g_psi_diag). psi, hpsi, spsi (npwx x nvecx) and the
+ * reduced matrices stay in device memory for the whole solve; `diaghg` is cusolverDnZhegvd / Dsygvd (libcusolver is
+ * opened at run time, QEB_CUSOLVER_LIB overrides the name). evc (npwx x nvec, INOUT) may be a host or a device pointer;
+ * e (nvec, OUT), btype (nvec, IN: 1 = occupied, threshold ethr; 0 = empty, threshold max(5 ethr, 1e-5)), notcnv,
+ * dav_iter, nhpsi (OUT) are host data. One band group, serial diagonalisation, npol = 1; other cases return an error
+ * and the Fortran shim keeps the reference routine for them. */
+int qeb_cegterg(qeb_ctx* ctx, int npw, int npwx, int nvec, int nvecx, int npol, void* evc, double ethr, int uspp, double* e,
+                const int* btype, int* notcnv, int lrot, int* dav_iter, int* nhpsi);
+int qeb_regterg(qeb_ctx* ctx, int npw, int npwx, int nvec, int nvecx, void* evc, double ethr, int uspp, double* e,
+                const int* btype, int* notcnv, int lrot, int* dav_iter, int* nhpsi);
+
 /* ---- multi-GPU (one process per GPU) ----------------------------------- */
 /* divide_all(comm, m, m_start, m_end, recv_counts, displs)  UtilXlib/divide.f90:55-106.
  * 0-based start/end(exclusive) of group `me` of `nproc`. */

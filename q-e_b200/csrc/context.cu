@@ -90,6 +90,7 @@ int qeb_destroy(qeb_ctx* c)
                       &c->qnc_d};
     for (void* m : c->p2p_opened) cudaIpcCloseMemHandle(m);
     c->p2p_opened.clear();
+    qeb_solver_release(c);
     for (DevBuf* b : bufs) b->release();
     c->p2p_flags_d.release();
     c->p2p_ptrs_d.release();

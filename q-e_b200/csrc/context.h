@@ -51,6 +51,9 @@ inline bool is_device_ptr(const void* p)
     return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
+struct qeb_solver_state;  // solver.cu: work arrays of the device-resident Davidson solver
+void qeb_solver_release(struct qeb_ctx* c);
+
 struct qeb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -157,6 +160,7 @@ struct qeb_ctx {
     DevBuf p2p_flags_d, p2p_ptrs_d;
     bool p2p_exported = false;
     std::vector<void*> p2p_opened;  // cudaIpcOpenMemHandle mappings to close
+    qeb_solver_state* solver = nullptr;
 };
 
 #define QEB_FAIL(ctx, code, msg)   \

@@ -56,6 +56,8 @@ def load_library():
     L.qeb_set_vloc.argtypes = [P, P]
     L.qeb_set_nonlocal.argtypes = [P, I, I, P, P, P]
     L.qeb_h_psi.argtypes = [P, I, I, I, P, P]
+    L.qeb_cegterg.argtypes = [P, I, I, I, I, I, P, ctypes.c_double, I, P, P, P, I, P, P]
+    L.qeb_regterg.argtypes = [P, I, I, I, I, P, ctypes.c_double, I, P, P, P, I, P, P]
     L.qeb_vloc_psi_k.argtypes = [P, I, I, I, P, P, P]
     L.qeb_vloc_psi_gamma.argtypes = [P, I, I, I, P, P, P]
     L.qeb_set_vloc_nc.argtypes = [P, P]
@@ -363,6 +365,25 @@ class HPsi:
         self._ck(self._L.qeb_dav_gemm_nn(self._h, n, _ptr(A), lda, k, _ptr(B), ldb, m, _ptr(C), ldc, int(accumulate)),
                  "qeb_dav_gemm_nn")
         return C
+
+    def cegterg(self, npw, npwx, nvec, nvecx, evc, ethr, uspp, btype, lrot=False, npol=1):
+        """cegterg / regterg (KS_Solvers/Davidson/cegterg.f90:18, regterg.f90:18) with the context's operators: evc
+        (nvec, npwx) complex, host array or device tensor, is refined in place; returns (e, notcnv, dav_iter, nhpsi)."""
+        e = np.zeros(nvec)
+        bt = np.ascontiguousarray(btype, dtype=np.int32)
+        out = (ctypes.c_int * 3)()
+        pn, pi, ph = (ctypes.cast(ctypes.byref(out, 4 * k), ctypes.c_void_p) for k in range(3))
+        if self.gamma_only:
+            rc = self._L.qeb_regterg(self._h, npw, npwx, nvec, nvecx, _ptr(evc), float(ethr), int(bool(uspp)), _ptr(e), _ptr(bt),
+                                     pn, int(bool(lrot)), pi, ph)
+            self._ck(rc, "qeb_regterg")
+        else:
+            rc = self._L.qeb_cegterg(self._h, npw, npwx, nvec, nvecx, npol, _ptr(evc), float(ethr), int(bool(uspp)), _ptr(e),
+                                     _ptr(bt), pn, int(bool(lrot)), pi, ph)
+            self._ck(rc, "qeb_cegterg")
+        return e, int(out[0]), int(out[1]), int(out[2])
+
+    regterg = cegterg
 
     # -- reference entry points --------------------------------------------
     def s_psi(self, lda, n, m, psi, spsi):
