@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--parity-cols", type=int, default=8)
     ap.add_argument("--no-library-bar", action="store_true", help="skip the cuFFT + cuBLAS bar")
     ap.add_argument("--no-davidson", action="store_true", help="skip the device-resident Davidson solve (qeb_cegterg)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling modes measured beside the k-pools line")
     ap.add_argument("--davidson-ethr", type=float, default=1e-4)
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
@@ -231,6 +232,96 @@ def parity_check(torch, d, lda, n, m, psi, hpsi, vkb, vrs, deeq, nh, ofs, k=8):
     return {"cols": int(kk), "max_rel": float((num / den).max()), "tolerance": 1e-11,
             "checker": ("reference C FFT engine (oracle/_ref)" if use_ref else "numpy restatement") + " + numpy zgemm",
             "pad_rows_zero": bool(np.all(got[:, n:] == 0))}
+
+
+# ---------------------------------------------------------------------------
+# strong-scaling modes, measured in the same run as the k-pools line
+# ---------------------------------------------------------------------------
+def strong_mode(torch, dist, qe_b200, wname, mode, world, rank, local, stream, steps=3, group=None, gsize=None, grank=None,
+                exchange="p2p", seed=0):
+    """one h_psi call of `wname` per step with the work of ONE k-point split over `gsize` ranks (the ranks of `group`):
+    mode "bgrp": band groups + all-gather of hpsi (h_psi.f90:53-67); mode "rg": slab-distributed FFT + becp all-reduce
+    (fft_parallel_2d.f90, becmod.f90:395-399). Returns (bands per step of the group, ms per step as max over ranks)."""
+    gsize = gsize or world
+    grank = rank if grank is None else grank
+    dev = torch.device("cuda", local)
+    d, c, nh = workload(wname, seed=seed)
+    m_total = c["nbnd"]
+    nkb = int(nh.sum())
+    rg = mode == "rg"
+    if rg:
+        d.distribute(gsize)
+        rk = d.ranks[grank]
+        n = rk.npw
+    else:
+        n = d.npw
+    lda = n
+    g = torch.Generator(device=dev).manual_seed(99 + grank)
+    psi = torch.randn((m_total, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(2 * d.npw)
+    if d.gamma_only:
+        psi[:, 0, 1] = 0.0
+    hpsi = torch.zeros_like(psi)
+    vkb = torch.randn((nkb, lda, 2), generator=g, device=dev, dtype=torch.float64) / np.sqrt(d.npw)
+    if d.gamma_only:
+        vkb[:, 0, 1] = 0.0
+    rng = np.random.default_rng(77 + grank)
+    nhm = int(nh.max())
+    deeq = np.random.default_rng(4234).uniform(-1, 1, (len(nh), nhm, nhm))
+    deeq = 0.5 * (deeq + deeq.transpose(0, 2, 1))
+    ofs = np.concatenate([[0], np.cumsum(nh)[:-1]]).astype(np.int32)
+    h = qe_b200.HPsi(device=local, stream=stream)
+    if rg:
+        h.set_grid_dist(d.nr1, d.nr2, d.nr3, gsize, grank, d.nr3p, d.nsw, d.iss, d.ismap, rk.nl,
+                        rk.nlm if d.gamma_only else None, d.gamma_only)
+        if gsize > 1:
+            h.nccl_init(qe_b200.COMM_RG)
+        h.set_kpoint(n, lda, None if d.gamma_only else rk.igk, rk.g2kin, vkb, nkb, rk.gstart)
+        h.set_vloc(rng.uniform(-1.0, 0.0, d.nr1 * d.nr2 * int(d.nr3p[grank])))
+        if gsize > 1 and exchange == "p2p":
+            h.p2p_setup()
+    else:
+        h.set_grid(d.nr1, d.nr2, d.nr3, d.nl, d.nlm if d.gamma_only else None, d.gamma_only)
+        h.set_kpoint(n, lda, None if d.gamma_only else d.igk, d.g2kin, vkb, nkb, d.gstart)
+        h.set_vloc(rng.uniform(-1.0, 0.0, d.nnr))
+    h.set_nonlocal(nh, ofs, deeq)
+    h.set_async(True)
+    m0, m1 = (0, m_total) if rg else qe_b200.divide_all(m_total, gsize, grank)
+    bounds = [qe_b200.divide_all(m_total, gsize, r) for r in range(gsize)]
+
+    def step():
+        if rg or gsize == 1:
+            h.h_psi(lda, n, m_total, psi, hpsi)
+            return
+        h.h_psi_bgrp(lda, n, m_total, psi, hpsi, gsize, grank)
+        blocks = [hpsi[s_:e_] for s_, e_ in bounds]
+        if len({b.shape[0] for b in blocks}) == 1:
+            dist.all_gather(blocks, hpsi[m0:m1], group=group)
+        else:
+            for r, b in enumerate(blocks):
+                dist.broadcast(b, src=dist.get_global_rank(group, r) if group is not None else r, group=group)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(3):
+        step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    h.close()
+    del psi, hpsi, vkb
+    torch.cuda.empty_cache()
+    return m_total, float(t.item())
 
 
 def run_reference(args):
@@ -545,6 +636,29 @@ def run_ours(args):
             lib_bar = {"unavailable": repr(exc)[:200]}
         torch.cuda.empty_cache()
 
+    # ---- strong-scaling modes of ONE k-point over the same GPUs (values only; efficiencies follow from the N=1 run) ----
+    strong = None
+    if pools and not args.no_strong and args.workload == "ausurf112":
+        strong = {}
+        try:
+            mb, msb = strong_mode(torch, dist, qe_b200, "ausurf112", "bgrp", world, rank, local, stream)
+            strong["bgrp"] = {"workload": "ausurf112", "layout": f"{world} band groups", "bands_per_step": mb, "ms_per_step": msb,
+                              "value": mb / (msb * 1e-3), "unit": "band-applications/s"}
+            if world >= 4 and world % 2 == 0:
+                half = world // 2
+                groups = [dist.new_group(list(range(p_ * half, (p_ + 1) * half))) for p_ in range(2)]
+                pool = rank // half
+                mb, msb = strong_mode(torch, dist, qe_b200, "ausurf112", "bgrp", world, rank, local, stream, group=groups[pool],
+                                      gsize=half, grank=rank % half, seed=pool)
+                strong["pools2xbgrp"] = {"workload": "ausurf112", "layout": f"2 k-pools x {half} band groups (the 2 k-points of AUSURF112)",
+                                         "bands_per_step": 2 * mb, "ms_per_step": msb, "value": 2 * mb / (msb * 1e-3),
+                                         "unit": "band-applications/s"}
+            mb, msb = strong_mode(torch, dist, qe_b200, "si512", "rg", world, rank, local, stream, exchange=args.exchange)
+            strong["rg_si512"] = {"workload": "si512", "layout": f"R&G slab FFT over {world} ranks ({args.exchange} exchange)",
+                                  "bands_per_step": mb, "ms_per_step": msb, "value": mb / (msb * 1e-3), "unit": "band-applications/s"}
+        except Exception as exc:  # noqa: BLE001
+            strong["error"] = repr(exc)[:300]
+
     if rank == 0:
         line = {
             "metric": "h_psi band-applications/s", "value": value, "unit": "band-applications/s", "n_gpus": world,
@@ -560,6 +674,7 @@ def run_ours(args):
             "parity_check": parity,
             "gpu_library_bar": lib_bar,
             "davidson": davidson,
+            "strong": strong,
             "gpu_launches": launches_step * args.steps,
             "clocks": clocks,
         }
