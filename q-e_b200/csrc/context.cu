@@ -302,7 +302,7 @@ int qeb_set_grid_dist(qeb_ctx* c, int nr1, int nr2, int nr3, int nproc, int mype
     // exchange tables: owner and position-in-owner of every plane-ordered stick
     {
         const int nst = c->Hp.nst;
-        std::vector<int> host((size_t)2 * nst + 2 * nproc);
+        std::vector<int> host((size_t)4 * nst + 3 * nproc + nr3);
         for (int sg = 0; sg < nst; ++sg) {
             const int col = c->Hp.stick_x[sg] + nr1 * c->Hp.stick_y[sg];
             host[sg] = c->col_owner[col];
@@ -311,6 +311,17 @@ int qeb_set_grid_dist(qeb_ctx* c, int nr1, int nr2, int nr3, int nproc, int mype
         for (int p = 0; p < nproc; ++p) {
             host[2 * nst + p] = D.nsw[p];
             host[2 * nst + nproc + p] = D.prefix[p];
+        }
+        // fused exchange (VlocTables::peer_* / r_*): per plane-ordered stick the owner's prefix and stick count, per
+        // plane its owner, per rank its first plane
+        int* fx = host.data() + 2 * nst + 2 * nproc;
+        for (int sg = 0; sg < nst; ++sg) {
+            fx[sg] = D.prefix[host[sg]];
+            fx[nst + sg] = D.nsw[host[sg]];
+        }
+        for (int p = 0; p < nproc; ++p) {
+            fx[2 * nst + nr3 + p] = D.i0r3p[p];
+            for (int z = D.i0r3p[p]; z < D.i0r3p[p] + D.nr3p[p]; ++z) fx[2 * nst + z] = p;
         }
         QEB_CUDA(c, c->dist_tab_d.ensure(host.size() * 4 + 16));
         QEB_CUDA(c, cudaMemcpyAsync(c->dist_tab_d.p, host.data(), host.size() * 4, cudaMemcpyHostToDevice, c->stream));
@@ -325,6 +336,11 @@ int qeb_set_grid_dist(qeb_ctx* c, int nr1, int nr2, int nr3, int nproc, int mype
         c->DD.sidx = b + nst;
         c->DD.nsw = b + 2 * nst;
         c->DD.prefix = b + 2 * nst + nproc;
+        const int* fxd = b + 2 * nst + 2 * nproc;
+        c->fx_rpref = fxd;
+        c->fx_rnsw = fxd + nst;
+        c->fx_zown = fxd + 2 * nst;
+        c->fx_zi0 = fxd + 2 * nst + nr3;
     }
     c->dist = true;
     c->have_grid = true;
@@ -1119,8 +1135,36 @@ static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hp
             tp.g2 += si * g2_slice;
             const char* msg = "";
             int rc;
-            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
             const bool p2p = c->P2P.ok && D.nproc > 1;
+            // Fused exchange (peer-to-peer mapping, three-kernel plane path): the z-inverse pass stores straight into the
+            // plane owners' R buffers over NVLink, the y passes read and write R itself - no S staging and no repack
+            // kernels on the forward leg, no pack kernel on the backward leg (fft_scatter_2d.f90:123,226 folded into the
+            // neighbouring passes). QEB_FUSED_X=0: the unfused sequence.
+            const bool fused = p2p && !vloc_uses_plane_kernel(tp, c->cfgp) && D.nproc <= 16 && env_flag("QEB_FUSED_X", 1);
+            if (fused) {
+                tz.peer_on = 1;
+                tz.peer_nb = nb;
+                tz.peer_zown = c->fx_zown;
+                tz.peer_zi0 = c->fx_zi0;
+                for (int q = 0; q < D.nproc; ++q)
+                    tz.peer_base[q] = c->P2P.peer_R[q] + (size_t)si * ((size_t)D.nst_tot * D.nr3p[q] * c->P2P.batch) +
+                                      (size_t)nb * D.nr3p[q] * D.prefix[D.me];
+                QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
+                tz.peer_on = 0;
+                if ((rc = dist_p2p_sync(D, c->P2P, true, si, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+                tp.g1 = R;
+                tp.r_on = 1;
+                tp.r_nb = nb;
+                tp.r_pref = c->fx_rpref;
+                tp.r_nsw = c->fx_rnsw;
+                tp.r_sidx = c->DD.sidx;
+                QEB_CUDA(c, vloc_launch_planes(tp, c->cfgp, nb, st));
+                if ((rc = dist_exchange_p2p(D, c->P2P, false, si, S, R, nb, c->nr3, st, &msg)))
+                    QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+                QEB_CUDA(c, vloc_launch_zpass(false, tz, io, c->cfg, nb, st));
+                continue;
+            }
+            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
             if ((rc = p2p ? dist_exchange_p2p(D, c->P2P, true, si, S, R, nb, c->nr3, st, &msg)
                           : dist_exchange(D, c->nccl_rg, true, S, R, nb, st, &msg)))
                 QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);

@@ -155,6 +155,7 @@ struct qeb_ctx {
     VlocLaunchCfg cfgp;
     DevBuf tabp_d, planp_d, dist_tab_d, sbuf_d, rbuf_d;
     DistDev DD;
+    const int *fx_rpref = nullptr, *fx_rnsw = nullptr, *fx_zown = nullptr, *fx_zi0 = nullptr;  // fused exchange tables
     // peer-to-peer exchange (qeb_p2p_export / qeb_p2p_import)
     P2PState P2P;
     DevBuf p2p_flags_d, p2p_ptrs_d;
@@ -176,6 +177,12 @@ struct qeb_ctx {
             return 100 + (int)e__;                                                          \
         }                                                                                   \
     } while (0)
+
+static inline bool env_flag(const char* name, int dflt)
+{
+    const char* e = getenv(name);
+    return (e ? atoi(e) : dflt) != 0;
+}
 
 static inline int finish(qeb_ctx* c)
 {

@@ -151,4 +151,21 @@ int dist_exchange_p2p(const DistHost& h, P2PState& p, bool forward, int slot, cp
     return 0;
 }
 
+int dist_p2p_sync(const DistHost& h, P2PState& p, bool forward, int slot, cudaStream_t st, const char** msg)
+{
+    const int np = h.nproc, me = h.me;
+    const int dir = forward ? 0 : 1;
+    const unsigned epoch = ++p.epoch[dir][slot];
+    const int word0 = (dir * p.nslots + slot) * np;
+    const int thr = ((np + 31) / 32) * 32;
+    k_p2p_signal<<<1, thr, 0, st>>>(p.peer_flags_dev, np, me, word0, epoch);
+    k_p2p_wait<<<1, thr, 0, st>>>(p.peer_flags[me] + word0, np, me, epoch);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        *msg = cudaGetErrorString(e);
+        return 1000 + (int)e;
+    }
+    return 0;
+}
+
 }  // namespace qeb

@@ -48,4 +48,7 @@ struct P2PState {
 int dist_exchange_p2p(const DistHost& h, P2PState& p, bool forward, int slot, cplx* S, cplx* R, int nb, int nr3,
                       cudaStream_t st, const char** msg);
 
+// signal + wait only (the fused forward leg: the z pass has already written the peers' R buffers)
+int dist_p2p_sync(const DistHost& h, P2PState& p, bool forward, int slot, cudaStream_t st, const char** msg);
+
 }  // namespace qeb

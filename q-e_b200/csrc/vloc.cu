@@ -169,6 +169,12 @@ bool vloc_plane_available(const VlocTables& t)
     return false;
 }
 
+bool vloc_uses_plane_kernel(const VlocTables& t, const VlocLaunchCfg& cfg)
+{
+    return t.pl_v && cfg.smem_plane != 0 && cfg.smem_plane <= cfg.max_smem && !env_int("QEB_GENERIC", 0) && env_int("QEB_PLANE", 1) &&
+           vloc_plane_available(t);
+}
+
 static bool launch_plane(const VlocTables& t, const VlocLaunchCfg& cfg, int nboxes, cudaStream_t st)
 {
     if (!t.pl_v || cfg.smem_plane == 0 || cfg.smem_plane > cfg.max_smem || env_int("QEB_GENERIC", 0) ||

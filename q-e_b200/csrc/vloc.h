@@ -36,4 +36,6 @@ cudaError_t vloc_prepare_v_plane(const double* v, double* vpl, const int* rev_x,
                                  int nr3, double scale, cudaStream_t st);
 // true when an instantiated plane kernel exists for these tables' (x,y) plans
 bool vloc_plane_available(const VlocTables& t);
+// true when vloc_launch_planes would run a fused plane kernel (not the y | x | y kernels) for these tables
+bool vloc_uses_plane_kernel(const VlocTables& t, const VlocLaunchCfg& cfg);
 }  // namespace qeb

@@ -54,7 +54,10 @@ QEB_HD void zinv_fast_phase(int ph, int tid, int nthr, const VlocTables& t, cons
     const int nl = t.grp_nl[grp];
     LaneTile s{smem, t.TZ};
     NoMid nm;
-    if (p == PL::NP - 1) {
+    if (p == PL::NP - 1 && t.peer_on) {  // fused exchange: straight into the plane owners' buffers
+        G1PeerDst d{t.peer_base, t.peer_zown, t.peer_zi0, ft.rev, ft.sticks, t.peer_nb, box, t.nst};
+        SPassSel<PL, false, false, 0, false, SUB>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, d, nm);
+    } else if (p == PL::NP - 1) {
         G1Dst d{t.g1 + (size_t)box * t.g1_box, ft.rev, ft.sticks, t.g1_zs};
         SPassSel<PL, false, false, 0, false, SUB>::run(p, warp, nwarps, lane, nl, ft.tw, +1.0, s, d, nm);
     } else {

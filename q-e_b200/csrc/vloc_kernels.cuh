@@ -60,6 +60,22 @@ struct VlocTables {
     const int* pl_xact;    // [nxw]     xa -> x
     const double* pl_v;    // [nr3][nr1 xpos][nr2 ypos] = v(rev_x[xpos], rev_y[ypos], z)/(nr1 nr2 nr3)
     int pl_ldp;            // row stride of the shared-memory plane (odd, >= nr1)
+    // Slab-distributed path, fused exchange (distfft.h): peer_on != 0 makes the LAST z-inverse pass store each (z, stick)
+    // element straight into the exchange buffer R of the rank that owns plane z - over NVLink when that is a peer -
+    // in the layout the owner's y pass reads: R_q[block of the sender][z - i0(q)][box][stick of the sender]. 16 sticks of
+    // a z-pass tile are 256 contiguous bytes there. peer_base[q] already points at this rank's block in q's slice.
+    int peer_on;
+    int peer_nb;                 // boxes of this batch
+    cplx* peer_base[16];         // [nproc]
+    const int* peer_zown;        // [nr3] owner of plane z
+    const int* peer_zi0;         // [nproc] first plane of rank q
+    // r_on != 0: the y passes read / write the exchange buffer R itself (t.g1 = this slot's R slice), element
+    // (box, zl, sg) at r_nb*nr3*r_pref[sg] + (zl*r_nb + box)*r_nsw[sg] + r_sidx[sg] (fft_scatter_2d.f90:123,226 unpack / pack
+    // through ismap, fused into the pass instead of a repack kernel)
+    int r_on, r_nb;
+    const int* r_pref;           // [nst] sticks on the ranks below the owner of sg
+    const int* r_nsw;            // [nst] sticks of the owner of sg
+    const int* r_sidx;           // [nst] position of sg in its owner's list
     // noncollinear 2x2 potential (vloc_psi_nc): four arrays in the vp layout, consecutive, nr1*npos doubles each:
     // v(:,1) .. v(:,4) of PW/src/vloc_psi_acc.f90:291, each /(nr1 nr2 nr3); nullptr: not set
     const double* vnc;
@@ -87,6 +103,20 @@ struct G1Dst {  // last z-DIF pass: position -> z = rev[pos], line -> stick
     size_t zs;
     QEB_HD void store(int line, int pos, cplx v) const { g1[(size_t)rev[pos] * zs + sticks[line]] = v; }
     QEB_HD cplx load(int line, int pos) const { return g1[(size_t)rev[pos] * zs + sticks[line]]; }
+};
+
+struct G1PeerDst {  // last z-DIF pass of the fused exchange: (z, stick) -> R of the owner of plane z (VlocTables::peer_*)
+    cplx* const* base;
+    const int* zown;
+    const int* zi0;
+    const int* rev;
+    const int* sticks;
+    int nb, box, nst_me;
+    QEB_HD void store(int line, int pos, cplx v) const
+    {
+        const int z = rev[pos], q = zown[z];
+        base[q][((size_t)(z - zi0[q]) * nb + box) * nst_me + sticks[line]] = v;
+    }
 };
 
 QEB_HD int zinv_nphase(const VlocTables& t) { return 2 + t.pz.npass; }
@@ -162,7 +192,10 @@ QEB_HD void zinv_phase(int ph, int tid, int nthr, const VlocTables& t, const Vlo
     const PassDesc pd = pass_of(t.pz, p);
     SmemTile s{smem, TZ};
     NoMid nm;
-    if (p == t.pz.npass - 1) {
+    if (p == t.pz.npass - 1 && t.peer_on) {
+        G1PeerDst d{t.peer_base, t.peer_zown, t.peer_zi0, t.pz.rev, t.grp_stick + (size_t)grp * TZ, t.peer_nb, box, t.nst};
+        fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.pz.tw, +1.0, s, d, nm);
+    } else if (p == t.pz.npass - 1) {
         G1Dst d{t.g1 + (size_t)box * t.g1_box, t.pz.rev, t.grp_stick + (size_t)grp * TZ, t.g1_zs};
         fft_pass<false, false>(tid, nthr, nl, dnl, pd, t.pz.tw, +1.0, s, d, nm);
     } else {
@@ -312,6 +345,15 @@ QEB_HD void yinv_load_phase(int tid, int nthr, const VlocTables& t, int ztile, i
     const cplx* g1 = t.g1 + (size_t)box * t.g1_box;
     const int lanes = nthr < 32 ? nthr : 32;
     const int nw = nthr / lanes, wid = tid / lanes, ln = tid % lanes;
+    if (t.r_on) {  // straight from the exchange buffer (no unpack pass)
+        for (int zl = wid; zl < nl; zl += nw)
+            for (int s = ln; s < ns; s += lanes) {
+                const int sg = s0 + s;
+                C[s * ldc + zl] = t.g1[(size_t)t.r_nb * t.nr3 * t.r_pref[sg] + ((size_t)(z0 + zl) * t.r_nb + box) * t.r_nsw[sg] +
+                                       t.r_sidx[sg]];
+            }
+        return;
+    }
     for (int zl = wid; zl < nl; zl += nw)
         for (int s = ln; s < ns; s += lanes) C[s * ldc + zl] = g1[(size_t)(z0 + zl) * t.nst + s0 + s];
 }
@@ -327,6 +369,15 @@ QEB_HD void yfwd_store_phase(int tid, int nthr, const VlocTables& t, int ztile, 
     cplx* g1 = t.g1 + (size_t)box * t.g1_box;
     const int lanes = nthr < 32 ? nthr : 32;
     const int nw = nthr / lanes, wid = tid / lanes, ln = tid % lanes;
+    if (t.r_on) {  // straight into the exchange buffer (no pack pass)
+        for (int zl = wid; zl < nl; zl += nw)
+            for (int s = ln; s < ns; s += lanes) {
+                const int sg = s0 + s;
+                t.g1[(size_t)t.r_nb * t.nr3 * t.r_pref[sg] + ((size_t)(z0 + zl) * t.r_nb + box) * t.r_nsw[sg] + t.r_sidx[sg]] =
+                    C[s * ldc + zl];
+            }
+        return;
+    }
     for (int zl = wid; zl < nl; zl += nw)
         for (int s = ln; s < ns; s += lanes) g1[(size_t)(z0 + zl) * t.nst + s0 + s] = C[s * ldc + zl];
 }

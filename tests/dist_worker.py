@@ -84,6 +84,19 @@ def main():
         e1 = float((np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max(axis=1) / np.abs(ref).max(axis=1)).max())
         ok = ok and e1 < TOL and np.all(out[:, rk.npw:] == 0)
     print(f"rank {rank} R&G p2p exchange: hpsi err {e1:.2e}", flush=True)
+    # the unfused sequence (S staging + copy-engine puts + repack kernels) on the same context: on the large grids the
+    # default is the fused exchange (z pass stores into the peers' buffers, y passes read / write the exchange buffer)
+    os.environ["QEB_FUSED_X"] = "0"
+    out = np.full((m, lda), np.nan + 1j * np.nan)
+    hp.h_psi(lda, rk.npw, m, psi_l, out)
+    e1u = float((np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max(axis=1) / np.abs(ref).max(axis=1)).max())
+    ok = ok and e1u < TOL and np.all(out[:, rk.npw:] == 0)
+    del os.environ["QEB_FUSED_X"]
+    out = np.full((m, lda), np.nan + 1j * np.nan)
+    hp.h_psi(lda, rk.npw, m, psi_l, out)  # and back: the slot epochs of both sequences stay in step
+    e1f = float((np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max(axis=1) / np.abs(ref).max(axis=1)).max())
+    ok = ok and e1f < TOL
+    print(f"rank {rank} R&G p2p unfused / fused again: hpsi err {e1u:.2e} {e1f:.2e}", flush=True)
     dist.barrier()
     hp.close()
     # ---- band groups: replicated data, column blocks, NCCL all-gather inside the library ----
