@@ -96,6 +96,23 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_set_qq(ctx, nat, nhm, qq_at) BIND(C, name='qeb_set_qq')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, qq_at; INTEGER(C_INT), VALUE :: nat, nhm
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_set_grid_dist(ctx, nr1, nr2, nr3, nproc, mype, nr3p, nsw, iss, ismap, nismap, ngm, nl, nlm, &
+                                              gamma_only) BIND(C, name='qeb_set_grid_dist')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, nr3p, nsw, iss, ismap, nl, nlm
+      INTEGER(C_INT), VALUE :: nr1, nr2, nr3, nproc, mype, nismap, ngm, gamma_only
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_nccl_unique_id(id128) BIND(C, name='qeb_nccl_unique_id')
+      IMPORT; TYPE(C_PTR), VALUE :: id128
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_nccl_init(ctx, role, id128, nranks, rank) BIND(C, name='qeb_nccl_init')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, id128; INTEGER(C_INT), VALUE :: role, nranks, rank
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_p2p_export(ctx, blob) BIND(C, name='qeb_p2p_export')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, blob
+    END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_p2p_import(ctx, blobs, nranks) BIND(C, name='qeb_p2p_import')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, blobs; INTEGER(C_INT), VALUE :: nranks
+    END FUNCTION
     INTEGER(C_INT) FUNCTION qeb_cegterg(ctx, npw, npwx, nvec, nvecx, npol, evc, ethr, uspp, e, btype, notcnv, lrot, &
                                         dav_iter, nhpsi) BIND(C, name='qeb_cegterg')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, evc, e, btype, notcnv, dav_iter, nhpsi
@@ -202,6 +219,41 @@ CONTAINS
   SUBROUTINE qeb200_touch_deeq();  deeq_version = deeq_version + 1; END SUBROUTINE
   SUBROUTINE qeb200_touch_kpoint(); k_set = -1; END SUBROUTINE   ! after init_us_2 when atoms move
 
+  SUBROUTINE qeb200_rg_communicator()
+    !! NCCL communicator of the R&G group (intra_bgrp_comm = dffts%comm): rank 0 makes the id, MPI broadcasts it
+    !! (qeb200.h: qeb_nccl_unique_id + qeb_nccl_init); used by the stick<->plane exchange fallback and by the becp
+    !! all-reduce (Modules/becmod.f90:395-399)
+    USE fft_base, ONLY: dffts
+    USE mp,       ONLY: mp_bcast
+    INTEGER(C_INT), TARGET :: id(32)          ! 128 bytes
+    id = 0
+    IF (dffts%mype == 0) CALL qeb200_check(qeb_nccl_unique_id(C_LOC(id)), 'qeb_nccl_unique_id')
+    CALL mp_bcast(id, 0, dffts%comm)
+    CALL qeb200_check(qeb_nccl_init(ctx, 1_C_INT, C_LOC(id), dffts%nproc, dffts%mype), 'qeb_nccl_init')   ! 1 = QEB_COMM_RG
+  END SUBROUTINE
+  SUBROUTINE qeb200_rg_peer_mapping()
+    !! Peer-to-peer exchange over NVLink for the ranks of one box (qeb_p2p_export -> all-gather of the 256-byte blobs in
+    !! rank order -> qeb_p2p_import -> barrier). QEB_P2P=0 in the environment keeps the NCCL exchange.
+    USE fft_base, ONLY: dffts
+    USE mp,       ONLY: mp_barrier
+#if defined(__MPI)
+    USE mpi
+#endif
+    INTEGER(C_INT8_T), ALLOCATABLE, TARGET :: blob(:), blobs(:)
+    INTEGER :: ierr
+    IF (dffts%nproc < 2) RETURN
+    ALLOCATE(blob(256), blobs(256 * dffts%nproc))
+    CALL qeb200_check(qeb_p2p_export(ctx, C_LOC(blob)), 'qeb_p2p_export')
+#if defined(__MPI)
+    CALL MPI_ALLGATHER(blob, 256, MPI_BYTE, blobs, 256, MPI_BYTE, dffts%comm, ierr)
+    IF (ierr /= 0) CALL errore('qeb200', 'MPI_Allgather of the peer blobs failed', ierr)
+#else
+    blobs(1:256) = blob
+#endif
+    CALL qeb200_check(qeb_p2p_import(ctx, C_LOC(blobs), dffts%nproc), 'qeb_p2p_import')
+    CALL mp_barrier(dffts%comm)
+    DEALLOCATE(blob, blobs)
+  END SUBROUTINE
   SUBROUTINE qeb200_sync_state()
     !! Pushes whatever module state changed since the last call into the context.
     USE fft_base,      ONLY: dffts
@@ -223,8 +275,16 @@ CONTAINS
       pnlm = C_NULL_PTR
       IF (gamma_only) pnlm = C_LOC(dffts%nlm)
       ig = 0; IF (gamma_only) ig = 1
-      CALL qeb200_check(qeb_set_grid(ctx, dffts%nr1, dffts%nr2, dffts%nr3, dffts%nr1x, dffts%nr2x, dffts%nr3x, &
-                        ngms, C_LOC(dffts%nl), pnlm, INT(ig, C_INT)), 'qeb_set_grid')
+      IF (dffts%lpara) THEN
+        ! slab-distributed dffts (fft_types.f90:35-185): the rank's descriptor + the R&G communicator (dffts%comm)
+        CALL qeb200_check(qeb_set_grid_dist(ctx, dffts%nr1, dffts%nr2, dffts%nr3, dffts%nproc, dffts%mype, &
+                          C_LOC(dffts%nr3p), C_LOC(dffts%nsw), C_LOC(dffts%iss), C_LOC(dffts%ismap), SIZE(dffts%ismap), &
+                          ngms, C_LOC(dffts%nl), pnlm, INT(ig, C_INT)), 'qeb_set_grid_dist')
+        CALL qeb200_rg_communicator()
+      ELSE
+        CALL qeb200_check(qeb_set_grid(ctx, dffts%nr1, dffts%nr2, dffts%nr3, dffts%nr1x, dffts%nr2x, dffts%nr3x, &
+                          ngms, C_LOC(dffts%nl), pnlm, INT(ig, C_INT)), 'qeb_set_grid')
+      END IF
       grid_set = .TRUE.
     END IF
     IF (k_set /= current_k) THEN
@@ -233,6 +293,8 @@ CONTAINS
       CALL qeb200_check(qeb_set_kpoint(ctx, ngk(current_k), npwx, pigk, C_LOC(g2kin), C_LOC(vkb), nkb, gstart), &
                         'qeb_set_kpoint')
       k_set = current_k
+      ! the exchange buffers are sized by qeb_set_kpoint: (re)publish them to the peers of the R&G group
+      IF (dffts%lpara) CALL qeb200_rg_peer_mapping()
     END IF
     IF (vloc_loaded /= vloc_version .OR. spin_loaded /= current_spin) THEN
       CALL qeb200_check(qeb_set_vloc(ctx, C_LOC(vrs(1, current_spin))), 'qeb_set_vloc')
@@ -336,8 +398,12 @@ CONTAINS
     USE ldaU,     ONLY: lda_plus_u
     USE bp,       ONLY: lelfield
     USE xc_lib,   ONLY: exx_is_active, xclib_dft_is
+    ! R&G-distributed grids: the slab decomposition (QE's default) is bound through qeb_set_grid_dist below; pencil
+    ! decomposition and task groups keep the reference routines
     qeb200_hpsi_supported = .NOT. (real_space .OR. dffts%has_task_groups .OR. lda_plus_u .OR. lelfield .OR. &
-                                   exx_is_active() .OR. xclib_dft_is('meta') .OR. dffts%lpara)
+                                   exx_is_active() .OR. xclib_dft_is('meta') .OR. &
+                                   (dffts%lpara .AND. (dffts%use_pencil_decomposition .OR. dffts%nr1x /= dffts%nr1 .OR. &
+                                                       dffts%nr2x /= dffts%nr2)))
   END FUNCTION
   SUBROUTINE qeb200_push_g_psi_diag(n, hd, sd)
     !! g_psi_mod::h_diag / s_diag of the current k-point -> context (PW/src/c_bands.f90 fills them before the solver)
