@@ -218,6 +218,13 @@ int qeb_dav_gemm_cn(qeb_ctx* ctx, int n, const void* A, int lda, int ka, const v
 int qeb_dav_gemm_nn(qeb_ctx* ctx, int n, const void* A, int lda, int k, const void* B, int ldb, int m, void* C,
                     int ldc, int accumulate);
 
+/* h_psi of nk k-points in one call: context k applies its Hamiltonian to psi[k] on its own stream and all streams are
+ * joined before the call returns (the k loop of PW/src/c_bands.f90:95-150; BASELINE configs 1-2 are launch-bound, so
+ * the k-points of a pool run concurrently). Repeated device-pointer calls of a context with unchanged state and
+ * arguments are replayed from a CUDA graph (one launch per h_psi; QEB_GRAPH=0 disables, =2 forces it for every size). */
+int qeb_h_psi_multi(int nk, qeb_ctx* const* ctxs, const int* lda, const int* n, const int* m, const void* const* psi,
+                    void* const* hpsi);
+
 /* ---- device-resident block-Davidson solver ----------------- */
 /* cegterg(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, npol, evc, ethr, e, btype, notcnv, lrot,
  *         dav_iter, nhpsi)                                 KS_Solvers/Davidson/cegterg.f90:18-700

@@ -6,6 +6,6 @@ entry points (h_psi, vloc_psi_k/gamma, invfft/fwfft, calbec, add_vuspsi) for
 Python callers, tests and the benchmark. There is no CPU fallback: creating a
 context without a CUDA device raises.
 """
-from .hpsi import (COMM_BGRP, COMM_RG, HPsi, QebError, allgather_columns, divide_all, lib_path,  # noqa: F401
+from .hpsi import (COMM_BGRP, COMM_RG, HPsi, QebError, allgather_columns, divide_all, h_psi_multi, lib_path,  # noqa: F401
                    load_library)
 from . import descriptor  # noqa: F401,E402

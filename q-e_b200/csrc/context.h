@@ -162,6 +162,17 @@ struct qeb_ctx {
     bool p2p_exported = false;
     std::vector<void*> p2p_opened;  // cudaIpcOpenMemHandle mappings to close
     qeb_solver_state* solver = nullptr;
+    // CUDA-graph replay of small h_psi calls (launch-bound k-points: SURVEY 7, BASELINE configs 1-2)
+    struct GraphEntry {
+        std::vector<unsigned long long> key;
+        cudaGraphExec_t exec = nullptr;
+        int seen = 0;
+    };
+    std::vector<GraphEntry> graphs;
+    std::vector<GraphEntry> mgraphs;     // qeb_h_psi_multi: all k-points of a call in ONE graph (kept in the first context)
+    cudaEvent_t mev[2] = {nullptr, nullptr};  // fork / join of this context's stream inside a multi-k capture
+    unsigned long long state_epoch = 0;  // bumped by every setter that changes what the kernels are launched with
+    int graph_mode = -1;                 // -1: automatic (small calls only), 0: off, 1: every device-pointer call
 };
 
 #define QEB_FAIL(ctx, code, msg)   \

@@ -56,6 +56,7 @@ def load_library():
     L.qeb_set_vloc.argtypes = [P, P]
     L.qeb_set_nonlocal.argtypes = [P, I, I, P, P, P]
     L.qeb_h_psi.argtypes = [P, I, I, I, P, P]
+    L.qeb_h_psi_multi.argtypes = [I, P, P, P, P, P, P]
     L.qeb_cegterg.argtypes = [P, I, I, I, I, I, P, ctypes.c_double, I, P, P, P, I, P, P]
     L.qeb_regterg.argtypes = [P, I, I, I, I, P, ctypes.c_double, I, P, P, P, I, P, P]
     L.qeb_vloc_psi_k.argtypes = [P, I, I, I, P, P, P]
@@ -136,7 +137,7 @@ def allgather_columns(hpsi, m: int, group=None):
 _CALLER_STREAMS = set()  # stream handles contexts were created on (HPsi(stream=...))
 
 
-def _ptr(a):
+def _ptr(a, sync=True):
     """address of a numpy array / torch tensor / None / int"""
     if a is None:
         return None
@@ -149,7 +150,7 @@ def _ptr(a):
     if hasattr(a, "data_ptr"):
         if not a.is_contiguous():
             raise QebError("tensor must be contiguous")
-        if getattr(a, "is_cuda", False):
+        if sync and getattr(a, "is_cuda", False):
             # The library's own streams are non-blocking: work the caller queued on torch's current stream (the fill or
             # the upload of this very tensor) is ordered before the library call here, as a Fortran caller's
             # synchronous host code is. A context created ON the caller's stream needs no such wait.
@@ -164,6 +165,23 @@ def _ptr(a):
 
 def _i32(a):
     return None if a is None else np.ascontiguousarray(a, dtype=np.int32)
+
+
+def h_psi_multi(ctxs, lda, n, m, psi, hpsi):
+    """qeb_h_psi_multi: one h_psi per context (k-point), all in flight together; lda/n/m ints or per-k lists; psi/hpsi lists
+    of device tensors (or host arrays)."""
+    nk = len(ctxs)
+    if nk == 0:
+        return hpsi
+    ilist = lambda v: (ctypes.c_int * nk)(*([v] * nk if isinstance(v, int) else list(v)))  # noqa: E731
+    hs = (ctypes.c_void_p * nk)(*[c._h.value for c in ctxs])
+    _ptr(psi[0])  # orders the caller's torch stream before the call, once for all k-points
+    pp = (ctypes.c_void_p * nk)(*[_ptr(a, sync=False).value for a in psi])
+    ph = (ctypes.c_void_p * nk)(*[_ptr(a, sync=False).value for a in hpsi])
+    L = ctxs[0]._L
+    rc = L.qeb_h_psi_multi(nk, hs, ilist(lda), ilist(n), ilist(m), pp, ph)
+    ctxs[0]._ck(rc, "qeb_h_psi_multi")
+    return hpsi
 
 
 class HPsi:
