@@ -113,6 +113,9 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_p2p_import(ctx, blobs, nranks) BIND(C, name='qeb_p2p_import')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, blobs; INTEGER(C_INT), VALUE :: nranks
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_hs_psi(ctx, lda, n, m, psi, hpsi, spsi) BIND(C, name='qeb_hs_psi')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, psi, hpsi, spsi; INTEGER(C_INT), VALUE :: lda, n, m
+    END FUNCTION
     INTEGER(C_INT) FUNCTION qeb_cegterg(ctx, npw, npwx, nvec, nvecx, npol, evc, ethr, uspp, e, btype, notcnv, lrot, &
                                         dav_iter, nhpsi) BIND(C, name='qeb_cegterg')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, evc, e, btype, notcnv, dav_iter, nhpsi
@@ -651,6 +654,48 @@ SUBROUTINE g_psi_qeb(lda, n, m, npol, psi, e)
   END IF
   CALL qeb200_check(qeb_g_psi(ctx, lda, n, m, npol, C_LOC(psi), C_LOC(e)), 'g_psi')
 END SUBROUTINE g_psi_qeb
+
+!----------------------------------------------------------------------------
+SUBROUTINE hs_psi_qeb(lda, n, m, psi, hpsi, spsi)
+  !! hs_psi(lda,n,m,psi,hpsi,spsi) (PW/src/hs_psi.f90:7): H and S on the same block, no band-group split; the scalar
+  !! (npol = 1) supported branches go to the library in one call, everything else through h_psi_qeb + s_psi_qeb
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE kinds,            ONLY: DP
+  USE noncollin_module, ONLY: npol, noncolin
+  USE becmod,           ONLY: becp
+  USE uspp,             ONLY: nkb
+  USE control_flags,    ONLY: gamma_only
+  USE qeb200_c
+  USE qeb200_state
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n, m
+  COMPLEX(DP), INTENT(IN),  TARGET :: psi(lda*npol, m)
+  COMPLEX(DP), INTENT(OUT), TARGET :: hpsi(lda*npol, m), spsi(lda*npol, m)
+  IF (noncolin .OR. .NOT. qeb200_hpsi_supported()) THEN
+    CALL h_psi_qeb(lda, n, m, psi, hpsi)
+    CALL s_psi_qeb(lda, n, m, psi, spsi)
+    RETURN
+  END IF
+  CALL qeb200_sync_state()
+  CALL qeb200_check(qeb_hs_psi(ctx, lda, n, m, C_LOC(psi), C_LOC(hpsi), C_LOC(spsi)), 'hs_psi')
+  IF (nkb > 0) THEN   ! becmod::becp as h_psi leaves it
+    IF (gamma_only) THEN
+      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%r), m), 'hs_psi')
+    ELSE
+      CALL qeb200_check(qeb_get_becp(ctx, C_LOC(becp%k), m), 'hs_psi')
+    END IF
+  END IF
+END SUBROUTINE hs_psi_qeb
+
+SUBROUTINE hs_1psi_qeb(lda, n, psi, hpsi, spsi)
+  !! hs_1psi(lda,n,psi,hpsi,spsi) (PW/src/hs_1psi.f90:7): one band
+  USE kinds,            ONLY: DP
+  USE noncollin_module, ONLY: npol
+  IMPLICIT NONE
+  INTEGER, INTENT(IN) :: lda, n
+  COMPLEX(DP) :: psi(lda*npol, 1), hpsi(lda*npol, 1), spsi(lda*npol, 1)
+  CALL hs_psi_qeb(lda, n, 1, psi, hpsi, spsi)
+END SUBROUTINE hs_1psi_qeb
 
 !----------------------------------------------------------------------------
 SUBROUTINE cegterg_qeb(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, npol, evc, ethr, e, btype, &

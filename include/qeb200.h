@@ -218,6 +218,10 @@ int qeb_dav_gemm_cn(qeb_ctx* ctx, int n, const void* A, int lda, int ka, const v
 int qeb_dav_gemm_nn(qeb_ctx* ctx, int n, const void* A, int lda, int k, const void* B, int ldb, int m, void* C,
                     int ldc, int accumulate);
 
+/* hs_psi(lda,n,m,psi,hpsi,spsi)  PW/src/hs_psi.f90:7-40;  hs_1psi(lda,n,psi,hpsi,spsi)  PW/src/hs_1psi.f90:7-60 (m = 1):
+ * H and S applied to the same block (the callers are the CG / PPCG / ParO solvers); S re-uses the becp of H. */
+int qeb_hs_psi(qeb_ctx* ctx, int lda, int n, int m, const void* psi, void* hpsi, void* spsi);
+
 /* h_psi of nk k-points in one call: context k applies its Hamiltonian to psi[k] on its own stream and all streams are
  * joined before the call returns (the k loop of PW/src/c_bands.f90:95-150; BASELINE configs 1-2 are launch-bound, so
  * the k-points of a pool run concurrently). Repeated device-pointer calls of a context with unchanged state and

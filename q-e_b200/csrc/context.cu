@@ -876,9 +876,9 @@ int qeb_sum_band_rho(qeb_ctx* c, int lda, int n, int m, const void* evc, const d
     int rc = check_call(c, lda, n, m, evc, rho, "qeb_sum_band_rho");
     if (rc) return rc;
     if (!w) QEB_FAIL(c, 97, "qeb_sum_band_rho: null weights");
-    if (c->dist) QEB_FAIL(c, 97, "qeb_sum_band_rho: the slab-distributed descriptor is not supported yet");
     if (m == 0) return 0;
-    const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
+    // slab-distributed descriptor: rho holds the rank's own z planes (dffts%nr3p(mype) of them), as in the reference
+    const size_t nnr = (size_t)c->nr1 * c->nr2 * (c->dist ? c->Tp.nr3 : c->nr3);
     const void* psi_d;
     if ((rc = stage_in(c, evc, (size_t)lda * m * 16, c->psi_stage, &psi_d))) return rc;
     const void* w_d;
@@ -902,7 +902,48 @@ int qeb_sum_band_rho(qeb_ctx* c, int lda, int n, int m, const void* evc, const d
     for (int b0 = 0; b0 < nboxes; b0 += c->batch) {  // one stream: batches add to the same rho
         const int nb = std::min(c->batch, nboxes - b0);
         io.band0 = c->gamma ? 2 * b0 : b0;
-        QEB_CUDA(c, vloc_launch_density(c->T, io, c->cfg, nb, (const double*)w_d, r, c->stream));
+        if (!c->dist) {
+            QEB_CUDA(c, vloc_launch_density(c->T, io, c->cfg, nb, (const double*)w_d, r, c->stream));
+            continue;
+        }
+        // wave_g2r on the distributed grid (fft_parallel_2d.f90:36-204): z pass on the own sticks, stick -> plane
+        // exchange, then y pass and |psi(r)|^2 accumulation on the own planes (exchange slot 0, the main stream)
+        const DistHost& D = c->DH;
+        const bool p2p = c->P2P.ok && D.nproc > 1;
+        if (D.nproc > 1 && !c->nccl_rg && !p2p)
+            QEB_FAIL(c, 53, "qeb_sum_band_rho: no NCCL communicator (qeb_nccl_init) or peer mapping (qeb_p2p_import) for the R&G group");
+        cudaStream_t st = c->stream;
+        cplx* S = (cplx*)c->sbuf_d.p;
+        cplx* R = (cplx*)c->rbuf_d.p;
+        VlocTables tz = c->T;
+        tz.g1 = S;
+        tz.g1_zs = (size_t)nb * tz.g1_box;
+        VlocTables tp = c->Tp;
+        const char* msg = "";
+        if (p2p && D.nproc <= 16) {  // fused forward leg, as in run_vloc
+            tz.peer_on = 1;
+            tz.peer_nb = nb;
+            tz.peer_zown = c->fx_zown;
+            tz.peer_zi0 = c->fx_zi0;
+            for (int q = 0; q < D.nproc; ++q)
+                tz.peer_base[q] = c->P2P.peer_R[q] + (size_t)nb * D.nr3p[q] * D.prefix[D.me];
+            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
+            if ((rc = dist_p2p_sync(D, c->P2P, true, 0, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            tp.g1 = R;
+            tp.r_on = 1;
+            tp.r_nb = nb;
+            tp.r_pref = c->fx_rpref;
+            tp.r_nsw = c->fx_rnsw;
+            tp.r_sidx = c->DD.sidx;
+            QEB_CUDA(c, vloc_launch_density(tp, io, c->cfgp, nb, (const double*)w_d, r, st, true));
+            // no data flows back: the backward flag words only tell the peers that this rank has consumed its R slice
+            if ((rc = dist_p2p_sync(D, c->P2P, false, 0, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+        } else {
+            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
+            if ((rc = dist_exchange(D, c->nccl_rg, true, S, R, nb, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
+            QEB_CUDA(c, dist_unpack(c->DD, R, tp.g1, nb, st));
+            QEB_CUDA(c, vloc_launch_density(tp, io, c->cfgp, nb, (const double*)w_d, r, st, true));
+        }
     }
     if (!rho_dev) {
         QEB_CUDA(c, cudaMemcpyAsync(rho, r, nnr * 8, cudaMemcpyDeviceToHost, c->stream));
@@ -1540,6 +1581,17 @@ int qeb_h_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
         return 0;
     }
     return finish(c);
+}
+
+// hs_psi(lda,n,m,psi,hpsi,spsi) (PW/src/hs_psi.f90:7-40) and, with m = 1, hs_1psi (PW/src/hs_1psi.f90:7-60): H and S on
+// the same block, S re-using the projections H just left in the context.
+int qeb_hs_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi, void* spsi)
+{
+    if (!c) return 1;
+    if (!spsi) QEB_FAIL(c, 62, "qeb_hs_psi: bad arguments");
+    const int rc = qeb_h_psi(c, lda, n, m, psi, hpsi);
+    if (rc) return rc;
+    return qeb_s_psi(c, lda, n, m, psi, spsi);
 }
 
 // h_psi of several k-points in one call (the k loop of PW/src/c_bands.f90:95-150 for the launch-bound configs): context

@@ -320,11 +320,11 @@ cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr
 }
 
 cudaError_t vloc_launch_density(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
-                                const double* w_dev, double* rho_dev, cudaStream_t st)
+                                const double* w_dev, double* rho_dev, cudaStream_t st, bool planes_only)
 {
     if (nboxes <= 0 || t.nxw <= 0) return cudaSuccess;
     cudaError_t e;
-    if ((e = vloc_launch_zpass(true, t, io, cfg, nboxes, st)) != cudaSuccess) return e;
+    if (!planes_only && (e = vloc_launch_zpass(true, t, io, cfg, nboxes, st)) != cudaSuccess) return e;
     if (!launch_y(true, t, cfg, nboxes, st))
         k_vloc_yinv<<<dim3(t.nty, t.nxw, nboxes), cfg.threads_y, cfg.smem_y, st>>>(t);
     const size_t smem = cfg.smem_x + (size_t)t.nr1 * t.TX * 8 + (size_t)t.nr1 * 4 + 16;

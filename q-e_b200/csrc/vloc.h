@@ -29,8 +29,9 @@ cudaError_t vloc_prepare_v(const double* v, double* vp, const int* rev_x, int nr
                            cudaStream_t st);
 // sum_band density accumulation for one batch: scatter + z inverse, y inverse, x inverse + rho += w |psi(r)|^2
 // (w_dev: the m band weights wg/omega on the device, indexed by io.band0 + box; rho_dev: nr1*nr2*nr3, x fastest)
+// planes_only: the y and x passes alone (slab-distributed path: the z pass and the exchange ran before, t = plane tables)
 cudaError_t vloc_launch_density(const VlocTables& t, const VlocIO& io, const VlocLaunchCfg& cfg, int nboxes,
-                                const double* w_dev, double* rho_dev, cudaStream_t st);
+                                const double* w_dev, double* rho_dev, cudaStream_t st, bool planes_only = false);
 // plane-kernel layout of the potential: vpl[(z*nr1 + xpos)*nr2 + ypos] = v[rev_x[xpos] + nr1*(rev_y[ypos] + nr2*z)] * scale
 cudaError_t vloc_prepare_v_plane(const double* v, double* vpl, const int* rev_x, const int* rev_y, int nr1, int nr2,
                                  int nr3, double scale, cudaStream_t st);

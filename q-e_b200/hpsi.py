@@ -57,6 +57,7 @@ def load_library():
     L.qeb_set_nonlocal.argtypes = [P, I, I, P, P, P]
     L.qeb_h_psi.argtypes = [P, I, I, I, P, P]
     L.qeb_h_psi_multi.argtypes = [I, P, P, P, P, P, P]
+    L.qeb_hs_psi.argtypes = [P, I, I, I, P, P, P]
     L.qeb_cegterg.argtypes = [P, I, I, I, I, I, P, ctypes.c_double, I, P, P, P, I, P, P]
     L.qeb_regterg.argtypes = [P, I, I, I, I, P, ctypes.c_double, I, P, P, P, I, P, P]
     L.qeb_vloc_psi_k.argtypes = [P, I, I, I, P, P, P]
@@ -412,6 +413,11 @@ class HPsi:
     def h_psi(self, lda, n, m, psi, hpsi):
         self._ck(self._L.qeb_h_psi(self._h, lda, n, m, _ptr(psi), _ptr(hpsi)), "qeb_h_psi")
         return hpsi
+
+    def hs_psi(self, lda, n, m, psi, hpsi, spsi):
+        """hs_psi(lda,n,m,psi,hpsi,spsi) (PW/src/hs_psi.f90:7); m = 1 is hs_1psi (PW/src/hs_1psi.f90:7)"""
+        self._ck(self._L.qeb_hs_psi(self._h, lda, n, m, _ptr(psi), _ptr(hpsi), _ptr(spsi)), "qeb_hs_psi")
+        return hpsi, spsi
 
     def h_psi_bgrp(self, lda, n, m, psi, hpsi, nbgrp, my_bgrp):
         self._ck(self._L.qeb_h_psi_bgrp(self._h, lda, n, m, _ptr(psi), _ptr(hpsi), nbgrp, my_bgrp), "qeb_h_psi_bgrp")

@@ -97,6 +97,22 @@ def main():
     e1f = float((np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max(axis=1) / np.abs(ref).max(axis=1)).max())
     ok = ok and e1f < TOL
     print(f"rank {rank} R&G p2p unfused / fused again: hpsi err {e1u:.2e} {e1f:.2e}", flush=True)
+    # sum_band density on the distributed descriptor (peer-to-peer exchange): this rank's z planes of the serial density
+    rngw = np.random.default_rng(17)
+    w = rngw.uniform(0.0, 2.0, m)
+    rho_ref = R.sum_band_rho(d, inp["lda"], n, m, inp["psi"], w, np.zeros(d.nnr)).reshape(d.nr3, d.nr2 * d.nr1)
+    z0 = int(np.sum(dd.nr3p[:rank]))
+    nzl = int(dd.nr3p[rank])
+    for rep in range(2):
+        rho = np.zeros(d.nr1 * d.nr2 * nzl)
+        hp.sum_band_rho(lda, rk.npw, m, np.nan_to_num(psi_l), w, rho)
+        er = float(np.abs(rho.reshape(nzl, -1) - rho_ref[z0:z0 + nzl]).max() / np.abs(rho_ref).max())
+        ok = ok and er < 1e-12
+    print(f"rank {rank} sum_band density on the slab descriptor: err {er:.2e}", flush=True)
+    out = np.full((m, lda), np.nan + 1j * np.nan)
+    hp.h_psi(lda, rk.npw, m, psi_l, out)  # the V_loc exchange still lines up after the one-way density exchange
+    e1d = float((np.abs(out[:, :rk.npw] - ref[:, rk.pw_l2g]).max(axis=1) / np.abs(ref).max(axis=1)).max())
+    ok = ok and e1d < TOL
     dist.barrier()
     hp.close()
     # ---- band groups: replicated data, column blocks, NCCL all-gather inside the library ----

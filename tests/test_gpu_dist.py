@@ -56,6 +56,14 @@ def test_dist_single_rank(mods, name, m, batch):
     assert _colerr(out[:, :rk.npw], ref[:, rk.pw_l2g]) < TOL
     assert np.all(out[:, rk.npw:] == 0)
     assert _colerr(h.get_becp(m), becp_ref) < TOL
+    # density part of sum_band on the distributed descriptor: the rank's own z planes (here: all of them)
+    rng = np.random.default_rng(3)
+    w = rng.uniform(0.0, 2.0, m)
+    rho0 = rng.uniform(0.0, 1.0, d.nnr)
+    rho_ref = R.sum_band_rho(d, inp["lda"], n, m, inp["psi"], w, rho0.copy())
+    rho = rho0.copy()
+    h.sum_band_rho(lda, rk.npw, m, np.nan_to_num(psi_l), w, rho)
+    assert np.abs(rho - rho_ref).max() / np.abs(rho_ref).max() < 1e-12
     h.close()
 
 

@@ -540,6 +540,29 @@ def test_h_psi_without_state_fails(mods):
     h.close()
 
 
+@pytest.mark.parametrize("name", ["si2_small", "si2_small_gamma"])
+def test_hs_psi_and_hs_1psi(mods, name):
+    """hs_psi / hs_1psi (PW/src/hs_psi.f90:7, hs_1psi.f90:7): H and S of the same block in one call"""
+    qe, D, R, torch = mods
+    d = D.config_descriptor(name)
+    m = 3
+    inp = R.synthetic_inputs(d, m, [4, 4], seed=23, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    qq = R.synthetic_qq([4, 4], seed=23)
+    h = qe.HPsi()
+    h.setup_from(d, inp)
+    h.set_qq(qq)
+    href, becp = R.h_psi(d, lda, n, m, inp["psi"], inp["vrs"], inp["vkb"], inp["deeq"], inp["nh_at"], inp["ofsbeta"])
+    sref = R.s_psi(d, lda, n, m, inp["psi"], becp, inp["vkb"], qq, inp["nh_at"], inp["ofsbeta"])
+    hp, sp = np.full_like(inp["psi"], np.nan), np.full_like(inp["psi"], np.nan)
+    h.hs_psi(lda, n, m, inp["psi"], hp, sp)
+    assert relerr(hp[:, :n], href[:, :n]) < TOL and relerr(sp[:, :n], sref[:, :n]) < TOL
+    h1, s1 = np.full_like(inp["psi"][:1], np.nan), np.full_like(inp["psi"][:1], np.nan)
+    h.hs_psi(lda, n, 1, inp["psi"][1:2].copy(), h1, s1)  # hs_1psi
+    assert relerr(h1[:, :n], href[1:2, :n]) < TOL and relerr(s1[:, :n], sref[1:2, :n]) < TOL
+    h.close()
+
+
 @pytest.mark.parametrize("name", ["ortho_small", "ortho_small_gamma"])
 def test_davidson_building_blocks(mods, name):
     """the device pieces of cegterg/regterg - reduced matrices psi^H hpsi (cegterg.f90:209, regterg.f90:203-205),
