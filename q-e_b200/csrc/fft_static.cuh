@@ -112,7 +112,7 @@ QEB_HD void spass(int warp, int nwarps, int lane_, int nl, const cplx* tw, doubl
 #pragma unroll
             for (int b = 0; b < R; ++b) v[b] = src.load(lane, base + A * b);
         }
-        if (DIT && A > 1) {
+        if (DIT && A > 1 && a != 0) {  // a == 0: every twiddle is 1 (warp-uniform test)
             const int st = a * NB;
 #pragma unroll
             for (int b = 1; b < R; ++b) v[b] = cmul(v[b], stw(tw, st * b, sgn));
@@ -123,7 +123,7 @@ QEB_HD void spass(int warp, int nwarps, int lane_, int nl, const cplx* tw, doubl
             for (int d = 0; d < R; ++d) v[d] = scal(v[d], f[d]);
             Bfly<R>::run(v, -sgn);
         }
-        if (!DIT && !FUSE2 && A > 1) {
+        if (!DIT && !FUSE2 && A > 1 && a != 0) {
             const int st = a * NB;
 #pragma unroll
             for (int d = 1; d < R; ++d) v[d] = cmul(v[d], stw(tw, st * d, sgn));

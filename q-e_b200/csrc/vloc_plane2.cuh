@@ -76,13 +76,13 @@ QEB_HD void p2_bfly_y(int j, bool active, int lane_col, int nxw, const cplx* tw,
 #pragma unroll
         for (int b = 0; b < R; ++b) v[b] = c[(A * b) * LDP];
     }
-    if (DIT && A > 1) {
+    if (DIT && A > 1 && a != 0) {  // a == 0: every twiddle is 1 (warp-uniform test)
         const int st = a * NB;
 #pragma unroll
         for (int b = 1; b < R; ++b) v[b] = cmul(v[b], stw(tw, st * b, sgn));
     }
     Bfly<R>::run(v, sgn);
-    if (!DIT && A > 1) {
+    if (!DIT && A > 1 && a != 0) {
         const int st = a * NB;
 #pragma unroll
         for (int d = 1; d < R; ++d) v[d] = cmul(v[d], stw(tw, st * d, sgn));
@@ -134,7 +134,7 @@ QEB_HD void p2_bfly_x(int j, bool active, const cplx* tw, cplx* row, const int* 
 #pragma unroll
         for (int b = 0; b < R; ++b) v[b] = r[A * b];
     }
-    if (DIT && A > 1) {
+    if (DIT && A > 1 && a != 0) {  // a == 0: every twiddle is 1 (warp-uniform test)
         const int st = a * NB;
 #pragma unroll
         for (int b = 1; b < R; ++b) v[b] = cmul(v[b], stw(tw, st * b, sgn));
@@ -145,7 +145,7 @@ QEB_HD void p2_bfly_x(int j, bool active, const cplx* tw, cplx* row, const int* 
         for (int d = 0; d < R; ++d) v[d] = scal(v[d], f[d]);
         Bfly<R>::run(v, -sgn);
     }
-    if (KIND == 0 && A > 1) {
+    if (KIND == 0 && A > 1 && a != 0) {
         const int st = a * NB;
 #pragma unroll
         for (int d = 1; d < R; ++d) v[d] = cmul(v[d], stw(tw, st * d, sgn));
