@@ -208,7 +208,9 @@ __global__ void __launch_bounds__(QEB_FAST_MAXTHREADS) k_vloc_xacc_f(const __gri
 {
     QEB_SMEM;
     double* racc = reinterpret_cast<double*>(smem + (size_t)t.nr1 * t.TX);
-    cplx* twS = reinterpret_cast<cplx*>(racc + (size_t)t.nr1 * t.TX);
+    // (the accumulator is padded to an even count: nr1 * TX is odd for an odd grid with an odd tile, e.g. the one-plane
+    // rank of a 15^3 grid distributed over 8 ranks, and the complex twiddles behind it need 16-byte alignment)
+    cplx* twS = reinterpret_cast<cplx*>(racc + (((size_t)t.nr1 * t.TX + 1) & ~(size_t)1));
     int* tabS = reinterpret_cast<int*>(twS + PL::N);
     int* irev = tabS + PL::N;
     for (int i = threadIdx.x; i < PL::N; i += blockDim.x) {
@@ -348,7 +350,7 @@ void FastLaunch<PL>::xacc(const VlocTables& t, const VlocIO& io, const VlocLaunc
                           double* rho, cudaStream_t st)
 {
     const int nw = env_int("QEB_NWX", pick_warps<PL>(4, 10));
-    const size_t smem = cfg.smem_x + (size_t)t.nr1 * t.TX * 8 + PL::N * 24 + 16;
+    const size_t smem = cfg.smem_x + (size_t)t.nr1 * t.TX * 8 + PL::N * 24 + 32;
     // box chunks: enough CTAs for ~4 waves of the resident slots
     int per_sm = (int)(cfg.max_smem / smem);
     if (per_sm < 1) per_sm = 1;

@@ -72,7 +72,14 @@ def _run_worker(nproc, name, m):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr",
            "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "dist_worker.py"), name, str(m)]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
-    return r.returncode, r.stdout + r.stderr
+    out = r.stdout + r.stderr
+    try:  # post-mortem copy (gpurun brings gpurun_out/ back)
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", f"dist_worker_{name}_n{nproc}.log"), "w") as f:
+            f.write(out)
+    except OSError:
+        pass
+    return r.returncode, out
 
 
 @pytest.mark.parametrize("name,m", [("ortho_small", 5), ("ortho_small_gamma", 5), ("si2_small_gamma", 3), ("si512", 5),
@@ -89,4 +96,5 @@ def test_dist_multi_gpu(mods, name, m):
     while d.nr3 < nproc:  # every rank needs a plane (fft_types.f90:633-635)
         nproc //= 2
     rc, out = _run_worker(nproc, name, m)
-    assert rc == 0 and "DIST_OK" in out, out[-3000:]
+    lines = [ln for ln in out.splitlines() if ("rank" in ln and "err" in ln) or "Error" in ln or "failed" in ln]
+    assert rc == 0 and "DIST_OK" in out, "\n".join(lines[-40:]) + "\n" + out[-1500:]
