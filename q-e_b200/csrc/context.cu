@@ -1,12 +1,14 @@
-// C ABI of the qeb200 library (include/qeb200.h): explicit context replacing
-// the Fortran module state h_psi reads, host/device pointer
-// handling, and the orchestration of the V_loc passes and projector GEMMs in
-// the reference's order (PW/src/h_psi.f90:138-147 kinetic, :180/:220 V_loc,
-// :229-236 nonlocal, :294-295 Gamma fix).
+// libqeb200, translation unit 1 of 6: the context behind the C ABI (include/qeb200.h) - lifetime, the setters that replace
+// the Fortran module state h_psi reads, table upload, workspace sizing, and the device-side producers of the
+// per-k-point state (g2_kin, init_us_2). The operators live in operators.cu, the host-array pipeline in pipeline.cu,
+// CUDA-graph replay / multi-k in graphs.cu, NCCL / peer mapping / band groups in multigpu.cu, the Davidson pieces in
+// dav_blocks.cu and solver.cu.
 #include "context.h"
 
+extern "C" {
+
 // returns a device pointer for `p` (copying host data into `stage` if needed)
-static int stage_in(qeb_ctx* c, const void* p, size_t bytes, DevBuf& stage, const void** out)
+int stage_in(qeb_ctx* c, const void* p, size_t bytes, DevBuf& stage, const void** out)
 {
     if (is_device_ptr(p)) {
         *out = p;
@@ -18,7 +20,6 @@ static int stage_in(qeb_ctx* c, const void* p, size_t bytes, DevBuf& stage, cons
     return 0;
 }
 
-extern "C" {
 
 const char* qeb_version(void) { return "qeb200 0.1 (sm_100a; FP64 DMMA projectors; radix-2/3/5 pencil FFT)"; }
 
@@ -567,7 +568,7 @@ int qeb_set_kpoint(qeb_ctx* c, int npw, int npwx, const int* igk, const double* 
     return 0;
 }
 
-static int prepare_v(qeb_ctx* c, const double* v)
+int prepare_v(qeb_ctx* c, const double* v)
 {
     // distributed: v holds the rank's own z planes (dffts%nnr points of the slab, x fastest)
     const int nz = c->dist ? c->DH.nr3p[c->DH.me] : c->nr3;
@@ -606,7 +607,7 @@ int qeb_set_vloc(qeb_ctx* c, const double* vrs)
 }
 
 // v(dffts%nnr, 4) of vloc_psi_nc (PW/src/vloc_psi_acc.f90:291): four consecutive arrays, each permuted like vp
-static int prepare_v_nc(qeb_ctx* c, const double* v4)
+int prepare_v_nc(qeb_ctx* c, const double* v4)
 {
     const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
     const void* vd = nullptr;
@@ -863,1307 +864,6 @@ int qeb_init_us_2(qeb_ctx* c, const double* q, double tpiba, void* vkb_out)
                                     is_device_ptr(vkb_out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
     QEB_CUDA(c, cudaStreamSynchronize(c->stream));  // host staging vectors go out of scope
     return 0;
-}
-
-// sum_band, density part (PW/src/sum_band.f90:326-437 Gamma, :440-647 k): rho(r) += sum_b w_b |psi_b(r)|^2 for the
-// m bands of evc, w_b = wg(b,ik)/omega. The reference loops wave_g2r + get_rho_k/get_rho_gamma per band (group);
-// here: scatter + z pass, y pass, then one kernel that x-transforms every box of a batch and accumulates.
-static int check_call(qeb_ctx* c, int lda, int n, int m, const void* psi, const void* hpsi, const char* who);
-int qeb_sum_band_rho(qeb_ctx* c, int lda, int n, int m, const void* evc, const double* w, double* rho)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, evc, rho, "qeb_sum_band_rho");
-    if (rc) return rc;
-    if (!w) QEB_FAIL(c, 97, "qeb_sum_band_rho: null weights");
-    if (m == 0) return 0;
-    // slab-distributed descriptor: rho holds the rank's own z planes (dffts%nr3p(mype) of them), as in the reference
-    const size_t nnr = (size_t)c->nr1 * c->nr2 * (c->dist ? c->Tp.nr3 : c->nr3);
-    const void* psi_d;
-    if ((rc = stage_in(c, evc, (size_t)lda * m * 16, c->psi_stage, &psi_d))) return rc;
-    const void* w_d;
-    if ((rc = stage_in(c, w, (size_t)m * 8, c->wts_d, &w_d))) return rc;
-    const bool rho_dev = is_device_ptr(rho);
-    double* r = rho;
-    if (!rho_dev) {
-        QEB_CUDA(c, c->rho_d.ensure(nnr * 8));
-        r = (double*)c->rho_d.p;
-        QEB_CUDA(c, cudaMemcpyAsync(r, rho, nnr * 8, cudaMemcpyHostToDevice, c->stream));
-    }
-    VlocIO io;
-    io.psi = (const cplx*)psi_d;
-    io.hpsi = nullptr;
-    io.g2kin = nullptr;
-    io.lda = lda;
-    io.n = n;
-    io.nbands = m;
-    io.gamma = c->gamma ? 1 : 0;
-    const int nboxes = c->gamma ? (m + 1) / 2 : m;
-    for (int b0 = 0; b0 < nboxes; b0 += c->batch) {  // one stream: batches add to the same rho
-        const int nb = std::min(c->batch, nboxes - b0);
-        io.band0 = c->gamma ? 2 * b0 : b0;
-        if (!c->dist) {
-            QEB_CUDA(c, vloc_launch_density(c->T, io, c->cfg, nb, (const double*)w_d, r, c->stream));
-            continue;
-        }
-        // wave_g2r on the distributed grid (fft_parallel_2d.f90:36-204): z pass on the own sticks, stick -> plane
-        // exchange, then y pass and |psi(r)|^2 accumulation on the own planes (exchange slot 0, the main stream)
-        const DistHost& D = c->DH;
-        const bool p2p = c->P2P.ok && D.nproc > 1;
-        if (D.nproc > 1 && !c->nccl_rg && !p2p)
-            QEB_FAIL(c, 53, "qeb_sum_band_rho: no NCCL communicator (qeb_nccl_init) or peer mapping (qeb_p2p_import) for the R&G group");
-        cudaStream_t st = c->stream;
-        cplx* S = (cplx*)c->sbuf_d.p;
-        cplx* R = (cplx*)c->rbuf_d.p;
-        VlocTables tz = c->T;
-        tz.g1 = S;
-        tz.g1_zs = (size_t)nb * tz.g1_box;
-        VlocTables tp = c->Tp;
-        const char* msg = "";
-        if (p2p && D.nproc <= 16) {  // fused forward leg, as in run_vloc
-            tz.peer_on = 1;
-            tz.peer_nb = nb;
-            tz.peer_zown = c->fx_zown;
-            tz.peer_zi0 = c->fx_zi0;
-            for (int q = 0; q < D.nproc; ++q)
-                tz.peer_base[q] = c->P2P.peer_R[q] + (size_t)nb * D.nr3p[q] * D.prefix[D.me];
-            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
-            if ((rc = dist_p2p_sync(D, c->P2P, true, 0, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-            tp.g1 = R;
-            tp.r_on = 1;
-            tp.r_nb = nb;
-            tp.r_pref = c->fx_rpref;
-            tp.r_nsw = c->fx_rnsw;
-            tp.r_sidx = c->DD.sidx;
-            QEB_CUDA(c, vloc_launch_density(tp, io, c->cfgp, nb, (const double*)w_d, r, st, true));
-            // no data flows back: the backward flag words only tell the peers that this rank has consumed its R slice
-            if ((rc = dist_p2p_sync(D, c->P2P, false, 0, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-        } else {
-            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
-            if ((rc = dist_exchange(D, c->nccl_rg, true, S, R, nb, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-            QEB_CUDA(c, dist_unpack(c->DD, R, tp.g1, nb, st));
-            QEB_CUDA(c, vloc_launch_density(tp, io, c->cfgp, nb, (const double*)w_d, r, st, true));
-        }
-    }
-    if (!rho_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(rho, r, nnr * 8, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    if (!is_device_ptr(evc) || !is_device_ptr(w)) QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return finish(c);
-}
-
-// ---- block-Davidson building blocks ---------------------------
-int qeb_set_g_psi_diag(qeb_ctx* c, int n, const double* h_diag, const double* s_diag)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (n < 1 || !h_diag || !s_diag) QEB_FAIL(c, 90, "qeb_set_g_psi_diag: bad arguments");
-    QEB_CUDA(c, c->gpsi_d.ensure((size_t)n * 16));
-    QEB_CUDA(c, cudaMemcpyAsync(c->gpsi_d.p, h_diag, (size_t)n * 8,
-                                is_device_ptr(h_diag) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    QEB_CUDA(c, cudaMemcpyAsync((double*)c->gpsi_d.p + n, s_diag, (size_t)n * 8,
-                                is_device_ptr(s_diag) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->gpsi_n = n;
-    return 0;
-}
-
-int qeb_g_psi(qeb_ctx* c, int lda, int n, int m, int npol, void* psi, const double* e)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (npol != 1) QEB_FAIL(c, 91, "qeb_g_psi: npol = 2 (noncollinear) is routed to the reference routine by the shim");
-    if (n < 1 || lda < n || m < 0 || !psi || !e) QEB_FAIL(c, 91, "qeb_g_psi: bad arguments");
-    if (c->gpsi_n < n) QEB_FAIL(c, 92, "qeb_g_psi: qeb_set_g_psi_diag has not been called for this n");
-    if (!is_device_ptr(psi)) QEB_FAIL(c, 93, "qeb_g_psi: psi must be a device pointer (the Davidson work arrays live on the device)");
-    if (m == 0) return 0;
-    const void* ed;
-    int rc = stage_in(c, e, (size_t)m * 8, c->dav_small_d, &ed);
-    if (rc) return rc;
-    QEB_CUDA(c, launch_g_psi(lda, n, m, (cplx*)psi, (const double*)ed, (const double*)c->gpsi_d.p,
-                             (const double*)c->gpsi_d.p + c->gpsi_n, c->stream));
-    if (!is_device_ptr(e)) QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return finish(c);
-}
-
-int qeb_col_dot(qeb_ctx* c, int n, int m, const void* a, int lda, const void* b, int ldb, double* out)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (n < 1 || m < 0 || lda < n || ldb < n || !a || !b || !out) QEB_FAIL(c, 94, "qeb_col_dot: bad arguments");
-    if (!is_device_ptr(a) || !is_device_ptr(b)) QEB_FAIL(c, 93, "qeb_col_dot: a and b must be device pointers");
-    if (m == 0) return 0;
-    const bool od = is_device_ptr(out);
-    double* o = out;
-    if (!od) {
-        QEB_CUDA(c, c->dav_small_d.ensure((size_t)m * 8));
-        o = (double*)c->dav_small_d.p;
-    }
-    QEB_CUDA(c, launch_col_dot(n, m, (const cplx*)a, lda, (const cplx*)b, ldb, c->gamma ? 1 : 0, c->gstart, o, c->stream));
-    if (!od) {
-        QEB_CUDA(c, cudaMemcpyAsync(out, o, (size_t)m * 8, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-// C(ka,mb) = A(1:n,1:ka)^H B(1:n,1:mb): the reduced matrices hc/sc of cegterg (ZGEMM 'C','N', cegterg.f90:209-229,
-// 478-499) and hr/sr of regterg (2*DGEMM('T','N') - DGER at G=0, regterg.f90:203-221, 402-429) on the calbec kernel.
-int qeb_dav_gemm_cn(qeb_ctx* c, int n, const void* A, int lda, int ka, const void* B, int ldb, int mb, void* C, int ldc)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->have_grid) QEB_FAIL(c, 95, "qeb_dav_gemm_cn: qeb_set_grid has not been called (gamma_only / gstart are context state)");
-    if (n < 1 || lda < n || ldb < n || ka < 0 || mb < 0 || ldc < ka || !A || !B || !C) QEB_FAIL(c, 95, "qeb_dav_gemm_cn: bad arguments");
-    if (!is_device_ptr(A) || !is_device_ptr(B)) QEB_FAIL(c, 93, "qeb_dav_gemm_cn: A and B must be device pointers");
-    if (ka == 0 || mb == 0) return 0;
-    const size_t el = c->gamma ? 8 : 16;
-    int nsplit, gchunk;
-    calbec_plan(n, ka, mb, !c->gamma, c->num_sms, &nsplit, &gchunk);
-    QEB_CUDA(c, c->part_d.ensure(calbec_workspace_bytes(ka, mb, nsplit, !c->gamma)));
-    QEB_CUDA(c, c->misc_stage.ensure((size_t)ka * mb * el));
-    QEB_CUDA(c, launch_calbec((const cplx*)A, lda, (const cplx*)B, ldb, n, ka, mb, !c->gamma, c->gstart, nsplit, gchunk,
-                              c->part_d.p, c->misc_stage.p, c->stream));
-    QEB_CUDA(c, cudaMemcpy2DAsync(C, (size_t)ldc * el, c->misc_stage.p, (size_t)ka * el, (size_t)ka * el, mb,
-                                  is_device_ptr(C) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
-    if (!is_device_ptr(C)) {
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-// C(1:n,1:m) (+)= A(1:n,1:k) B(1:k,1:m): the basis updates of cegterg (ZGEMM 'N','N', cegterg.f90:353-395, 588-632)
-// and regterg (DGEMM on the 2*npwx real view, B real) on the add_vuspsi kernel. accumulate == 0: C is overwritten
-// (rows n+1..ldc of C are left untouched, as ZGEMM does).
-int qeb_dav_gemm_nn(qeb_ctx* c, int n, const void* A, int lda, int k, const void* B, int ldb, int m, void* C, int ldc,
-                    int accumulate)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->have_grid) QEB_FAIL(c, 96, "qeb_dav_gemm_nn: qeb_set_grid has not been called");
-    if (n < 1 || lda < n || ldc < n || k < 0 || m < 0 || ldb < k || !A || !B || !C) QEB_FAIL(c, 96, "qeb_dav_gemm_nn: bad arguments");
-    if (!is_device_ptr(A) || !is_device_ptr(C)) QEB_FAIL(c, 93, "qeb_dav_gemm_nn: A and C must be device pointers");
-    if (m == 0) return 0;
-    if (!accumulate) QEB_CUDA(c, cudaMemset2DAsync(C, (size_t)ldc * 16, 0, (size_t)n * 16, m, c->stream));
-    if (k == 0) return finish(c);
-    const size_t el = c->gamma ? 8 : 16;
-    const int ldps = (k + 1) & ~1;
-    QEB_CUDA(c, c->misc_stage.ensure((size_t)ldps * m * el));
-    QEB_CUDA(c, cudaMemsetAsync(c->misc_stage.p, 0, (size_t)ldps * m * el, c->stream));
-    QEB_CUDA(c, cudaMemcpy2DAsync(c->misc_stage.p, (size_t)ldps * el, B, (size_t)ldb * el, (size_t)k * el, m,
-                                  is_device_ptr(B) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    QEB_CUDA(c, launch_addvus((const cplx*)A, lda, c->misc_stage.p, ldps, n, k, m, !c->gamma, (cplx*)C, ldc, c->stream));
-    if (!is_device_ptr(B)) QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return finish(c);
-}
-
-// ---- peer-to-peer stick <-> plane exchange over NVLink (cudaIpc) ------------
-struct P2PBlob {  // what one rank publishes to the others (fits QEB_P2P_BLOB_BYTES)
-    cudaIpcMemHandle_t s, r, f;
-    unsigned long long s_bytes, r_bytes;
-    int batch, nslots, rank, nproc;
-};
-
-int qeb_p2p_export(qeb_ctx* c, void* blob)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->dist || !c->have_k) QEB_FAIL(c, 98, "qeb_p2p_export: call after qeb_set_grid_dist + qeb_set_kpoint (the buffers must exist)");
-    if (!blob) QEB_FAIL(c, 98, "qeb_p2p_export: null blob");
-    static_assert(sizeof(P2PBlob) <= 256, "QEB_P2P_BLOB_BYTES");
-    const DistHost& D = c->DH;
-    const int ns = c->vloc_nstreams;
-    QEB_CUDA(c, c->p2p_flags_d.ensure((size_t)2 * ns * D.nproc * 4 + 64));
-    QEB_CUDA(c, cudaMemsetAsync(c->p2p_flags_d.p, 0, c->p2p_flags_d.cap, c->stream));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    P2PBlob b;
-    memset(&b, 0, sizeof(b));
-    QEB_CUDA(c, cudaIpcGetMemHandle(&b.s, c->sbuf_d.p));
-    QEB_CUDA(c, cudaIpcGetMemHandle(&b.r, c->rbuf_d.p));
-    QEB_CUDA(c, cudaIpcGetMemHandle(&b.f, c->p2p_flags_d.p));
-    b.s_bytes = c->sbuf_d.cap;
-    b.r_bytes = c->rbuf_d.cap;
-    b.batch = c->batch;
-    b.nslots = ns;
-    b.rank = D.me;
-    b.nproc = D.nproc;
-    memset(blob, 0, 256);
-    memcpy(blob, &b, sizeof(b));
-    c->p2p_exported = true;
-    c->P2P = P2PState();
-    return 0;
-}
-
-int qeb_p2p_import(qeb_ctx* c, const void* blobs, int nranks)
-{
-    if (!c) return 1;
-    ++c->state_epoch;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->p2p_exported) QEB_FAIL(c, 99, "qeb_p2p_import: qeb_p2p_export first");
-    const DistHost& D = c->DH;
-    if (!blobs || nranks != D.nproc) QEB_FAIL(c, 99, "qeb_p2p_import: one blob per rank of the R&G group expected");
-    P2PState& P = c->P2P;
-    P = P2PState();
-    for (void* m : c->p2p_opened) cudaIpcCloseMemHandle(m);  // mappings of a previous import
-    c->p2p_opened.clear();
-    P.nslots = c->vloc_nstreams;
-    P.batch = c->batch;
-    P.peer_S.assign(nranks, nullptr);
-    P.peer_R.assign(nranks, nullptr);
-    P.peer_flags.assign(nranks, nullptr);
-    for (int q = 0; q < nranks; ++q) {
-        P2PBlob b;
-        memcpy(&b, (const char*)blobs + (size_t)q * 256, sizeof(b));
-        if (b.rank != q || b.nproc != nranks) QEB_FAIL(c, 99, "qeb_p2p_import: blobs are not ordered by rank");
-        if (b.batch != c->batch || b.nslots != P.nslots) QEB_FAIL(c, 99, "qeb_p2p_import: ranks disagree on batch / streams");
-        if (q == D.me) {
-            P.peer_S[q] = (cplx*)c->sbuf_d.p;
-            P.peer_R[q] = (cplx*)c->rbuf_d.p;
-            P.peer_flags[q] = (unsigned*)c->p2p_flags_d.p;
-            continue;
-        }
-        void *ps = nullptr, *pr = nullptr, *pf = nullptr;
-        QEB_CUDA(c, cudaIpcOpenMemHandle(&ps, b.s, cudaIpcMemLazyEnablePeerAccess));
-        c->p2p_opened.push_back(ps);
-        QEB_CUDA(c, cudaIpcOpenMemHandle(&pr, b.r, cudaIpcMemLazyEnablePeerAccess));
-        c->p2p_opened.push_back(pr);
-        QEB_CUDA(c, cudaIpcOpenMemHandle(&pf, b.f, cudaIpcMemLazyEnablePeerAccess));
-        c->p2p_opened.push_back(pf);
-        P.peer_S[q] = (cplx*)ps;
-        P.peer_R[q] = (cplx*)pr;
-        P.peer_flags[q] = (unsigned*)pf;
-    }
-    QEB_CUDA(c, c->p2p_ptrs_d.ensure((size_t)nranks * sizeof(void*)));
-    QEB_CUDA(c, cudaMemcpyAsync(c->p2p_ptrs_d.p, P.peer_flags.data(), (size_t)nranks * sizeof(void*), cudaMemcpyHostToDevice,
-                                c->stream));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    P.peer_flags_dev = (unsigned**)c->p2p_ptrs_d.p;
-    const char* e = getenv("QEB_P2P");
-    P.ok = !(e && atoi(e) == 0);
-    return 0;
-}
-
-// ---- internal pieces ----------------------------------------------------
-static int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hpsi, bool kinetic)
-{
-    if (!c->have_v) QEB_FAIL(c, 50, "V_loc: no potential set (qeb_set_vloc)");
-    VlocIO io;
-    io.psi = psi;
-    io.hpsi = hpsi;
-    if (kinetic && !c->have_g2kin) QEB_FAIL(c, 55, "h_psi: no g2kin in the context (qeb_set_kpoint or qeb_g2_kin)");
-    io.g2kin = kinetic ? (const double*)c->g2kin_d.p : nullptr;
-    io.lda = lda;
-    io.n = n;
-    io.nbands = m;
-    io.gamma = c->gamma ? 1 : 0;
-    const int nboxes = c->gamma ? (m + 1) / 2 : m;
-    if (c->dist) {
-        // cft_1z | fft_scatter | cft_2xy * V * cft_2xy | fft_scatter | cft_1z  (fft_parallel_2d.f90:36-204)
-        const DistHost& D = c->DH;
-        if (D.nproc > 1 && !c->nccl_rg && !c->P2P.ok)
-            QEB_FAIL(c, 53, "V_loc: no NCCL communicator (qeb_nccl_init) or peer mapping (qeb_p2p_import) for the R&G group");
-        // batches alternate between the V_loc streams (own S/R/G1/G2 slices): the exchange of one batch overlaps
-        // the FFT passes of the other. Every rank issues the collectives in the same order.
-        const int nbatches_d = (nboxes + c->batch - 1) / c->batch;
-        const int nsd = std::min(c->vloc_nstreams, nbatches_d);
-        if (nsd > 1) {
-            QEB_CUDA(c, cudaEventRecord(c->vev[0], c->stream));
-            for (int s = 1; s < nsd; ++s) QEB_CUDA(c, cudaStreamWaitEvent(c->vstream[s], c->vev[0], 0));
-        }
-        const size_t s_slice = (size_t)D.nsw[D.me] * c->nr3 * c->batch;
-        const size_t r_slice = c->Tp.g1_box * c->batch;
-        const size_t g2_slice = c->Tp.g2_box * c->batch;
-        int ib = 0;
-        for (int b0 = 0; b0 < nboxes; b0 += c->batch, ++ib) {
-            const int nb = std::min(c->batch, nboxes - b0);
-            const int si = ib % nsd;
-            cudaStream_t st = si == 0 ? c->stream : c->vstream[si];
-            cplx* S = (cplx*)c->sbuf_d.p + si * s_slice;
-            cplx* R = (cplx*)c->rbuf_d.p + si * r_slice;
-            io.band0 = c->gamma ? 2 * b0 : b0;
-            VlocTables tz = c->T;
-            tz.g1 = S;
-            tz.g1_zs = (size_t)nb * tz.g1_box;
-            VlocTables tp = c->Tp;
-            tp.g1 += si * r_slice;
-            tp.g2 += si * g2_slice;
-            const char* msg = "";
-            int rc;
-            const bool p2p = c->P2P.ok && D.nproc > 1;
-            // Fused exchange (peer-to-peer mapping, three-kernel plane path): the z-inverse pass stores straight into the
-            // plane owners' R buffers over NVLink, the y passes read and write R itself - no S staging and no repack
-            // kernels on the forward leg, no pack kernel on the backward leg (fft_scatter_2d.f90:123,226 folded into the
-            // neighbouring passes). QEB_FUSED_X=0: the unfused sequence.
-            const bool fused = p2p && !vloc_uses_plane_kernel(tp, c->cfgp) && D.nproc <= 16 && env_flag("QEB_FUSED_X", 1);
-            if (fused) {
-                tz.peer_on = 1;
-                tz.peer_nb = nb;
-                tz.peer_zown = c->fx_zown;
-                tz.peer_zi0 = c->fx_zi0;
-                for (int q = 0; q < D.nproc; ++q)
-                    tz.peer_base[q] = c->P2P.peer_R[q] + (size_t)si * ((size_t)D.nst_tot * D.nr3p[q] * c->P2P.batch) +
-                                      (size_t)nb * D.nr3p[q] * D.prefix[D.me];
-                QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
-                tz.peer_on = 0;
-                if ((rc = dist_p2p_sync(D, c->P2P, true, si, st, &msg))) QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-                tp.g1 = R;
-                tp.r_on = 1;
-                tp.r_nb = nb;
-                tp.r_pref = c->fx_rpref;
-                tp.r_nsw = c->fx_rnsw;
-                tp.r_sidx = c->DD.sidx;
-                QEB_CUDA(c, vloc_launch_planes(tp, c->cfgp, nb, st));
-                if ((rc = dist_exchange_p2p(D, c->P2P, false, si, S, R, nb, c->nr3, st, &msg)))
-                    QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-                QEB_CUDA(c, vloc_launch_zpass(false, tz, io, c->cfg, nb, st));
-                continue;
-            }
-            QEB_CUDA(c, vloc_launch_zpass(true, tz, io, c->cfg, nb, st));
-            if ((rc = p2p ? dist_exchange_p2p(D, c->P2P, true, si, S, R, nb, c->nr3, st, &msg)
-                          : dist_exchange(D, c->nccl_rg, true, S, R, nb, st, &msg)))
-                QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-            QEB_CUDA(c, dist_unpack(c->DD, R, tp.g1, nb, st));
-            QEB_CUDA(c, vloc_launch_planes(tp, c->cfgp, nb, st));
-            QEB_CUDA(c, dist_pack(c->DD, tp.g1, R, nb, st));
-            if ((rc = p2p ? dist_exchange_p2p(D, c->P2P, false, si, S, R, nb, c->nr3, st, &msg)
-                          : dist_exchange(D, c->nccl_rg, false, S, R, nb, st, &msg)))
-                QEB_FAIL(c, rc, std::string("fft_scatter: ") + msg);
-            QEB_CUDA(c, vloc_launch_zpass(false, tz, io, c->cfg, nb, st));
-        }
-        for (int s = 1; s < nsd; ++s) {
-            QEB_CUDA(c, cudaEventRecord(c->vev[s], c->vstream[s]));
-            QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->vev[s], 0));
-        }
-        return 0;
-    }
-    const int nbatches = (nboxes + c->batch - 1) / c->batch;
-    const int ns = std::min(c->vloc_nstreams, nbatches);
-    if (ns > 1) {  // fork: the side streams start after everything queued so far on the main stream
-        QEB_CUDA(c, cudaEventRecord(c->vev[0], c->stream));
-        for (int s = 1; s < ns; ++s) QEB_CUDA(c, cudaStreamWaitEvent(c->vstream[s], c->vev[0], 0));
-    }
-    int ib = 0;
-    for (int b0 = 0; b0 < nboxes; b0 += c->batch, ++ib) {
-        const int nb = std::min(c->batch, nboxes - b0);
-        const int s = ib % ns;
-        io.band0 = c->gamma ? 2 * b0 : b0;
-        VlocTables T = c->T;
-        T.g1 += (size_t)s * c->batch * T.g1_box;
-        T.g2 += (size_t)s * c->batch * T.g2_box;
-        QEB_CUDA(c, vloc_launch_batch(T, io, c->cfg, nb, s == 0 ? c->stream : c->vstream[s]));
-    }
-    for (int s = 1; s < ns; ++s) {  // join
-        QEB_CUDA(c, cudaEventRecord(c->vev[s], c->vstream[s]));
-        QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->vev[s], 0));
-    }
-    return 0;
-}
-
-static int ensure_becp(qeb_ctx* c, int nkb, int m)
-{
-    const size_t el = c->gamma ? 8 : 16;
-    QEB_CUDA(c, c->becp_d.ensure((size_t)nkb * m * el));
-    const int ldps = (nkb + 1) & ~1;
-    const size_t need = (size_t)ldps * m * el;
-    if (need > c->ps_d.cap) {
-        QEB_CUDA(c, c->ps_d.ensure(need));
-    }
-    QEB_CUDA(c, cudaMemsetAsync(c->ps_d.p, 0, need, c->stream));
-    return 0;
-}
-
-static int run_calbec(qeb_ctx* c, const cplx* beta, int npwx, int nkb, const cplx* psi, int lda, int n, int m, void* becp_out)
-{
-    int nsplit, gchunk;
-    calbec_plan(n, nkb, m, !c->gamma, c->num_sms, &nsplit, &gchunk);
-    QEB_CUDA(c, c->part_d.ensure(calbec_workspace_bytes(nkb, m, nsplit, !c->gamma)));
-    QEB_CUDA(c, launch_calbec(beta, npwx, psi, lda, n, nkb, m, !c->gamma, c->gstart, nsplit, gchunk, c->part_d.p,
-                              becp_out, c->stream));
-    if (c->dist && c->DH.nproc > 1) {
-        // mp_sum(becp, intra_bgrp_comm): Modules/becmod.f90:395-399 (k), :327-331 (Gamma)
-        const NcclApi& A = nccl_api();
-        if (!A.ok || !c->nccl_rg) QEB_FAIL(c, 54, "calbec: no NCCL communicator for the R&G group (qeb_nccl_init)");
-        const int rc = A.AllReduce(becp_out, becp_out, (size_t)nkb * m * (c->gamma ? 1 : 2), kNcclDouble, kNcclSum,
-                                   c->nccl_rg, c->stream);
-        if (rc) QEB_FAIL(c, 900 + rc, std::string("ncclAllReduce(becp): ") + A.GetErrorString(rc));
-    }
-    return 0;
-}
-
-static int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi, int col0 = 0, const double* dmat = nullptr)
-{
-    if (!c->have_nl) QEB_FAIL(c, 51, "add_vuspsi: qeb_set_nonlocal has not been called");
-    if (!dmat) dmat = (const double*)c->deeq_d.p;
-    const int nkb = c->nkb;
-    if (nkb > c->nl_rows) QEB_FAIL(c, 52, "add_vuspsi: vkb has projectors not covered by ofsbeta/nh of qeb_set_nonlocal");
-    const int ldps = (nkb + 1) & ~1;
-    const size_t el = c->gamma ? 8 : 16;
-    const char* becp = (const char*)c->becp_d.p + (size_t)col0 * nkb * el;
-    char* ps = (char*)c->ps_d.p + (size_t)col0 * ldps * el;
-    QEB_CUDA(c, launch_apply_deeq(becp, nkb, m, !c->gamma, c->row_atom_d, c->ofs_d, c->nh_d,
-                                  dmat, c->nhm, ps, ldps, c->stream));
-    QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, ps, ldps, n, nkb, m, !c->gamma, hpsi, lda, c->stream));
-    return 0;
-}
-
-static int check_call(qeb_ctx* c, int lda, int n, int m, const void* psi, const void* hpsi, const char* who)
-{
-    if (!c->have_k) QEB_FAIL(c, 60, std::string(who) + ": qeb_set_kpoint has not been called");
-    if (n != c->npw) QEB_FAIL(c, 61, std::string(who) + ": n differs from the npw of qeb_set_kpoint");
-    if (lda < n || m < 0 || !psi || !hpsi) QEB_FAIL(c, 62, std::string(who) + ": bad arguments");
-    return 0;
-}
-
-// columns [col0, col0+m) of a call over m_total columns; psi_d / hpsi_d point at column col0. The projections of
-// the whole call live in becp_d (column j at j*nkb): the caller runs ensure_becp(m_total) once when col0 >= 0 is
-// used with m_total > m.
-static int h_psi_cols(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool do_vloc, bool do_nl,
-                      bool kinetic, int col0 = 0, int m_total = -1)
-{
-    int rc;
-    if (kinetic && lda > n) QEB_CUDA(c, launch_zero_pad_rows(hpsi_d, lda, n, m, c->stream));
-    if (do_vloc && (rc = run_vloc(c, lda, n, m, psi_d, hpsi_d, kinetic))) return rc;
-    if (do_nl && c->nkb > 0 && !c->vkb_d) QEB_FAIL(c, 56, "h_psi: no vkb in the context (qeb_set_kpoint or qeb_init_us_2)");
-    if (do_nl && c->nkb > 0) {
-        if (m_total < 0 && (rc = ensure_becp(c, c->nkb, m))) return rc;
-        char* becp = (char*)c->becp_d.p + (size_t)col0 * c->nkb * (c->gamma ? 8 : 16);
-        if ((rc = run_calbec(c, c->vkb_d, c->npwx, c->nkb, psi_d, lda, n, m, becp))) return rc;
-        c->becp_m = m_total < 0 ? m : (col0 + m);
-        if ((rc = run_addvus(c, lda, n, m, hpsi_d, col0))) return rc;
-    }
-    if (kinetic && c->gamma && c->gstart == 2) QEB_CUDA(c, launch_zero_im_g0(hpsi_d, lda, m, c->stream));
-    return 0;
-}
-
-// Page-locking of caller memory is EXPLICIT (qeb_pin_host / qeb_unpin_host, bracketing the lifetime of the caller's
-// work arrays): the library never registers memory on its own, because it cannot see the caller free and re-allocate
-// an array at the same address. Unpinned (pageable) arrays go through the same pipeline; cudaMemcpyAsync then stages
-// them through the driver's bounce buffers and the copies overlap less.
-
-// h_psi with HOST psi and hpsi: column chunks flow through three streams, so the H2D copy of chunk i+1 and the D2H
-// copy of chunk i-1 overlap the kernels of chunk i. Every column is independent in h_psi (h_psi.f90:53-67 splits
-// columns the same way over band groups), so the result is the one of the single call.
-static int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
-{
-    int rc;
-    const size_t col = (size_t)lda * 16;
-    int mc = c->pipeline_chunk;
-    if (mc <= 0) {
-        // whole band tiles of BOTH projector kernels (calbec: 48 bands, add_vuspsi: 64): multiples of 192; measured at
-        // AUSURF112 m=800 (tools/e2e_sweep.py): 96 -> 101.0, 128 -> 95.7, 192 -> 93.1, 256 -> 100.0, 400 -> 112.9 ms;
-        // with the sub-chunked first copy-in / last copy-outs below: 192 -> 87.9, 256 -> 91.5, 272 -> 93.0, 400 -> 91.2 ms
-        mc = m >= 384 ? 192 : ((m + 7) / 8 + 63) / 64 * 64;
-        if (mc < 64) mc = 64;
-    }
-    if (mc > m) mc = m;
-    if (mc & 1) ++mc;  // Gamma: band pairs stay together
-    // chunk schedule: the first copy-in and the last copy-out are the only transfers nothing overlaps, so in the
-    // automatic schedule the first and the last chunk are short (64 columns = one GEMM band tile)
-    std::vector<int> sizes;
-    {
-        int rem = m;
-        // (measured: no gain at AUSURF112, 96.9 vs 95.7 ms, because the short chunks run the GEMMs less efficiently;
-        // kept behind QEB_PIPE_RAMP for hosts with slower links)
-        const bool ramp = getenv("QEB_PIPE_RAMP") && c->pipeline_chunk <= 0 && m >= 4 * 64 && mc > 64;
-        if (ramp) {
-            sizes.push_back(64);
-            rem -= 128;  // first + last
-        }
-        while (rem > 0) {
-            const int t = std::min(mc, rem);
-            sizes.push_back(t);
-            rem -= t;
-        }
-        if (ramp) sizes.push_back(64);
-    }
-    const int nch = (int)sizes.size();
-    if (!c->s_in) QEB_CUDA(c, cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
-    if (!c->s_out) QEB_CUDA(c, cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
-    while ((int)c->ev.size() < 2 * nch) {
-        cudaEvent_t e;
-        QEB_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        c->ev.push_back(e);
-    }
-    QEB_CUDA(c, c->psi_stage.ensure(col * m));
-    QEB_CUDA(c, c->hpsi_stage.ensure(col * m));
-    if (c->nkb > 0 && (rc = ensure_becp(c, c->nkb, m))) return rc;
-    // the staging buffers may still be read by work queued earlier on the compute stream (async callers)
-    QEB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
-    QEB_CUDA(c, cudaStreamWaitEvent(c->s_in, c->ev[0], 0));
-    const char* ph = (const char*)psi;
-    char* hh = (char*)hpsi;
-    char* pd = (char*)c->psi_stage.p;
-    char* hd = (char*)c->hpsi_stage.p;
-    int c0 = 0;
-    // The copy-in of the first chunk is the one transfer no compute can hide. Its V_loc part only needs the columns
-    // that have landed, so the first chunk is copied in sub-chunks of `sub` columns and the V_loc passes follow them
-    // one sub-chunk behind; the projector GEMMs then run on the whole chunk (serial descriptor only: the distributed
-    // path keeps one collective schedule per chunk).
-    int sub = 40;
-    if (const char* e = getenv("QEB_PIPE_SUB")) sub = atoi(e);
-    if (sub & 1) ++sub;
-    int tsub = 64;  // one band tile of the add_vuspsi kernels
-    if (const char* e = getenv("QEB_PIPE_TAIL")) tsub = atoi(e);
-    if (tsub & 1) ++tsub;
-    for (int i = 0; i < nch; c0 += sizes[i], ++i) {
-        const int mm = sizes[i];
-        if (i == 0 && sub > 0 && mm > sub && !c->dist) {
-            while ((int)c->ev_sub.size() < (mm + sub - 1) / sub) {
-                cudaEvent_t e;
-                QEB_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-                c->ev_sub.push_back(e);
-            }
-            for (int s0 = 0, k = 0; s0 < mm; s0 += sub, ++k) {
-                const int ms = std::min(sub, mm - s0);
-                QEB_CUDA(c, cudaMemcpyAsync(pd + col * s0, ph + col * s0, col * ms, cudaMemcpyHostToDevice, c->s_in));
-                QEB_CUDA(c, cudaEventRecord(c->ev_sub[k], c->s_in));
-                QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_sub[k], 0));
-                if ((rc = h_psi_cols(c, lda, n, ms, (const cplx*)(pd + col * s0), (cplx*)(hd + col * s0), true, false, true)))
-                    return rc;
-            }
-            if ((rc = h_psi_cols(c, lda, n, mm, (const cplx*)pd, (cplx*)hd, false, true, true, 0, m))) return rc;
-            QEB_CUDA(c, cudaEventRecord(c->ev[1], c->stream));
-            QEB_CUDA(c, cudaStreamWaitEvent(c->s_out, c->ev[1], 0));
-            QEB_CUDA(c, cudaMemcpyAsync(hh, hd, col * mm, cudaMemcpyDeviceToHost, c->s_out));
-            continue;
-        }
-        QEB_CUDA(c, cudaMemcpyAsync(pd + col * c0, ph + col * c0, col * mm, cudaMemcpyHostToDevice, c->s_in));
-        QEB_CUDA(c, cudaEventRecord(c->ev[2 * i], c->s_in));
-        QEB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev[2 * i], 0));
-        if (i > 0 && i >= nch - 2 && tsub > 0 && mm > tsub && !c->dist && c->nkb > 0 && c->vkb_d && c->have_nl) {
-            // The copy-out of the last chunks is the other transfer little compute is left to hide: add_vuspsi, the last
-            // kernel of a chunk, runs in sub-chunks of one band tile and each sub-chunk is copied out behind it.
-            const cplx* pc = (const cplx*)(pd + col * c0);
-            cplx* hc = (cplx*)(hd + col * c0);
-            if ((rc = h_psi_cols(c, lda, n, mm, pc, hc, true, false, true))) return rc;
-            char* becp = (char*)c->becp_d.p + (size_t)c0 * c->nkb * (c->gamma ? 8 : 16);
-            if ((rc = run_calbec(c, c->vkb_d, c->npwx, c->nkb, pc, lda, n, mm, becp))) return rc;
-            c->becp_m = c0 + mm;
-            while ((int)c->ev_tail.size() < (mm + tsub - 1) / tsub) {
-                cudaEvent_t e;
-                QEB_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-                c->ev_tail.push_back(e);
-            }
-            for (int s0 = 0, k = 0; s0 < mm; s0 += tsub, ++k) {
-                const int ms = std::min(tsub, mm - s0);
-                cplx* hs = hc + (size_t)s0 * lda;
-                if ((rc = run_addvus(c, lda, n, ms, hs, c0 + s0))) return rc;
-                if (c->gamma && c->gstart == 2) QEB_CUDA(c, launch_zero_im_g0(hs, lda, ms, c->stream));
-                QEB_CUDA(c, cudaEventRecord(c->ev_tail[k], c->stream));
-                QEB_CUDA(c, cudaStreamWaitEvent(c->s_out, c->ev_tail[k], 0));
-                QEB_CUDA(c, cudaMemcpyAsync(hh + col * (c0 + s0), hs, col * ms, cudaMemcpyDeviceToHost, c->s_out));
-            }
-            continue;
-        }
-        if ((rc = h_psi_cols(c, lda, n, mm, (const cplx*)(pd + col * c0), (cplx*)(hd + col * c0), true, true, true, c0, m)))
-            return rc;
-        QEB_CUDA(c, cudaEventRecord(c->ev[2 * i + 1], c->stream));
-        QEB_CUDA(c, cudaStreamWaitEvent(c->s_out, c->ev[2 * i + 1], 0));
-        QEB_CUDA(c, cudaMemcpyAsync(hh + col * c0, hd + col * c0, col * mm, cudaMemcpyDeviceToHost, c->s_out));
-    }
-    QEB_CUDA(c, cudaStreamSynchronize(c->s_out));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return 0;
-}
-
-// ---- CUDA-graph replay of h_psi -------------------------------------------------------------------------------
-// The small BASELINE configs are launch-bound (Si-2: 8 launches for 3 MB of work, 0.12 ms per call): the third call
-// with the same arguments and context state is captured into a graph (the V_loc side streams fork and join inside the
-// capture) and later calls replay it with one launch. The key holds everything a launch depends on: the arguments,
-// the setters' epoch, and the addresses of the buffers the kernels receive.
-static std::vector<unsigned long long> graph_key(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
-{
-    auto P = [](const void* p) { return (unsigned long long)(uintptr_t)p; };
-    return {(unsigned long long)lda, (unsigned long long)n, (unsigned long long)m, P(psi), P(hpsi), c->state_epoch,
-            P(c->vkb_d), P(c->g2kin_d.p), P(c->vp_d.p), P(c->vpl_d.p), P(c->deeq_d.p), P(c->nlint_d.p), P(c->tab_d.p),
-            P(c->plan_d.p), P(c->g1_d.p), P(c->g2_d.p), P(c->becp_d.p), P(c->ps_d.p), P(c->part_d.p),
-            (unsigned long long)c->nkb, (unsigned long long)c->batch};
-}
-
-static bool graph_wanted(qeb_ctx* c, int n, int m)
-{
-    const char* e = getenv("QEB_GRAPH");  // 0: off, 2: every device-pointer call, otherwise automatic (read per call)
-    c->graph_mode = e ? (atoi(e) == 0 ? 0 : (atoi(e) == 2 ? 1 : 2)) : 2;
-    if (c->graph_mode == 0 || c->dist) return false;
-    if (c->graph_mode == 1) return true;
-    return (long long)n * m <= (1LL << 17);  // automatic: calls whose kernels are shorter than their launches
-}
-
-static void graph_clear(qeb_ctx* c)
-{
-    for (auto& g : c->graphs)
-        if (g.exec) cudaGraphExecDestroy(g.exec);
-    c->graphs.clear();
-}
-
-// returns 0 and sets *done when the call was served by a graph (captured now or replayed)
-static int h_psi_graph(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool* done)
-{
-    *done = false;
-    const std::vector<unsigned long long> key = graph_key(c, lda, n, m, psi_d, hpsi_d);
-    qeb_ctx::GraphEntry* ent = nullptr;
-    for (auto& g : c->graphs)
-        if (g.key == key) ent = &g;
-    if (!ent) {
-        if (c->graphs.size() >= 64) graph_clear(c);  // a caller that never repeats a call
-        c->graphs.push_back({});
-        ent = &c->graphs.back();
-        ent->key = key;
-    }
-    if (ent->exec) {
-        QEB_CUDA(c, cudaGraphLaunch(ent->exec, c->stream));
-        *done = true;
-        return 0;
-    }
-    if (++ent->seen < 2) return 0;  // the first sight of a key runs eagerly (the very first call also sizes the work
-                                    // buffers, which changes the key): capture at the second
-    cudaGraph_t graph = nullptr;
-    QEB_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
-    const int rc = h_psi_cols(c, lda, n, m, psi_d, hpsi_d, true, true, true);
-    const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
-    if (rc != 0 || e != cudaSuccess || !graph) {
-        if (graph) cudaGraphDestroy(graph);
-        cudaGetLastError();
-        ent->seen = -(1 << 30);  // never try this key again
-        return 0;                // the eager path runs (and reports its own error, if any, with a clean stream)
-    }
-    cudaGraphExec_t exec = nullptr;
-    const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (ei != cudaSuccess) {
-        cudaGetLastError();
-        ent->seen = -(1 << 30);
-        return 0;
-    }
-    ent->exec = exec;
-    QEB_CUDA(c, cudaGraphLaunch(exec, c->stream));
-    *done = true;
-    return 0;
-}
-
-int qeb_h_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_h_psi");
-    if (rc) return rc;
-    if (m == 0) return 0;
-    const size_t bytes = (size_t)lda * m * 16;
-    const bool out_dev = is_device_ptr(hpsi);
-    // (distributed grids: the choice must not depend on the rank's own row count - every rank has to issue the same
-    // sequence of collectives)
-    if (!out_dev && !is_device_ptr(psi) && m >= c->pipeline_min_cols &&
-        (bytes >= ((size_t)8 << 20) || c->pipeline_chunk > 0 || c->dist))
-        return h_psi_host_pipeline(c, lda, n, m, psi, hpsi);
-    const void* psi_d;
-    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
-    cplx* hpsi_d = (cplx*)hpsi;
-    if (!out_dev) {
-        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
-        hpsi_d = (cplx*)c->hpsi_stage.p;
-    }
-    bool replayed = false;
-    if (out_dev && is_device_ptr(psi) && graph_wanted(c, n, m)) {
-        if ((rc = h_psi_graph(c, lda, n, m, (const cplx*)psi_d, hpsi_d, &replayed))) return rc;
-        if (replayed) {
-            if (c->nkb > 0) c->becp_m = m;
-            return finish(c);
-        }
-    }
-    if ((rc = h_psi_cols(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true, true, true))) return rc;
-    if (!out_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hpsi_d, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-// hs_psi(lda,n,m,psi,hpsi,spsi) (PW/src/hs_psi.f90:7-40) and, with m = 1, hs_1psi (PW/src/hs_1psi.f90:7-60): H and S on
-// the same block, S re-using the projections H just left in the context.
-int qeb_hs_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi, void* spsi)
-{
-    if (!c) return 1;
-    if (!spsi) QEB_FAIL(c, 62, "qeb_hs_psi: bad arguments");
-    const int rc = qeb_h_psi(c, lda, n, m, psi, hpsi);
-    if (rc) return rc;
-    return qeb_s_psi(c, lda, n, m, psi, spsi);
-}
-
-// h_psi of several k-points in one call (the k loop of PW/src/c_bands.f90:95-150 for the launch-bound configs): context
-// k applies ITS Hamiltonian to psi[k] on its own stream (graph replay when warm), all streams are joined at the end.
-// all k-points of a multi call in ONE graph: the capture starts on the first context's stream, every other context's
-// stream is forked from it with an event, runs its own h_psi (which forks its V_loc side streams in turn) and joins
-// back. One cudaGraphLaunch then replaces nk x ~8 kernel launches and the k-points run as parallel branches.
-static int h_psi_multi_graph(int nk, qeb_ctx* const* ctxs, const int* lda, const int* n, const int* m, const void* const* psi,
-                             void* const* hpsi, bool* done)
-{
-    *done = false;
-    qeb_ctx* c0 = ctxs[0];
-    std::vector<unsigned long long> key;
-    for (int k = 0; k < nk; ++k) {
-        qeb_ctx* c = ctxs[k];
-        if (!c || c->device != c0->device || !c->have_k || n[k] != c->npw || lda[k] < n[k] || m[k] < 1 || !is_device_ptr(psi[k]) ||
-            !is_device_ptr(hpsi[k]) || !graph_wanted(c, n[k], m[k]))
-            return 0;
-        const auto kk = graph_key(c, lda[k], n[k], m[k], psi[k], hpsi[k]);
-        key.push_back((unsigned long long)(uintptr_t)c);
-        key.insert(key.end(), kk.begin(), kk.end());
-    }
-    qeb_ctx::GraphEntry* ent = nullptr;
-    for (auto& g : c0->mgraphs)
-        if (g.key == key) ent = &g;
-    if (!ent) {
-        if (c0->mgraphs.size() >= 16) {
-            for (auto& g : c0->mgraphs)
-                if (g.exec) cudaGraphExecDestroy(g.exec);
-            c0->mgraphs.clear();
-        }
-        c0->mgraphs.push_back({});
-        ent = &c0->mgraphs.back();
-        ent->key = key;
-    }
-    if (!ent->exec) {
-        if (++ent->seen < 2) return 0;  // as in h_psi_graph
-        for (int k = 0; k < nk; ++k)
-            for (int j = 0; j < 2; ++j)
-                if (!ctxs[k]->mev[j]) QEB_CUDA(c0, cudaEventCreateWithFlags(&ctxs[k]->mev[j], cudaEventDisableTiming));
-        cudaGraph_t graph = nullptr;
-        QEB_CUDA(c0, cudaStreamBeginCapture(c0->stream, cudaStreamCaptureModeThreadLocal));
-        int rc = 0;
-        cudaError_t e = cudaEventRecord(c0->mev[0], c0->stream);
-        for (int k = 0; k < nk && rc == 0 && e == cudaSuccess; ++k) {
-            qeb_ctx* c = ctxs[k];
-            if (k > 0 && c->stream != c0->stream) e = cudaStreamWaitEvent(c->stream, c0->mev[0], 0);
-            if (e == cudaSuccess) rc = h_psi_cols(c, lda[k], n[k], m[k], (const cplx*)psi[k], (cplx*)hpsi[k], true, true, true);
-            if (rc == 0 && e == cudaSuccess && k > 0 && c->stream != c0->stream) {
-                e = cudaEventRecord(c->mev[1], c->stream);
-                if (e == cudaSuccess) e = cudaStreamWaitEvent(c0->stream, c->mev[1], 0);
-            }
-        }
-        const cudaError_t ee = cudaStreamEndCapture(c0->stream, &graph);
-        cudaGraphExec_t exec = nullptr;
-        if (rc != 0 || e != cudaSuccess || ee != cudaSuccess || !graph ||
-            cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) {
-            if (graph) cudaGraphDestroy(graph);
-            if (getenv("QEB_GRAPH_DEBUG"))
-                fprintf(stderr, "qeb_h_psi_multi: graph capture failed (rc %d: %s; cuda %s / %s), eager launches from now on\n", rc,
-                        rc ? ctxs[0]->err.c_str() : "", cudaGetErrorString(e), cudaGetErrorString(ee));
-            cudaGetLastError();
-            ent->seen = -(1 << 30);  // never again for this key; the eager path serves the call
-            return 0;
-        }
-        cudaGraphDestroy(graph);
-        ent->exec = exec;
-    }
-    QEB_CUDA(c0, cudaGraphLaunch(ent->exec, c0->stream));
-    for (int k = 0; k < nk; ++k)
-        if (ctxs[k]->nkb > 0) ctxs[k]->becp_m = m[k];
-    *done = true;
-    return 0;
-}
-
-int qeb_h_psi_multi(int nk, qeb_ctx* const* ctxs, const int* lda, const int* n, const int* m, const void* const* psi,
-                    void* const* hpsi)
-{
-    if (nk < 0 || (nk > 0 && (!ctxs || !lda || !n || !m || !psi || !hpsi))) return 1;
-    if (nk == 0) return 0;
-    for (int k = 0; k < nk; ++k)
-        if (!ctxs[k]) return 1;
-    int rc = 0;
-    bool done = false;
-    cudaSetDevice(ctxs[0]->device);
-    if ((rc = h_psi_multi_graph(nk, ctxs, lda, n, m, psi, hpsi, &done))) return rc;
-    if (done) {  // everything hangs off the first context's stream
-        if (!ctxs[0]->async) {
-            const cudaError_t e = cudaStreamSynchronize(ctxs[0]->stream);
-            if (e != cudaSuccess) {
-                ctxs[0]->err = std::string("qeb_h_psi_multi: ") + cudaGetErrorString(e);
-                return 100 + (int)e;
-            }
-        }
-        return 0;
-    }
-    for (int k = 0; k < nk && rc == 0; ++k) {
-        const bool was = ctxs[k]->async;
-        ctxs[k]->async = true;  // queue only; joined below
-        rc = qeb_h_psi(ctxs[k], lda[k], n[k], m[k], psi[k], hpsi[k]);
-        ctxs[k]->async = was;
-        if (rc && k > 0) ctxs[0]->err = "qeb_h_psi_multi: k-point " + std::to_string(k) + ": " + ctxs[k]->err;
-    }
-    // join: every other context's stream first, then the first context's unless it is asynchronous
-    for (int k = nk - 1; k >= 0; --k) {
-        if (k == 0 && ctxs[0]->async) continue;
-        cudaSetDevice(ctxs[k]->device);
-        const cudaError_t e = cudaStreamSynchronize(ctxs[k]->stream);
-        if (e != cudaSuccess && rc == 0) {
-            ctxs[0]->err = std::string("qeb_h_psi_multi: ") + cudaGetErrorString(e);
-            rc = 100 + (int)e;
-        }
-    }
-    return rc;
-}
-
-static int vloc_entry(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v, void* hpsi, bool want_gamma,
-                      const char* who)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, psi, hpsi, who);
-    if (rc) return rc;
-    if (want_gamma != c->gamma) QEB_FAIL(c, 63, std::string(who) + ": grid was set with a different gamma_only");
-    if (m == 0) return 0;
-    if (v && (rc = prepare_v(c, v))) return rc;
-    const size_t bytes = (size_t)lda * m * 16;
-    const void* psi_d;
-    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
-    const bool out_dev = is_device_ptr(hpsi);
-    const void* hin;
-    if ((rc = stage_in(c, hpsi, bytes, c->hpsi_stage, &hin))) return rc;  // INOUT
-    cplx* hpsi_d = (cplx*)hin;
-    if ((rc = h_psi_cols(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true, false, false))) return rc;
-    if (!out_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hpsi_d, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-// m spinors = 2m component columns of leading dimension lda through the 2x2 potential; kinetic: hpsi = g2kin*psi + ...
-static int run_vloc_nc(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool kinetic)
-{
-    if (!c->have_vnc) QEB_FAIL(c, 50, "vloc_psi_nc: no 2x2 potential set (qeb_set_vloc_nc)");
-    if (2 * c->cfg.smem_x > c->max_smem) QEB_FAIL(c, 64, "vloc_psi_nc: x tile of this grid does not fit twice in shared memory");
-    if (kinetic && !c->have_g2kin) QEB_FAIL(c, 55, "h_psi_nc: no g2kin in the context (qeb_set_kpoint or qeb_g2_kin)");
-    VlocIO io;
-    io.psi = psi_d;
-    io.hpsi = hpsi_d;
-    io.g2kin = kinetic ? (const double*)c->g2kin_d.p : nullptr;
-    io.lda = lda;
-    io.n = n;
-    io.nbands = 2 * m;
-    io.gamma = 0;
-    const int bands_per_batch = std::max(1, c->batch / 2);
-    for (int b0 = 0; b0 < m; b0 += bands_per_batch) {
-        const int nb = std::min(bands_per_batch, m - b0);
-        io.band0 = 2 * b0;
-        QEB_CUDA(c, vloc_launch_batch_nc(c->T, io, c->cfg, nb, c->stream));
-    }
-    return 0;
-}
-
-// vloc_psi_nc with domag (PW/src/vloc_psi_acc.f90:269-369): psi(lda*2, m), hpsi(lda, 2, m) INOUT. The two components of a
-// band are columns 2b, 2b+1 of leading dimension lda, i.e. boxes 2b, 2b+1 of the batch.
-int qeb_vloc_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v4, void* hpsi)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_vloc_psi_nc");
-    if (rc) return rc;
-    if (c->dist || c->gamma) QEB_FAIL(c, 63, "qeb_vloc_psi_nc: serial k-point descriptor only");
-    if (m == 0) return 0;
-    if (v4 && (rc = prepare_v_nc(c, v4))) return rc;
-    const size_t bytes = (size_t)lda * 2 * m * 16;
-    const void* psi_d;
-    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
-    const bool out_dev = is_device_ptr(hpsi);
-    const void* hin;
-    if ((rc = stage_in(c, hpsi, bytes, c->hpsi_stage, &hin))) return rc;  // INOUT
-    if ((rc = run_vloc_nc(c, lda, n, m, (const cplx*)psi_d, (cplx*)hin, false))) return rc;
-    if (!out_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hin, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-// deeq_nc(nhm,nhm,nat,4) complex of add_vuspsi_nc (PW/src/add_vuspsi.f90:174-234); nat/nhm as in qeb_set_nonlocal
-int qeb_set_nonlocal_nc(qeb_ctx* c, const void* deeq_nc)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->have_nl) QEB_FAIL(c, 51, "qeb_set_nonlocal_nc: qeb_set_nonlocal has not been called (nat, nhm, nh, ofsbeta)");
-    if (!deeq_nc) QEB_FAIL(c, 40, "qeb_set_nonlocal_nc: null deeq_nc");
-    const size_t nd = (size_t)c->nhm * c->nhm * c->nat * 4;
-    QEB_CUDA(c, c->dnc_d.ensure(nd * 16 + 16));
-    if (nd)
-        QEB_CUDA(c, cudaMemcpyAsync(c->dnc_d.p, deeq_nc, nd * 16,
-                                    is_device_ptr(deeq_nc) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->have_dnc = true;
-    return 0;
-}
-
-// h_psi_ for noncollinear spinors with magnetisation / spin-orbit (PW/src/h_psi.f90:138-148,184-190,225-229):
-// kinetic term on both components, vloc_psi_nc, calbec_nc (= calbec on 2m columns, becmod.f90:575-616), add_vuspsi_nc.
-// psi(lda*2,m) -> hpsi(lda*2,m); leaves becp%nc(nkb,2,m) in the context (qeb_get_becp with 2m columns).
-int qeb_h_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_h_psi_nc");
-    if (rc) return rc;
-    if (c->dist || c->gamma) QEB_FAIL(c, 63, "qeb_h_psi_nc: serial k-point descriptor only");
-    if (m == 0) return 0;
-    const int nkb = c->nkb;
-    if (nkb > 0 && !c->vkb_d) QEB_FAIL(c, 56, "qeb_h_psi_nc: no vkb in the context (qeb_set_kpoint or qeb_init_us_2)");
-    if (nkb > 0 && !c->have_dnc) QEB_FAIL(c, 51, "qeb_h_psi_nc: no deeq_nc in the context (qeb_set_nonlocal_nc)");
-    if (nkb > c->nl_rows) QEB_FAIL(c, 52, "qeb_h_psi_nc: vkb has projectors not covered by ofsbeta/nh of qeb_set_nonlocal");
-    const size_t bytes = (size_t)lda * 2 * m * 16;
-    const bool out_dev = is_device_ptr(hpsi);
-    const void* psi_d;
-    if ((rc = stage_in(c, psi, bytes, c->psi_stage, &psi_d))) return rc;
-    cplx* hpsi_d = (cplx*)hpsi;
-    if (!out_dev) {
-        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
-        hpsi_d = (cplx*)c->hpsi_stage.p;
-    }
-    if (lda > n) QEB_CUDA(c, launch_zero_pad_rows(hpsi_d, lda, n, 2 * m, c->stream));
-    if ((rc = run_vloc_nc(c, lda, n, m, (const cplx*)psi_d, hpsi_d, true))) return rc;
-    if (nkb > 0) {
-        if ((rc = ensure_becp(c, nkb, 2 * m))) return rc;
-        if ((rc = run_calbec(c, c->vkb_d, c->npwx, nkb, (const cplx*)psi_d, lda, n, 2 * m, c->becp_d.p))) return rc;
-        c->becp_m = 2 * m;
-        const int ldps = (nkb + 1) & ~1;
-        QEB_CUDA(c, launch_apply_deeq_nc(c->becp_d.p, nkb, m, c->row_atom_d, c->ofs_d, c->nh_d, c->dnc_d.p, c->nhm, c->nat,
-                                         c->ps_d.p, ldps, c->stream));
-        QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, c->ps_d.p, ldps, n, nkb, 2 * m, true, hpsi_d, lda, c->stream));
-    }
-    if (!out_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hpsi_d, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-int qeb_vloc_psi_k(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v, void* hpsi)
-{
-    return vloc_entry(c, lda, n, m, psi, v, hpsi, false, "qeb_vloc_psi_k");
-}
-int qeb_vloc_psi_gamma(qeb_ctx* c, int lda, int n, int m, const void* psi, const double* v, void* hpsi)
-{
-    return vloc_entry(c, lda, n, m, psi, v, hpsi, true, "qeb_vloc_psi_gamma");
-}
-
-int qeb_calbec(qeb_ctx* c, int n, const void* beta, int nkb, const void* psi, int lda, int m, void* becp)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->have_k) QEB_FAIL(c, 70, "qeb_calbec: qeb_set_kpoint has not been called");
-    if (n < 1 || n > c->npwx || lda < n || m < 0 || !psi || !becp) QEB_FAIL(c, 71, "qeb_calbec: bad arguments");
-    if (!beta) {
-        if (nkb != c->nkb) QEB_FAIL(c, 72, "qeb_calbec: nkb differs from the context's vkb");
-        beta = c->vkb_d;
-    }
-    if (nkb == 0 || m == 0) return 0;
-    int rc;
-    const void *beta_d, *psi_d;
-    if ((rc = stage_in(c, beta, (size_t)c->npwx * nkb * 16, c->beta_stage, &beta_d))) return rc;
-    if ((rc = stage_in(c, psi, (size_t)lda * m * 16, c->psi_stage, &psi_d))) return rc;
-    const size_t el = c->gamma ? 8 : 16;
-    const bool keep = (beta_d == (const void*)c->vkb_d);
-    void* out_d;
-    if (keep) {
-        if ((rc = ensure_becp(c, nkb, m))) return rc;
-        out_d = c->becp_d.p;
-    } else {
-        QEB_CUDA(c, c->misc_stage.ensure((size_t)nkb * m * el));
-        out_d = c->misc_stage.p;
-    }
-    if ((rc = run_calbec(c, (const cplx*)beta_d, c->npwx, nkb, (const cplx*)psi_d, lda, n, m, out_d))) return rc;
-    if (keep) c->becp_m = m;
-    QEB_CUDA(c, cudaMemcpyAsync(becp, out_d, (size_t)nkb * m * el,
-                                is_device_ptr(becp) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
-    if (!is_device_ptr(becp)) {
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-int qeb_add_vuspsi(qeb_ctx* c, int lda, int n, int m, void* hpsi, const void* becp)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, hpsi, hpsi, "qeb_add_vuspsi");
-    if (rc) return rc;
-    if (m == 0 || c->nkb == 0) return 0;
-    const size_t el = c->gamma ? 8 : 16;
-    if (becp) {
-        if ((rc = ensure_becp(c, c->nkb, m))) return rc;
-        QEB_CUDA(c, cudaMemcpyAsync(c->becp_d.p, becp, (size_t)c->nkb * m * el,
-                                    is_device_ptr(becp) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-        c->becp_m = m;
-    } else if (c->becp_m < m) {
-        QEB_FAIL(c, 73, "qeb_add_vuspsi: no projections in the context for these bands");
-    }
-    const size_t bytes = (size_t)lda * m * 16;
-    const bool out_dev = is_device_ptr(hpsi);
-    const void* hin;
-    if ((rc = stage_in(c, hpsi, bytes, c->hpsi_stage, &hin))) return rc;
-    if ((rc = run_addvus(c, lda, n, m, (cplx*)hin))) return rc;
-    if (!out_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(hpsi, hin, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-int qeb_set_qq(qeb_ctx* c, int nat, int nhm, const double* qq_at)
-{
-    if (!c) return 1;
-    ++c->state_epoch;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->have_nl) QEB_FAIL(c, 42, "qeb_set_qq: qeb_set_nonlocal has not been called");
-    if (nat != c->nat || nhm != c->nhm) QEB_FAIL(c, 43, "qeb_set_qq: nat/nhm differ from qeb_set_nonlocal");
-    const size_t nd = (size_t)nhm * nhm * nat;
-    if (nd && !qq_at) QEB_FAIL(c, 43, "qeb_set_qq: null qq_at");
-    QEB_CUDA(c, c->qq_d.ensure(nd * 8 + 8));
-    if (nd)
-        QEB_CUDA(c, cudaMemcpyAsync(c->qq_d.p, qq_at, nd * 8,
-                                    is_device_ptr(qq_at) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->have_qq = true;
-    return 0;
-}
-
-// s_psi_ (PW/src/s_psi.f90:79-262): spsi = psi (all lda rows, threaded_memcpy :118), then, when there are
-// projectors with an augmentation part, spsi(1:n,:) += vkb * (blockdiag(qq_at) * becp) with the becp that h_psi or
-// calbec left behind (:15, :132 "the becp are already computed"). Atoms of a non-ultrasoft type contribute
-// ps = 0 (:232-240): the caller passes qq_at = 0 for them, which is what uspp holds for such types.
-int qeb_s_psi(qeb_ctx* c, int lda, int n, int m, const void* psi, void* spsi)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, psi, spsi, "qeb_s_psi");
-    if (rc) return rc;
-    if (m == 0) return 0;
-    const size_t bytes = (size_t)lda * m * 16;
-    const bool okvan = c->nkb > 0 && c->have_qq;
-    if (okvan && c->becp_m < m) QEB_FAIL(c, 76, "qeb_s_psi: no projections in the context for these bands (h_psi/calbec first)");
-    const bool out_dev = is_device_ptr(spsi);
-    cplx* sd = (cplx*)spsi;
-    if (!out_dev) {
-        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
-        sd = (cplx*)c->hpsi_stage.p;
-    }
-    QEB_CUDA(c, cudaMemcpyAsync(sd, psi, bytes, is_device_ptr(psi) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
-                                c->stream));
-    if (okvan) {
-        const int ldps = (c->nkb + 1) & ~1;
-        QEB_CUDA(c, cudaMemsetAsync(c->ps_d.p, 0, (size_t)ldps * m * (c->gamma ? 8 : 16), c->stream));
-        if ((rc = run_addvus(c, lda, n, m, sd, 0, (const double*)c->qq_d.p))) return rc;
-    }
-    if (!out_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(spsi, sd, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-// s_psi_nc (PW/src/s_psi.f90:308-370): qq_nc(nhm,nhm,nat,4) complex, per atom: qq_so(:,:,1:4,ityp(na)) with spin-orbit,
-// else qq_at(:,:,na) in blocks 1 and 4 and zero in 2 and 3 (:336-351)
-int qeb_set_qq_nc(qeb_ctx* c, const void* qq_nc)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->have_nl) QEB_FAIL(c, 51, "qeb_set_qq_nc: qeb_set_nonlocal has not been called (nat, nhm, nh, ofsbeta)");
-    if (!qq_nc) QEB_FAIL(c, 40, "qeb_set_qq_nc: null qq_nc");
-    const size_t nd = (size_t)c->nhm * c->nhm * c->nat * 4;
-    QEB_CUDA(c, c->qnc_d.ensure(nd * 16 + 16));
-    if (nd)
-        QEB_CUDA(c, cudaMemcpyAsync(c->qnc_d.p, qq_nc, nd * 16,
-                                    is_device_ptr(qq_nc) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->have_qnc = true;
-    return 0;
-}
-
-// spsi(lda*2,m) = psi + vkb (qq_nc becp%nc) with the becp%nc the preceding qeb_h_psi_nc left in the context
-int qeb_s_psi_nc(qeb_ctx* c, int lda, int n, int m, const void* psi, void* spsi)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, psi, spsi, "qeb_s_psi_nc");
-    if (rc) return rc;
-    if (c->dist || c->gamma) QEB_FAIL(c, 63, "qeb_s_psi_nc: serial k-point descriptor only");
-    if (m == 0) return 0;
-    const size_t bytes = (size_t)lda * 2 * m * 16;
-    const bool okvan = c->nkb > 0 && c->have_qnc;
-    if (okvan && c->becp_m < 2 * m)
-        QEB_FAIL(c, 76, "qeb_s_psi_nc: no projections in the context for these spinors (qeb_h_psi_nc first)");
-    const bool out_dev = is_device_ptr(spsi);
-    cplx* sd = (cplx*)spsi;
-    if (!out_dev) {
-        QEB_CUDA(c, c->hpsi_stage.ensure(bytes));
-        sd = (cplx*)c->hpsi_stage.p;
-    }
-    QEB_CUDA(c, cudaMemcpyAsync(sd, psi, bytes, is_device_ptr(psi) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
-                                c->stream));
-    if (okvan) {
-        const int nkb = c->nkb, ldps = (nkb + 1) & ~1;
-        QEB_CUDA(c, cudaMemsetAsync(c->ps_d.p, 0, (size_t)ldps * 2 * m * 16, c->stream));
-        QEB_CUDA(c, launch_apply_deeq_nc(c->becp_d.p, nkb, m, c->row_atom_d, c->ofs_d, c->nh_d, c->qnc_d.p, c->nhm, c->nat,
-                                         c->ps_d.p, ldps, c->stream));
-        QEB_CUDA(c, launch_addvus(c->vkb_d, c->npwx, c->ps_d.p, ldps, n, nkb, 2 * m, true, sd, lda, c->stream));
-    }
-    if (!out_dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(spsi, sd, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-int qeb_get_becp(qeb_ctx* c, void* becp, int m)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (m > c->becp_m || !becp) QEB_FAIL(c, 74, "qeb_get_becp: no projections for that many bands");
-    const size_t el = c->gamma ? 8 : 16;
-    QEB_CUDA(c, cudaMemcpyAsync(becp, c->becp_d.p, (size_t)c->nkb * m * el,
-                                is_device_ptr(becp) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
-    QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return 0;
-}
-
-int qeb_nonlocal_only(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    int rc = check_call(c, lda, n, m, psi, hpsi, "qeb_nonlocal_only");
-    if (rc) return rc;
-    if (!is_device_ptr(psi) || !is_device_ptr(hpsi)) QEB_FAIL(c, 75, "qeb_nonlocal_only: device pointers required");
-    if ((rc = h_psi_cols(c, lda, n, m, (const cplx*)psi, (cplx*)hpsi, false, true, false))) return rc;
-    return finish(c);
-}
-
-int qeb_fft(qeb_ctx* c, int sign, int kind, void* f, int howmany)
-{
-    if (!c) return 1;
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    if (!c->have_grid) QEB_FAIL(c, 80, "qeb_fft: qeb_set_grid has not been called");
-    if (!f || howmany < 1 || sign == 0 || (kind != QEB_FFT_RHO && kind != QEB_FFT_WAVE)) QEB_FAIL(c, 81, "qeb_fft: bad arguments");
-    const size_t nnr = (size_t)c->nr1 * c->nr2 * c->nr3;
-    const size_t bytes = nnr * 16 * howmany;
-    const bool dev = is_device_ptr(f);
-    const void* fin;
-    int rc;
-    if ((rc = stage_in(c, f, bytes, c->hpsi_stage, &fin))) return rc;
-    QEB_CUDA(c, fullfft_launch(c->fpx, c->fpy, c->fpz, (cplx*)fin, howmany, sign, c->max_smem, c->stream));
-    if (!dev) {
-        QEB_CUDA(c, cudaMemcpyAsync(f, fin, bytes, cudaMemcpyDeviceToHost, c->stream));
-        QEB_CUDA(c, cudaStreamSynchronize(c->stream));
-        return 0;
-    }
-    return finish(c);
-}
-
-int qeb_divide_all(int m, int nproc, int me, int* start, int* end)
-{
-    if (m < 0 || nproc < 1 || me < 0 || me >= nproc || !start || !end) return 1;
-    const int base = m / nproc, rest = m % nproc;
-    // first `rest` groups get base+1 columns (UtilXlib/divide.f90:55-106)
-    const int s = me * base + (me < rest ? me : rest);
-    *start = s;
-    *end = s + base + (me < rest ? 1 : 0);
-    return 0;
-}
-
-int qeb_set_nccl(qeb_ctx* c, void* comm, int nranks, int rank)
-{
-    return qeb_set_nccl_comm(c, QEB_COMM_BGRP, comm, nranks, rank);
-}
-
-int qeb_set_nccl_comm(qeb_ctx* c, int role, void* comm, int nranks, int rank)
-{
-    if (!c || nranks < 1 || rank < 0 || rank >= nranks || (role != QEB_COMM_BGRP && role != QEB_COMM_RG)) return 1;
-    ++c->state_epoch;
-    const NcclApi& A = nccl_api();
-    if (role == QEB_COMM_BGRP) {
-        if (c->nccl && c->nccl_owned && A.ok) A.CommDestroy(c->nccl);
-        c->nccl = comm;
-        c->nccl_owned = false;
-        c->nranks = nranks;
-        c->rank = rank;
-    } else {
-        if (c->nccl_rg && c->nccl_rg_owned && A.ok) A.CommDestroy(c->nccl_rg);
-        c->nccl_rg = comm;
-        c->nccl_rg_owned = false;
-    }
-    return 0;
-}
-
-int qeb_nccl_unique_id(void* id128)
-{
-    const NcclApi& A = nccl_api();
-    if (!A.ok || !id128) return 1;
-    return A.GetUniqueId((NcclUniqueId*)id128);
-}
-
-int qeb_nccl_init(qeb_ctx* c, int role, const void* id128, int nranks, int rank)
-{
-    if (!c) return 1;
-    if (!id128 || nranks < 1 || rank < 0 || rank >= nranks || (role != QEB_COMM_BGRP && role != QEB_COMM_RG))
-        QEB_FAIL(c, 91, "qeb_nccl_init: bad arguments");
-    QEB_CUDA(c, cudaSetDevice(c->device));
-    const NcclApi& A = nccl_api();
-    if (!A.ok) QEB_FAIL(c, 92, std::string("qeb_nccl_init: ") + A.why);
-    NcclUniqueId id;
-    memcpy(&id, id128, sizeof(id));
-    NcclComm comm = nullptr;
-    const int rc = A.CommInitRank(&comm, nranks, id, rank);
-    if (rc) QEB_FAIL(c, 900 + rc, std::string("ncclCommInitRank: ") + A.GetErrorString(rc));
-    qeb_set_nccl_comm(c, role, comm, nranks, rank);
-    if (role == QEB_COMM_BGRP)
-        c->nccl_owned = true;
-    else
-        c->nccl_rg_owned = true;
-    return 0;
-}
-
-int qeb_h_psi_bgrp(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi, int nbgrp, int my_bgrp)
-{
-    if (!c) return 1;
-    int s, e;
-    if (qeb_divide_all(m, nbgrp, my_bgrp, &s, &e)) QEB_FAIL(c, 90, "qeb_h_psi_bgrp: bad band-group arguments");
-    const bool gather = c->nccl && c->nranks == nbgrp && c->rank == my_bgrp && nbgrp > 1 && is_device_ptr(hpsi);
-    if (e > s) {
-        const char* p = (const char*)psi + (size_t)s * lda * 16;
-        char* h = (char*)hpsi + (size_t)s * lda * 16;
-        const bool was_async = c->async;
-        if (gather) c->async = true;  // the all-gather is queued behind the kernels; one sync at the end
-        const int rc = qeb_h_psi(c, lda, n, e - s, p, h);
-        c->async = was_async;
-        if (rc) return rc;
-    }
-    if (!gather) return 0;
-    // mp_allgather(hpsi, column_type, recv_counts, displs, inter_bgrp_comm)  (PW/src/h_psi.f90:58-63): every group
-    // sends its column block to all others; blocks may differ by one column (divide_all)
-    const NcclApi& A = nccl_api();
-    if (!A.ok) QEB_FAIL(c, 92, std::string("qeb_h_psi_bgrp: ") + A.why);
-    int rc = A.GroupStart();
-    for (int q = 0; q < nbgrp && rc == 0; ++q) {
-        if (q == my_bgrp) continue;
-        int qs, qe;
-        qeb_divide_all(m, nbgrp, q, &qs, &qe);
-        if (e > s) rc = A.Send((char*)hpsi + (size_t)s * lda * 16, (size_t)(e - s) * lda * 2, kNcclDouble, q, c->nccl, c->stream);
-        if (rc == 0 && qe > qs)
-            rc = A.Recv((char*)hpsi + (size_t)qs * lda * 16, (size_t)(qe - qs) * lda * 2, kNcclDouble, q, c->nccl, c->stream);
-    }
-    const int rc2 = A.GroupEnd();
-    if (rc == 0) rc = rc2;
-    if (rc) QEB_FAIL(c, 900 + rc, std::string("all-gather of hpsi: ") + A.GetErrorString(rc));
-    return finish(c);
 }
 
 int qeb_vloc_kernels_per_batch(qeb_ctx* c)

@@ -201,3 +201,21 @@ static inline int finish(qeb_ctx* c)
     return 0;
 }
 
+// ---- functions shared by the translation units of the library (context.cu: state and setters; operators.cu: the
+// reference entry points; pipeline.cu: host-array pipeline; graphs.cu: CUDA-graph replay and multi-k; multigpu.cu: NCCL,
+// peer mapping, band groups; dav_blocks.cu + solver.cu: Davidson) ----
+extern "C" {
+int stage_in(qeb_ctx* c, const void* p, size_t bytes, DevBuf& stage, const void** out);
+int check_call(qeb_ctx* c, int lda, int n, int m, const void* psi, const void* hpsi, const char* who);
+int prepare_v(qeb_ctx* c, const double* vrs);
+int prepare_v_nc(qeb_ctx* c, const double* v4);
+int run_vloc(qeb_ctx* c, int lda, int n, int m, const cplx* psi, cplx* hpsi, bool kinetic);
+int ensure_becp(qeb_ctx* c, int nkb, int m);
+int run_calbec(qeb_ctx* c, const cplx* beta, int npwx, int nkb, const cplx* psi, int lda, int n, int m, void* becp_out);
+int run_addvus(qeb_ctx* c, int lda, int n, int m, cplx* hpsi, int col0 = 0, const double* dmat = nullptr);
+int h_psi_cols(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool do_vloc, bool do_nl, bool kinetic,
+               int col0 = 0, int m_total = -1);
+int h_psi_host_pipeline(qeb_ctx* c, int lda, int n, int m, const void* psi, void* hpsi);
+bool graph_wanted(qeb_ctx* c, int n, int m);
+int h_psi_graph(qeb_ctx* c, int lda, int n, int m, const cplx* psi_d, cplx* hpsi_d, bool* done);
+}
