@@ -27,14 +27,17 @@ w = tj.setdefault(a.workload, {})
 
 def last_per_kernel(fn):
     rows = list(csv.reader(open(fn)))
-    h = rows[0]
+    h, units = rows[0], rows[1]
+    bscale = {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}
+    tscale = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}
     out = {}
     for r in rows[2:]:
         name = r[h.index("Kernel Name")]
         key = "zinv" if "zinv" in name else "zfwd" if "zfwd" in name else "plane" if "plane" in name else "calbec" if "calbec" in name \
             else "addvus" if "addvus" in name else name[:24]
-        mb = float(r[h.index("dram__bytes_read.sum")]) + float(r[h.index("dram__bytes_write.sum")])
-        out[key] = (mb, float(r[h.index("gpu__time_duration.sum")]))
+        ir, iw, it = h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum"), h.index("gpu__time_duration.sum")
+        mb = float(r[ir]) * bscale[units[ir]] + float(r[iw]) * bscale[units[iw]]  # MB
+        out[key] = (mb, float(r[it]) * tscale[units[it]])                             # us
     return out
 
 
