@@ -142,6 +142,18 @@ int qeb_fft(qeb_ctx* ctx, int sign, int kind, void* f, int howmany);
  * becp: complex(nkb,m) for k, real(nkb,m) for Gamma. */
 int qeb_calbec(qeb_ctx* ctx, int n, const void* beta, int nkb, const void* psi, int lda, int m, void* becp);
 
+/* qeb_calbec without any allocation. No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Same
+ * arguments and result as qeb_calbec, but beta (NULL: the context's vkb), psi and becp must be DEVICE pointers (nothing
+ * is staged), the context must not be slab-distributed, and the kernel's split-K partial sums live in a file-scope
+ * device array of QEB_STATIC_SCRATCH_MAX_BYTES that every GPU loading the library holds until the process exits.
+ * Limit: nkb*m*16 bytes (k; *8 Gamma) <= QEB_STATIC_SCRATCH_MAX_BYTES, i.e. nkb*m <= 2097152 complex projections;
+ * beyond it the call fails with code 75 (the split count is lowered to fit below it). Calls no cudaMalloc / cudaFree or
+ * allocating library routine. All calls on one device share the array: calls that overlap on the GPU race. */
+#define QEB_STATIC_SCRATCH_MAX_BYTES (32u << 20)
+int qeb_calbec_static(qeb_ctx* ctx, int n, const void* beta, int nkb, const void* psi, int lda, int m, void* becp);
+size_t qeb_static_scratch_bytes(void); /* the size compiled into the library (== QEB_STATIC_SCRATCH_MAX_BYTES) */
+
 /* add_vuspsi(lda,n,m,hpsi)  PW/src/add_vuspsi.f90:10-237:
  * hpsi(1:n,1:m) += vkb * (blockdiag(deeq) * becp). becp == NULL: use the
  * projections left in the context by the last qeb_h_psi / qeb_calbec. */

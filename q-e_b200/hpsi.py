@@ -70,6 +70,10 @@ def load_library():
     L.qeb_s_psi_nc.argtypes = [P, I, I, I, P, P]
     L.qeb_fft.argtypes = [P, I, I, P, I]
     L.qeb_calbec.argtypes = [P, I, P, I, P, I, I, P]
+    L.qeb_calbec_static.argtypes = [P, I, P, I, P, I, I, P]
+    L.qeb_calbec_static.restype = I
+    L.qeb_static_scratch_bytes.argtypes = []
+    L.qeb_static_scratch_bytes.restype = ctypes.c_size_t
     L.qeb_add_vuspsi.argtypes = [P, I, I, I, P, P]
     L.qeb_get_becp.argtypes = [P, P, I]
     L.qeb_set_qq.argtypes = [P, I, I, P]
@@ -477,6 +481,17 @@ class HPsi:
         if nkb is None:
             nkb = self.nkb if beta is None else beta.shape[0]
         self._ck(self._L.qeb_calbec(self._h, npw, _ptr(beta), nkb, _ptr(psi), lda, nbnd, _ptr(betapsi)), "qeb_calbec")
+        return betapsi
+
+    def calbec_static(self, npw, beta, psi, betapsi, nbnd, lda=None, nkb=None):
+        """qeb_calbec_static: calbec on device arrays with the kernel's scratch in the library's static device array;
+        allocates nothing (no reference counterpart; see include/qeb200.h)."""
+        if lda is None:
+            lda = psi.shape[-1]
+        if nkb is None:
+            nkb = self.nkb if beta is None else beta.shape[0]
+        self._ck(self._L.qeb_calbec_static(self._h, npw, _ptr(beta), nkb, _ptr(psi), lda, nbnd, _ptr(betapsi)),
+                 "qeb_calbec_static")
         return betapsi
 
     def add_vuspsi(self, lda, n, m, hpsi, becp=None):
