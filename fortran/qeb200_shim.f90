@@ -151,6 +151,9 @@ MODULE qeb200_c
     INTEGER(C_INT) FUNCTION qeb_sum_band_rho(ctx, lda, n, m, evc, w, rho) BIND(C, name='qeb_sum_band_rho')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, evc, w, rho; INTEGER(C_INT), VALUE :: lda, n, m
     END FUNCTION
+    INTEGER(C_INT) FUNCTION qeb_sum_band_rho_nc(ctx, lda, n, m, evc, w, rho, domag) BIND(C, name='qeb_sum_band_rho_nc')
+      IMPORT; TYPE(C_PTR), VALUE :: ctx, evc, w, rho; INTEGER(C_INT), VALUE :: lda, n, m, domag
+    END FUNCTION
     ! --- block-Davidson building blocks (SURVEY 8 f3) ---
     INTEGER(C_INT) FUNCTION qeb_set_g_psi_diag(ctx, n, h_diag, s_diag) BIND(C, name='qeb_set_g_psi_diag')
       IMPORT; TYPE(C_PTR), VALUE :: ctx, h_diag, s_diag; INTEGER(C_INT), VALUE :: n

@@ -207,6 +207,11 @@ int qeb_init_us_2(qeb_ctx* ctx, const double* q, double tpiba, void* vkb_out);
  * w(b) = wg(b,ik)/omega; Gamma: two bands per transform, w1 Re^2 + w2 Im^2. Uses grid / k-point of the context.
  * (becsum, the augmentation part, and the k/spin loops stay in the caller.) */
 int qeb_sum_band_rho(qeb_ctx* ctx, int lda, int n, int m, const void* evc, const double* w, double* rho);
+/* The `noncolin` branch of the same loop (PW/src/sum_band.f90:555-575; get_rho_domag :699-729): evc(2*lda,m) spinors
+ * (up in rows 1:lda, down in rows lda+1:2*lda, as evc(npwx*npol,nbnd)); rho(nnr,1) += w (|up(r)|^2 + |dw(r)|^2) and,
+ * when domag != 0, rho(nnr,2:4) += w * (2 Re(conj(up) dw), 2 Im(conj(up) dw), |up|^2 - |dw|^2). rho is (nnr,4) when
+ * domag != 0, (nnr,1) otherwise. Not for gamma_only grids. */
+int qeb_sum_band_rho_nc(qeb_ctx* ctx, int lda, int n, int m, const void* evc, const double* w, double* rho, int domag);
 
 /* ---- block-Davidson building blocks ------------------------ */
 /* The work arrays of cegterg/regterg (psi, hpsi, spsi: npwx x nvecx) live on the device in a GPU run; these entry

@@ -222,6 +222,30 @@ def sum_band_rho(d: Descriptor, lda: int, n: int, m: int, evc: np.ndarray, w: np
     return rho
 
 
+def sum_band_rho_nc(d: Descriptor, lda: int, n: int, m: int, evc: np.ndarray, w: np.ndarray, rho: np.ndarray,
+                    domag: bool = True):
+    """`noncolin` branch of the sum_band band loop (PW/src/sum_band.f90:555-575): one wave_g2r per spinor component
+    (evc(1:npw,ibnd), evc(npwx+1:npwx+npw,ibnd)), get_rho_k on both into rho(:,1) (:650-671) and, with domag,
+    get_rho_domag into rho(:,2:4) (:699-729). evc: (m, 2*lda); rho: (4, nnr) INOUT, or (nnr,) when not domag."""
+    nr = (d.nr1, d.nr2, d.nr3)
+    idx = d.nl[d.igk[:n] - 1] - 1
+    r1 = rho[0] if domag else rho
+    for b in range(m):
+        psic = []
+        for ipol in range(2):
+            box = np.zeros(d.nnr, dtype=np.complex128)
+            box[idx] = evc[b, ipol * lda:ipol * lda + n]
+            psic.append(cfft3ds(box, nr, +1, d.isind, d.iplw))
+        p1, p2 = psic
+        for p in psic:
+            r1 += w[b] * (p.real**2 + p.imag**2)
+        if domag:
+            rho[1] += w[b] * 2.0 * (p1.real * p2.real + p1.imag * p2.imag)
+            rho[2] += w[b] * 2.0 * (p1.real * p2.imag - p2.real * p1.imag)
+            rho[3] += w[b] * (p1.real**2 + p1.imag**2 - p2.real**2 - p2.imag**2)
+    return rho
+
+
 # ----------------------------------------------------------------------------
 # Nonlocal
 # ----------------------------------------------------------------------------

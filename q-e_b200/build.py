@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libqeb200.so")
 BUILD = os.path.join(HERE, "build")
-SOURCES = ["context.cu", "operators.cu", "pipeline.cu", "graphs.cu", "multigpu.cu", "dav_blocks.cu", "vloc.cu", "gemm.cu", "fullfft.cu", "distfft.cu", "nccl_glue.cu", "descriptor.cu", "uspp.cu", "davidson.cu", "solver.cu", "static_scratch.cu"] + [
+SOURCES = ["context.cu", "operators.cu", "pipeline.cu", "graphs.cu", "multigpu.cu", "dav_blocks.cu", "vloc.cu", "gemm.cu", "fullfft.cu", "distfft.cu", "nccl_glue.cu", "descriptor.cu", "uspp.cu", "davidson.cu", "solver.cu", "static_scratch.cu", "density_nc.cu"] + [
     f"vloc_fast_{n}.cu" for n in (15, 25, 27, 64, 125, 135, 144, 200, "200b", "200c", "200d")] + [
     f"vloc_plane_{a}_{b}.cu" for a, b in ((125, 64), (25, 25), (27, 27), (15, 15), (64, 64), ("125b", 64), ("125b", "64b"))] + [
     f"vloc_plane2_{a}_{b}.cu" for a, b in ((125, 64), ("125b", 64), (25, 25), (27, 27), (15, 15), (64, 64))]

@@ -88,7 +88,7 @@ int qeb_destroy(qeb_ctx* c)
                       &c->psi_stage, &c->hpsi_stage, &c->beta_stage, &c->misc_stage, &c->tabp_d, &c->planp_d,
                       &c->dist_tab_d, &c->sbuf_d, &c->rbuf_d, &c->qq_d, &c->us_int_d, &c->tab_beta_d, &c->us_scratch_d,
                       &c->us_in_d, &c->gv_g_d, &c->gv_mill_d, &c->igk_dev_d, &c->st_eig_d, &c->st_int_d, &c->gpsi_d, &c->dav_small_d, &c->rho_d, &c->wts_d, &c->vnc_d, &c->dnc_d,
-                      &c->qnc_d};
+                      &c->qnc_d, &c->nc_rho_d, &c->nc_comb_d, &c->nc_w_d, &c->nc_w2_d};
     for (void* m : c->p2p_opened) cudaIpcCloseMemHandle(m);
     c->p2p_opened.clear();
     qeb_solver_release(c);

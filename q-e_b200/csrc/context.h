@@ -91,6 +91,7 @@ struct qeb_ctx {
     DevBuf st_eig_d, st_int_d;
     // g_psi_mod::h_diag / s_diag (qeb_set_g_psi_diag) and small staging of the Davidson helpers
     DevBuf gpsi_d, dav_small_d, rho_d, wts_d;
+    DevBuf nc_rho_d, nc_comb_d, nc_w_d, nc_w2_d;  // density_nc.cu: partial densities, combined columns, weights
     int gpsi_n = 0;
     const cplx* vkb_d = nullptr;
     // V_loc tables

@@ -85,6 +85,8 @@ def load_library():
     L.qeb_set_structure.argtypes = [P, I, P, P, I, I, I, P, P, P]
     L.qeb_init_us_2.argtypes = [P, P, D, P]
     L.qeb_sum_band_rho.argtypes = [P, I, I, I, P, P, P]
+    L.qeb_sum_band_rho_nc.argtypes = [P, I, I, I, P, P, P, I]
+    L.qeb_sum_band_rho_nc.restype = I
     L.qeb_p2p_export.argtypes = [P, P]
     L.qeb_p2p_import.argtypes = [P, P, I]
     L.qeb_set_g_psi_diag.argtypes = [P, I, P, P]
@@ -361,6 +363,15 @@ class HPsi:
         if isinstance(w, np.ndarray):
             w = np.ascontiguousarray(w, dtype=np.float64)
         self._ck(self._L.qeb_sum_band_rho(self._h, lda, n, m, _ptr(evc), _ptr(w), _ptr(rho)), "qeb_sum_band_rho")
+        return rho
+
+    def sum_band_rho_nc(self, lda, n, m, evc, w, rho, domag=True):
+        """noncollinear branch of the sum_band loop (PW/src/sum_band.f90:555-575, get_rho_domag :699-729): evc (m, 2*lda)
+        spinors; rho (4, nnr) when domag (density, m_x, m_y, m_z), (nnr,) otherwise."""
+        if isinstance(w, np.ndarray):
+            w = np.ascontiguousarray(w, dtype=np.float64)
+        self._ck(self._L.qeb_sum_band_rho_nc(self._h, lda, n, m, _ptr(evc), _ptr(w), _ptr(rho), 1 if domag else 0),
+                 "qeb_sum_band_rho_nc")
         return rho
 
     # -- block-Davidson building blocks (SURVEY 8 f3); big arrays are torch CUDA tensors ---------

@@ -251,6 +251,46 @@ def test_sum_band_rho_restatement_parseval():
         assert abs(rho.sum() / d.nnr - (w * nrm).sum()) < 1e-12
 
 
+def test_sum_band_rho_nc_restatement():
+    """oracle sum_band_rho_nc (PW/src/sum_band.f90:555-575, get_rho_domag :699-729) against (a) the Pauli-matrix form
+    rho_k(r) = w psi^+(r) sigma_k psi(r) from a dense numpy transform of the two components, and (b) the decomposition
+    the library uses (density_nc.cu): four scalar densities A, B, C = |u + d|^2, D = |u - i d|^2."""
+    d = D.config_descriptor("ortho_small")
+    m = 3
+    inp = R.synthetic_inputs(d, 2 * m, [4, 4, 4], seed=5, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    evc = np.ascontiguousarray(inp["psi"]).reshape(m, 2 * lda)
+    w = np.array([2.0, 0.75, 0.1])
+    rho0 = np.random.default_rng(3).uniform(-1.0, 1.0, (4, d.nnr))
+    rho = R.sum_band_rho_nc(d, lda, n, m, evc, w, rho0.copy())
+    idx = d.nl[d.igk[:n] - 1] - 1
+    sig = np.array([[[1, 0], [0, 1]], [[0, 1], [1, 0]], [[0, -1j], [1j, 0]], [[1, 0], [0, -1]]])
+    ref = rho0.copy()
+    for b in range(m):
+        sp = []
+        for ipol in range(2):
+            box = np.zeros(d.nnr, complex)
+            box[idx] = evc[b, ipol * lda:ipol * lda + n]
+            sp.append(np.fft.ifftn(box.reshape(d.nr3, d.nr2, d.nr1)).ravel() * d.nnr)
+        sp = np.array(sp)
+        for k in range(4):
+            ref[k] += w[b] * np.einsum("ar,ab,br->r", np.conj(sp), sig[k], sp).real
+    assert np.abs(rho - ref).max() < 1e-12 * np.abs(ref).max()
+    # without magnetisation only the density is accumulated
+    r1 = R.sum_band_rho_nc(d, lda, n, m, evc, w, rho0[0].copy(), domag=False)
+    assert np.abs(r1 - rho[0]).max() < 1e-13 * np.abs(rho[0]).max()
+    # the four-scalar-density decomposition
+    z = lambda: np.zeros(d.nnr)
+    up, dw = evc[:, :lda], evc[:, lda:]
+    A = R.sum_band_rho(d, lda, n, m, up, w, z())
+    B = R.sum_band_rho(d, lda, n, m, dw, w, z())
+    C = R.sum_band_rho(d, lda, n, m, up + dw, w, z())
+    Dd = R.sum_band_rho(d, lda, n, m, up - 1j * dw, w, z())
+    dec = rho0 + np.array([A + B, C - (A + B), Dd - (A + B), A - B])
+    for k in range(4):
+        assert np.abs(dec[k] - rho[k]).max() < 1e-12 * np.abs(rho[k]).max()
+
+
 def test_vloc_psi_nc_reduces_to_scalar_and_is_hermitian():
     """vloc_psi_nc (vloc_psi_acc.f90:269-369): with v2=v3=v4=0 it is vloc_psi_k on both components; with a general
     real v(:,1:4) the 2x2 operator is Hermitian: <phi|V psi> = conj(<psi|V phi>) on the sphere."""
