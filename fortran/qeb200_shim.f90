@@ -652,6 +652,8 @@ SUBROUTINE g_psi_qeb(lda, n, m, npol, psi, e)
   COMPLEX(DP), INTENT(INOUT), TARGET :: psi(lda, npol, m)
   REAL(DP), INTENT(IN), TARGET :: e(m)
   IF (npol /= 1) THEN
+    ! reached only from the reference solver (the fallback of cegterg_qeb), which has not pushed h_diag(lda, npol);
+    ! the library's own npol = 2 solver applies qeb_g_psi itself
     CALL g_psi(lda, n, m, npol, psi, e)
     RETURN
   END IF
@@ -706,12 +708,12 @@ SUBROUTINE cegterg_qeb(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, n
   !! cegterg(...) (KS_Solvers/Davidson/cegterg.f90:18-21), same argument list, for the call in PW/src/c_bands.f90
   !! (diag_bands_k). The whole solve runs on the device with psi, hpsi, spsi resident in HBM (qeb_cegterg); the
   !! EXTERNAL operator arguments are accepted for signature compatibility and used only by the fallback: the library
-  !! applies ITS h_psi / s_psi / g_psi, which are what h_psi_qeb / s_psi_qeb / g_psi_qeb would compute. Spinors, more
+  !! applies ITS h_psi / s_psi / g_psi, which are what h_psi_qeb / s_psi_qeb / g_psi_qeb would compute. Non-magnetic spinors, more
   !! than one band group, parallel diagonalisation and every h_psi_ branch the library does not build (see h_psi_qeb)
   !! go to the reference cegterg with the pointers the caller passed. g_psi_mod::h_diag / s_diag are pushed here.
   USE, INTRINSIC :: ISO_C_BINDING
   USE kinds,            ONLY: DP
-  USE noncollin_module, ONLY: noncolin
+  USE noncollin_module, ONLY: noncolin, domag, lspinorb
   USE mp_bands,         ONLY: nbgrp
   USE g_psi_mod,        ONLY: h_diag, s_diag
   USE qeb200_c
@@ -719,19 +721,30 @@ SUBROUTINE cegterg_qeb(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, n
   IMPLICIT NONE
   EXTERNAL :: h_psi_ptr, s_psi_ptr, g_psi_ptr
   LOGICAL, INTENT(IN) :: uspp, lrot
+  LOGICAL :: magnetic
   INTEGER, INTENT(IN) :: npw, npwx, nvec, nvecx, npol
   COMPLEX(DP), INTENT(INOUT), TARGET :: evc(npwx*npol, nvec)
   REAL(DP), INTENT(IN) :: ethr
   REAL(DP), INTENT(OUT), TARGET :: e(nvec)
   INTEGER, INTENT(IN), TARGET :: btype(nvec)
   INTEGER, INTENT(OUT), TARGET :: notcnv, dav_iter, nhpsi
-  IF (noncolin .OR. npol /= 1 .OR. nbgrp > 1 .OR. .NOT. qeb200_hpsi_supported()) THEN
+  ! magnetic / spin-orbit spinors: the library's solver runs with npol = 2 on its own h_psi_nc / s_psi_nc / g_psi
+  ! (kdim = npwx*npol, cegterg.f90:131-142); non-magnetic spinors keep the reference solver
+  magnetic = noncolin .AND. (domag .OR. lspinorb) .AND. npol == 2
+  IF ((noncolin .AND. .NOT. magnetic) .OR. (npol /= 1 .AND. .NOT. magnetic) .OR. nbgrp > 1 .OR. &
+      .NOT. qeb200_hpsi_supported()) THEN
     CALL cegterg(h_psi_ptr, s_psi_ptr, uspp, g_psi_ptr, npw, npwx, nvec, nvecx, npol, evc, ethr, e, btype, &
                  notcnv, lrot, dav_iter, nhpsi)
     RETURN
   END IF
-  CALL qeb200_sync_state()
-  CALL qeb200_push_g_psi_diag(npw, h_diag, s_diag)
+  IF (magnetic) THEN
+    CALL qeb200_sync_state_nc()
+    IF (uspp) CALL qeb200_sync_qq_nc()
+    CALL qeb200_push_g_psi_diag(npwx*npol, h_diag, s_diag)   ! h_diag(npwx, npol), s_diag(npwx, npol)
+  ELSE
+    CALL qeb200_sync_state()
+    CALL qeb200_push_g_psi_diag(npw, h_diag, s_diag)
+  END IF
   CALL qeb200_check(qeb_cegterg(ctx, npw, npwx, nvec, nvecx, npol, C_LOC(evc), ethr, MERGE(1, 0, uspp), C_LOC(e), &
                                 C_LOC(btype), C_LOC(notcnv), MERGE(1, 0, lrot), C_LOC(dav_iter), C_LOC(nhpsi)), 'cegterg')
 END SUBROUTINE cegterg_qeb

@@ -220,7 +220,8 @@ int qeb_sum_band_rho_nc(qeb_ctx* ctx, int lda, int n, int m, const void* evc, co
  *
  * g_psi(lda,n,m,npol,psi,e)  PW/src/g_psi.f90:10-70 (TEST_NEW_PRECONDITIONING branch, the one the file defines):
  * psi(i,k) /= 0.5 (1 + x + sqrt(1 + (x-1)^2)), x = h_diag(i) - e(k) s_diag(i); h_diag/s_diag = g_psi_mod
- * (set once per k-point with qeb_set_g_psi_diag). */
+ * (set once per k-point with qeb_set_g_psi_diag). npol = 2: psi(lda,npol,m), h_diag / s_diag (lda,npol), i.e.
+ * qeb_set_g_psi_diag with n = lda*npol (:44-62). */
 int qeb_set_g_psi_diag(qeb_ctx* ctx, int n, const double* h_diag, const double* s_diag);
 int qeb_g_psi(qeb_ctx* ctx, int lda, int n, int m, int npol, void* psi, const double* e);
 /* ew(k) = <a_k|b_k> over n plane waves: MYDDOT(2*npw, a_k, b_k) (cegterg.f90:421); Gamma: 2*dot - a(1)b(1) when
@@ -255,8 +256,10 @@ int qeb_h_psi_multi(int nk, qeb_ctx* const* ctxs, const int* lda, const int* n, 
  * reduced matrices stay in device memory for the whole solve; `diaghg` is cusolverDnZhegvd / Dsygvd (libcusolver is
  * opened at run time, QEB_CUSOLVER_LIB overrides the name). evc (npwx x nvec, INOUT) may be a host or a device pointer;
  * e (nvec, OUT), btype (nvec, IN: 1 = occupied, threshold ethr; 0 = empty, threshold max(5 ethr, 1e-5)), notcnv,
- * dav_iter, nhpsi (OUT) are host data. One band group, serial diagonalisation, npol = 1; other cases return an error
- * and the Fortran shim keeps the reference routine for them. */
+ * dav_iter, nhpsi (OUT) are host data. npol = 2 (qeb_cegterg only): spinors evc(npwx*npol, nvec) with zero pad rows, the
+ * operators are qeb_h_psi_nc / qeb_s_psi_nc, the products run over kdim = npwx*npol rows (cegterg.f90:131-142) and the
+ * preconditioner diagonals are h_diag(npwx,npol), s_diag(npwx,npol) (qeb_set_g_psi_diag with n = npwx*npol). One band
+ * group, serial diagonalisation; other cases return an error and the Fortran shim keeps the reference routine for them. */
 int qeb_cegterg(qeb_ctx* ctx, int npw, int npwx, int nvec, int nvecx, int npol, void* evc, double ethr, int uspp, double* e,
                 const int* btype, int* notcnv, int lrot, int* dav_iter, int* nhpsi);
 int qeb_regterg(qeb_ctx* ctx, int npw, int npwx, int nvec, int nvecx, void* evc, double ethr, int uspp, double* e,

@@ -41,18 +41,32 @@ def g_psi(psi, e, n, h_diag, s_diag):
     psi[:, :n] /= denm
 
 
+def g_psi_nc(psi, e, n, lda, h_diag, s_diag):
+    """g_psi with npol = 2 (PW/src/g_psi.f90:44-62): psi (m, 2*lda), h_diag / s_diag (2, lda) = Fortran (npwx, npol)"""
+    for ipol in range(2):
+        x = h_diag[ipol][None, :n] - e[:, None] * s_diag[ipol][None, :n]
+        denm = 0.5 * (1.0 + x + np.sqrt(1.0 + (x - 1.0) * (x - 1.0)))
+        psi[:, ipol * lda:ipol * lda + n] /= denm
+
+
 def davidson(h_op, s_op, g_op, npw, npwx, nvec, nvecx, evc, ethr, uspp, btype, lrot=False, gamma=False, gstart=1,
-             maxter=MAXTER):
+             maxter=MAXTER, npol=1):
     """returns (e, evc, notcnv, dav_iter, nhpsi); evc is also updated in place.
 
-    h_op(psi) -> hpsi, s_op(psi) -> spsi on (m, npwx) blocks; g_op(psi, e) preconditions in place."""
+    h_op(psi) -> hpsi, s_op(psi) -> spsi on (m, npwx*npol) blocks; g_op(psi, e) preconditions in place.
+    npol = 2 (noncollinear spinors): kdim = kdmx = npwx*npol, i.e. the products run over the pad rows too
+    (cegterg.f90:131-142)."""
     if nvec > nvecx // 2:
         raise ValueError("nvecx is too small")  # cegterg.f90:125
     empty_ethr = max(ethr * 5.0, 1e-5)  # :128
     dt = np.float64 if gamma else np.complex128
-    psi = np.zeros((nvecx, npwx), complex)
-    hpsi = np.zeros((nvecx, npwx), complex)
-    spsi = np.zeros((nvecx, npwx), complex) if uspp else None
+    npw1 = npw  # plane waves of one component
+    kdmx = npwx * npol
+    if npol != 1:
+        npw = kdmx  # kdim
+    psi = np.zeros((nvecx, kdmx), complex)
+    hpsi = np.zeros((nvecx, kdmx), complex)
+    spsi = np.zeros((nvecx, kdmx), complex) if uspp else None
     hc = np.zeros((nvecx, nvecx), dt)
     sc = np.zeros((nvecx, nvecx), dt)
     vc = np.zeros((nvecx, nvecx), dt)
@@ -104,9 +118,12 @@ def davidson(h_op, s_op, g_op, npw, npwx, nvec, nvecx, evc, ethr, uspp, btype, l
         psi[new, :npw] = vc[:nbase, :notcnv].T @ sb[:nbase, :npw]
         psi[new, :npw] *= -ew[new, None]
         psi[new, :npw] += vc[:nbase, :notcnv].T @ hpsi[:nbase, :npw]
-        psi[new, npw:] = 0.0  # :400
+        psi[new, npw1:npwx] = 0.0  # :400
+        if npol == 2:
+            psi[new, npwx + npw1:] = 0.0  # :401
         g_op(psi[new], ew[new])  # :407
-        # normalise the correction vectors (:415-460; regterg.f90:358-361)
+        # normalise the correction vectors (:415-460; regterg.f90:358-361); npol = 2: both components (:428-434), whose
+        # pad rows are zero here
         nrm = np.einsum("ij,ij->i", np.conj(psi[new, :npw]), psi[new, :npw]).real
         if gamma:
             nrm = 2.0 * nrm

@@ -24,16 +24,23 @@ int qeb_g_psi(qeb_ctx* c, int lda, int n, int m, int npol, void* psi, const doub
 {
     if (!c) return 1;
     QEB_CUDA(c, cudaSetDevice(c->device));
-    if (npol != 1) QEB_FAIL(c, 91, "qeb_g_psi: npol = 2 (noncollinear) is routed to the reference routine by the shim");
+    if (npol != 1 && npol != 2) QEB_FAIL(c, 91, "qeb_g_psi: npol must be 1 or 2");
     if (n < 1 || lda < n || m < 0 || !psi || !e) QEB_FAIL(c, 91, "qeb_g_psi: bad arguments");
     if (c->gpsi_n < n) QEB_FAIL(c, 92, "qeb_g_psi: qeb_set_g_psi_diag has not been called for this n");
+    // npol = 2: the diagonals are h_diag(npwx, npol), s_diag(npwx, npol) with npwx = lda, set with n = npwx*npol
+    if (npol == 2 && c->gpsi_n != 2 * lda)
+        QEB_FAIL(c, 92, "qeb_g_psi: npol = 2 needs qeb_set_g_psi_diag with n = 2*lda (h_diag(npwx,npol), s_diag(npwx,npol))");
     if (!is_device_ptr(psi)) QEB_FAIL(c, 93, "qeb_g_psi: psi must be a device pointer (the Davidson work arrays live on the device)");
     if (m == 0) return 0;
     const void* ed;
     int rc = stage_in(c, e, (size_t)m * 8, c->dav_small_d, &ed);
     if (rc) return rc;
-    QEB_CUDA(c, launch_g_psi(lda, n, m, (cplx*)psi, (const double*)ed, (const double*)c->gpsi_d.p,
-                             (const double*)c->gpsi_d.p + c->gpsi_n, c->stream));
+    if (npol == 2)
+        QEB_CUDA(c, launch_g_psi_nc(lda, n, m, (cplx*)psi, (const double*)ed, (const double*)c->gpsi_d.p,
+                                    (const double*)c->gpsi_d.p + c->gpsi_n, c->stream));
+    else
+        QEB_CUDA(c, launch_g_psi(lda, n, m, (cplx*)psi, (const double*)ed, (const double*)c->gpsi_d.p,
+                                 (const double*)c->gpsi_d.p + c->gpsi_n, c->stream));
     if (!is_device_ptr(e)) QEB_CUDA(c, cudaStreamSynchronize(c->stream));
     return finish(c);
 }

@@ -24,6 +24,30 @@ cudaError_t launch_g_psi(int lda, int n, int m, cplx* psi, const double* e, cons
     return cudaGetLastError();
 }
 
+// npol = 2 (g_psi.f90:44-62): psi(lda, 2, m), h_diag / s_diag (lda, 2); column j of the (lda, 2m) view is component
+// j & 1 of band j >> 1
+__global__ void k_g_psi_nc(int lda, int n, int m, cplx* __restrict__ psi, const double* __restrict__ e,
+                           const double* __restrict__ h_diag, const double* __restrict__ s_diag)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= n || j >= 2 * m) return;
+    const int ipol = j & 1, k = j >> 1;
+    const double x = h_diag[(size_t)ipol * lda + i] - e[k] * s_diag[(size_t)ipol * lda + i];
+    const double denm = 0.5 * (1.0 + x + sqrt(1.0 + (x - 1.0) * (x - 1.0)));
+    cplx* p = psi + (size_t)j * lda + i;
+    const cplx v = *p;
+    *p = mk(v.x / denm, v.y / denm);
+}
+
+cudaError_t launch_g_psi_nc(int lda, int n, int m, cplx* psi, const double* e, const double* h_diag, const double* s_diag,
+                            cudaStream_t st)
+{
+    if (n <= 0 || m <= 0) return cudaSuccess;
+    k_g_psi_nc<<<dim3((n + 255) / 256, 2 * m), 256, 0, st>>>(lda, n, m, psi, e, h_diag, s_diag);
+    return cudaGetLastError();
+}
+
 __global__ void __launch_bounds__(256) k_col_dot(int n, const cplx* __restrict__ a, int lda, const cplx* __restrict__ b,
                                                  int ldb, int gamma, int gstart, double* __restrict__ out)
 {

@@ -203,13 +203,24 @@ static int dav_solve(qeb_ctx* c, int npw, int npwx, int nvec, int nvecx, int npo
     if (!c) return 1;
     QEB_CUDA(c, cudaSetDevice(c->device));
     if (!c->have_k) QEB_FAIL(c, 60, std::string(who) + ": qeb_set_kpoint has not been called");
-    if (npol != 1) QEB_FAIL(c, 110, std::string(who) + ": npol = 2 is not built (the shim keeps the reference routine for spinors)");
+    if (npol != 1 && npol != 2) QEB_FAIL(c, 110, std::string(who) + ": npol must be 1 or 2");
+    if (npol == 2 && c->gamma) QEB_FAIL(c, 110, std::string(who) + ": npol = 2 on a gamma_only grid");
     if (c->dist && c->DH.nproc > 1)
         QEB_FAIL(c, 111, std::string(who) + ": slab-distributed grids are not built (mp_sum of the reduced matrices over intra_bgrp_comm)");
     if (npw != c->npw || npwx < npw || nvec < 1 || !evc || !e || !btype)
         QEB_FAIL(c, 112, std::string(who) + ": bad arguments (npw must be the npw of qeb_set_kpoint)");
     if (nvec > nvecx / 2) QEB_FAIL(c, 113, std::string(who) + ": nvecx is too small");  // cegterg.f90:125
-    if (c->gpsi_n < npw) QEB_FAIL(c, 114, std::string(who) + ": no preconditioner diagonals (qeb_set_g_psi_diag)");
+    if (npol == 1 ? c->gpsi_n < npw : c->gpsi_n != 2 * npwx)
+        QEB_FAIL(c, 114, std::string(who) + ": no preconditioner diagonals (qeb_set_g_psi_diag; npol = 2: n = npwx*npol)");
+    // cegterg.f90:131-142: spinors are (npwx*npol) long and every product runs over the pad rows too
+    const int kdim = npol == 1 ? npw : npwx * npol;
+    const int kdmx = npwx * npol;
+    auto apply_h = [&](const cplx* x, cplx* hx, int m) {
+        return npol == 1 ? qeb_h_psi(c, npwx, npw, m, x, hx) : qeb_h_psi_nc(c, npwx, npw, m, x, hx);
+    };
+    auto apply_s = [&](const cplx* x, cplx* sx, int m) {
+        return npol == 1 ? qeb_s_psi(c, npwx, npw, m, x, sx) : qeb_s_psi_nc(c, npwx, npw, m, x, sx);
+    };
     const SolverApi& A = solver_api();
     if (!A.ok) QEB_FAIL(c, 115, std::string(who) + ": " + A.why);
     if (!c->solver) c->solver = new qeb_solver_state();
@@ -218,7 +229,7 @@ static int dav_solve(qeb_ctx* c, int npw, int npwx, int nvec, int nvecx, int npo
     A.SetStream(B.handle, c->stream);
     const bool cp = !c->gamma;
     const size_t el = cp ? 16 : 8;
-    const size_t col = (size_t)npwx * 16;
+    const size_t col = (size_t)kdmx * 16;
     QEB_CUDA(c, B.psi.ensure(col * nvecx));
     QEB_CUDA(c, B.hpsi.ensure(col * nvecx));
     if (uspp) QEB_CUDA(c, B.spsi.ensure(col * nvecx));
@@ -250,7 +261,7 @@ static int dav_solve(qeb_ctx* c, int npw, int npwx, int nvec, int nvecx, int npo
         bool a;
         ~Restore() { c->async = a; }
     } restore{c, was_async};
-    auto colp = [&](cplx* base, int k) { return base + (size_t)k * npwx; };
+    auto colp = [&](cplx* base, int k) { return base + (size_t)k * kdmx; };
     auto red_at = [&](DevBuf& b, int row, int colm) { return (char*)b.p + ((size_t)colm * nvecx + row) * el; };
     const dim3 tb(256);
     int rc;
@@ -264,12 +275,12 @@ static int dav_solve(qeb_ctx* c, int npw, int npwx, int nvec, int nvecx, int npo
     QEB_CUDA(c, cudaMemsetAsync(B.vc.p, 0, red, c->stream));
     QEB_CUDA(c, cudaMemcpyAsync(psi, evc_d, col * nvec, cudaMemcpyDeviceToDevice, c->stream));  // :190
     if (!cp && c->gstart == 2) QEB_CUDA(c, launch_zero_im_g0(psi, npwx, nvec, c->stream));       // regterg.f90:174
-    if ((rc = qeb_h_psi(c, npwx, npw, nvec, psi, hpsi))) return rc;                               // :192
+    if ((rc = apply_h(psi, hpsi, nvec))) return rc;                                          // :192
     nhpsi += nvec;
-    if (uspp && (rc = qeb_s_psi(c, npwx, npw, nvec, psi, spsi))) return rc;                      // :196
+    if (uspp && (rc = apply_s(psi, spsi, nvec))) return rc;                                 // :196
     // hc = psi^H hpsi, sc = psi^H spsi (:209-229)
-    if ((rc = qeb_dav_gemm_cn(c, npw, psi, npwx, nbase, hpsi, npwx, nbase, B.hc.p, nvecx))) return rc;
-    if ((rc = qeb_dav_gemm_cn(c, npw, psi, npwx, nbase, sb, npwx, nbase, B.sc.p, nvecx))) return rc;
+    if ((rc = qeb_dav_gemm_cn(c, kdim, psi, kdmx, nbase, hpsi, kdmx, nbase, B.hc.p, nvecx))) return rc;
+    if ((rc = qeb_dav_gemm_cn(c, kdim, psi, kdmx, nbase, sb, kdmx, nbase, B.sc.p, nvecx))) return rc;
     auto symmetrise = [&](int lo, int hi) {
         const dim3 g((hi + 255) / 256, hi);
         if (cp) {
@@ -324,25 +335,25 @@ static int dav_solve(qeb_ctx* c, int npw, int npwx, int nvec, int nvecx, int npo
         const int nb1 = nbase;
         cplx* pnew = colp(psi, nb1);
         // ( H - e S ) |psi> of the unconverged roots (:340-400)
-        if ((rc = qeb_dav_gemm_nn(c, npw, sb, npwx, nbase, B.vc.p, nvecx, notcnv, pnew, npwx, 0))) return rc;
-        k_dav_scale_cols<0><<<dim3((npw + 255) / 256, notcnv), tb, 0, c->stream>>>(pnew, npwx, npw, notcnv, ew_d + nb1);
+        if ((rc = qeb_dav_gemm_nn(c, kdim, sb, kdmx, nbase, B.vc.p, nvecx, notcnv, pnew, kdmx, 0))) return rc;
+        k_dav_scale_cols<0><<<dim3((kdim + 255) / 256, notcnv), tb, 0, c->stream>>>(pnew, kdmx, kdim, notcnv, ew_d + nb1);
         QEB_CUDA(c, cudaGetLastError());
-        if ((rc = qeb_dav_gemm_nn(c, npw, hpsi, npwx, nbase, B.vc.p, nvecx, notcnv, pnew, npwx, 1))) return rc;
-        if (npwx > npw) QEB_CUDA(c, launch_zero_pad_rows(pnew, npwx, npw, notcnv, c->stream));  // :400
+        if ((rc = qeb_dav_gemm_nn(c, kdim, hpsi, kdmx, nbase, B.vc.p, nvecx, notcnv, pnew, kdmx, 1))) return rc;
+        if (npwx > npw) QEB_CUDA(c, launch_zero_pad_rows(pnew, npwx, npw, npol * notcnv, c->stream));  // :400-401
         // approximate inverse iteration, then normalisation (:407-460)
-        if ((rc = qeb_g_psi(c, npwx, npw, notcnv, 1, pnew, ew_d + nb1))) return rc;
-        if ((rc = qeb_col_dot(c, npw, notcnv, pnew, npwx, pnew, npwx, ew_d))) return rc;
-        k_dav_scale_cols<1><<<dim3((npw + 255) / 256, notcnv), tb, 0, c->stream>>>(pnew, npwx, npw, notcnv, ew_d);
+        if ((rc = qeb_g_psi(c, npwx, npw, notcnv, npol, pnew, ew_d + nb1))) return rc;
+        if ((rc = qeb_col_dot(c, kdim, notcnv, pnew, kdmx, pnew, kdmx, ew_d))) return rc;  // npol = 2: pad rows are zero (:428-434)
+        k_dav_scale_cols<1><<<dim3((kdim + 255) / 256, notcnv), tb, 0, c->stream>>>(pnew, kdmx, kdim, notcnv, ew_d);
         QEB_CUDA(c, cudaGetLastError());
         if (!cp && c->gstart == 2) QEB_CUDA(c, launch_zero_im_g0(pnew, npwx, notcnv, c->stream));  // regterg.f90:375
         // H and S on the new vectors (:465-467)
-        if ((rc = qeb_h_psi(c, npwx, npw, notcnv, pnew, colp(hpsi, nb1)))) return rc;
+        if ((rc = apply_h(pnew, colp(hpsi, nb1), notcnv))) return rc;
         nhpsi += notcnv;
-        if (uspp && (rc = qeb_s_psi(c, npwx, npw, notcnv, pnew, colp(spsi, nb1)))) return rc;
+        if (uspp && (rc = apply_s(pnew, colp(spsi, nb1), notcnv))) return rc;
         // rows nb1.. of the reduced matrices (:478-499), then the Hermitian fill (:520-533)
         const int tot = nbase + notcnv;
-        if ((rc = qeb_dav_gemm_cn(c, npw, colp(hpsi, nb1), npwx, notcnv, psi, npwx, tot, red_at(B.hc, nb1, 0), nvecx))) return rc;
-        if ((rc = qeb_dav_gemm_cn(c, npw, colp(sb, nb1), npwx, notcnv, psi, npwx, tot, red_at(B.sc, nb1, 0), nvecx))) return rc;
+        if ((rc = qeb_dav_gemm_cn(c, kdim, colp(hpsi, nb1), kdmx, notcnv, psi, kdmx, tot, red_at(B.hc, nb1, 0), nvecx))) return rc;
+        if ((rc = qeb_dav_gemm_cn(c, kdim, colp(sb, nb1), kdmx, notcnv, psi, kdmx, tot, red_at(B.sc, nb1, 0), nvecx))) return rc;
         nbase = tot;
         QEB_CUDA(c, symmetrise(nb1, nbase));
         if ((rc = dav_diaghg(c, B, nbase, nvec, nvecx, cp, ew.data()))) return rc;  // :545
@@ -354,16 +365,16 @@ static int dav_solve(qeb_ctx* c, int npw, int npwx, int nvec, int nvecx, int npo
             e[i] = ew[i];
         }
         if (notcnv == 0 || nbase + notcnv > nvecx || dav_iter == 20) {  // :576-669
-            if ((rc = qeb_dav_gemm_nn(c, npw, psi, npwx, nbase, B.vc.p, nvecx, nvec, evc_d, npwx, 0))) return rc;  // :588
+            if ((rc = qeb_dav_gemm_nn(c, kdim, psi, kdmx, nbase, B.vc.p, nvecx, nvec, evc_d, kdmx, 0))) return rc;  // :588
             if (notcnv == 0 || dav_iter == 20) break;
             // refresh psi, H psi, S psi (:600-632); the columns nvec.. of psi are the scratch, as in the reference
             QEB_CUDA(c, cudaMemcpyAsync(psi, evc_d, col * nvec, cudaMemcpyDeviceToDevice, c->stream));
             if (uspp) {
-                if ((rc = qeb_dav_gemm_nn(c, npw, spsi, npwx, nbase, B.vc.p, nvecx, nvec, colp(psi, nvec), npwx, 0))) return rc;
-                QEB_CUDA(c, cudaMemcpy2DAsync(spsi, col, colp(psi, nvec), col, (size_t)npw * 16, nvec, cudaMemcpyDeviceToDevice, c->stream));
+                if ((rc = qeb_dav_gemm_nn(c, kdim, spsi, kdmx, nbase, B.vc.p, nvecx, nvec, colp(psi, nvec), kdmx, 0))) return rc;
+                QEB_CUDA(c, cudaMemcpy2DAsync(spsi, col, colp(psi, nvec), col, (size_t)kdim * 16, nvec, cudaMemcpyDeviceToDevice, c->stream));
             }
-            if ((rc = qeb_dav_gemm_nn(c, npw, hpsi, npwx, nbase, B.vc.p, nvecx, nvec, colp(psi, nvec), npwx, 0))) return rc;
-            QEB_CUDA(c, cudaMemcpy2DAsync(hpsi, col, colp(psi, nvec), col, (size_t)npw * 16, nvec, cudaMemcpyDeviceToDevice, c->stream));
+            if ((rc = qeb_dav_gemm_nn(c, kdim, hpsi, kdmx, nbase, B.vc.p, nvecx, nvec, colp(psi, nvec), kdmx, 0))) return rc;
+            QEB_CUDA(c, cudaMemcpy2DAsync(hpsi, col, colp(psi, nvec), col, (size_t)kdim * 16, nvec, cudaMemcpyDeviceToDevice, c->stream));
             nbase = nvec;
             QEB_CUDA(c, cudaMemcpyAsync(ew_d, e, (size_t)nvec * 8, cudaMemcpyHostToDevice, c->stream));
             const dim3 g((nbase + 255) / 256, nbase);

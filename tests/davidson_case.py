@@ -78,3 +78,68 @@ def dense_eigenvalues(case, nvec):
     S = to_x(case["s_op"](basis)).T
     H, S = 0.5 * (H + H.T), 0.5 * (S + S.T)
     return sl.eigh(H, S, eigvals_only=True)[:nvec]
+
+
+def build_nc(name, nvec, seed=21, nh=(4, 4)):
+    """the same for noncollinear spinors (npol = 2): H = h_psi_nc with a magnetic 2x2 potential and a Hermitian
+    deeq_nc, S = s_psi_nc with qq_at on the spin diagonal; vectors are (2*lda) long, pad rows zero"""
+    d = D.config_descriptor(name)
+    inp = R.synthetic_inputs(d, 2 * nvec, list(nh), seed=seed, poison=False)
+    lda, n = inp["lda"], inp["n"]
+    rng = np.random.default_rng(200 + seed)
+    nh_at, ofs, vkb = inp["nh_at"], inp["ofsbeta"], inp["vkb"]
+    nhm = int(np.max(nh_at))
+    v4 = np.ascontiguousarray(rng.uniform(-1.0, 1.0, (4, d.nnr)))
+    v4[0] = inp["vrs"]
+    v4[1:] *= 0.3
+    dnc = R.synthetic_deeq_nc(nh_at, seed=seed)
+    qq = np.zeros((len(nh_at), nhm, nhm))
+    for a, k in enumerate(nh_at):
+        A = rng.uniform(-1, 1, (k, k))
+        qq[a, :k, :k] = 0.2 * (A @ A.T)
+    qnc = np.zeros((4, len(nh_at), nhm, nhm), dtype=np.complex128)
+    qnc[0] = qq
+    qnc[3] = qq
+
+    def h_op(p):
+        out, _ = R.h_psi_nc(d, lda, n, p.shape[0], p, v4, vkb, dnc, nh_at, ofs)
+        return out
+
+    def s_op(p):
+        _, becp = R.h_psi_nc(d, lda, n, p.shape[0], p, v4, vkb, dnc, nh_at, ofs)
+        return R.s_psi_nc(lda, n, p.shape[0], p, becp, vkb, qnc, nh_at, ofs)
+
+    # h_diag(npwx, npol), s_diag(npwx, npol) (usnldiag.f90 with the spin-diagonal blocks of deeq_nc)
+    h_diag = np.zeros((2, lda))
+    s_diag = np.ones((2, lda))
+    for ipol in range(2):
+        h_diag[ipol, :n] = np.asarray(d.g2kin[:n], dtype=float) + v4[0].mean()
+        for a, k in enumerate(nh_at):
+            for ih in range(k):
+                b = np.abs(vkb[ofs[a] + ih, :n]) ** 2
+                h_diag[ipol, :n] += dnc[3 * ipol, a, ih, ih].real * b
+                s_diag[ipol, :n] += qq[a, ih, ih] * b
+
+    def g_op(p, e):
+        DR.g_psi_nc(p, e, n, lda, h_diag, s_diag)
+
+    evc = np.ascontiguousarray(inp["psi"]).reshape(nvec, 2 * lda).copy()
+    evc[:, n:lda] = 0.0
+    evc[:, lda + n:] = 0.0
+    return dict(d=d, inp=inp, lda=lda, n=n, v4=v4, dnc=dnc, qnc=qnc, h_op=h_op, s_op=s_op, g_op=g_op, h_diag=h_diag,
+                s_diag=s_diag, evc=evc)
+
+
+def dense_eigenvalues_nc(case, nvec):
+    import scipy.linalg as sl
+
+    n, lda = case["n"], case["lda"]
+    rows = np.concatenate([np.arange(n), lda + np.arange(n)])
+    eye = np.zeros((2 * n, 2 * lda), complex)
+    eye[np.arange(2 * n), rows] = 1.0
+    H = case["h_op"](eye)[:, rows].T
+    S = case["s_op"](eye)[:, rows].T
+    assert np.abs(H - H.conj().T).max() < 1e-10 * np.abs(H).max()
+    assert np.abs(S - S.conj().T).max() < 1e-10 * np.abs(S).max()
+    H, S = 0.5 * (H + H.conj().T), 0.5 * (S + S.conj().T)
+    return sl.eigh(H, S, eigvals_only=True)[:nvec]

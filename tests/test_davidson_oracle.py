@@ -44,3 +44,25 @@ def test_davidson_restatement_lrot_and_empty_bands():
     assert notcnv == 0
     assert np.abs(e[:2] - w[:2]).max() < 1e-7
     assert np.abs(e - w).max() < 1e-3
+
+
+def test_davidson_restatement_npol2_vs_dense():
+    """npol = 2 (cegterg.f90:131-142: kdim = kdmx = npwx*npol; :401 pad rows of the second component; :428-434 norm over
+    both components; g_psi.f90:44-62 with h_diag(npwx, npol)) against a dense eigensolve of the spinor H and S"""
+    from davidson_case import build_nc, dense_eigenvalues_nc
+
+    nvec = 4
+    c = build_nc("si2_small", nvec)
+    n, lda = c["n"], c["lda"]
+    evc = c["evc"].copy()
+    for ntry in range(4):
+        e, evc, notcnv, it, nhpsi = DR.davidson(c["h_op"], c["s_op"], c["g_op"], n, lda, nvec, 4 * nvec, evc, 1e-11, True,
+                                                np.ones(nvec, int), npol=2, lrot=ntry > 0)
+        if notcnv == 0:
+            break
+    w = dense_eigenvalues_nc(c, nvec)
+    assert notcnv == 0
+    assert np.abs(e - w).max() < 1e-9 * max(1.0, np.abs(w).max())
+    assert np.all(evc[:, n:lda] == 0) and np.all(evc[:, lda + n:] == 0)
+    r = c["h_op"](evc) - e[:, None] * c["s_op"](evc)
+    assert np.abs(r).max() < 1e-5
